@@ -1,0 +1,172 @@
+/*
+ * msr.h -- C ABI of libmsr.so, the B200 (sm_100a) retrieval-scoring library.
+ *
+ * The reference (cjc20000323/mllm_sparse_retrieval) has no FFI layer of its own: its search step calls two
+ * third-party engines and one in-tree pure-Python function.  Each entry point below names the reference call
+ * site it replaces; INTEGRATION.md shows the ctypes stub a maintainer would add.
+ *
+ *   msr_sparse_*   replaces  pyserini LuceneImpactSearcher(<sparse_index>/index).batch_search(...)
+ *                            called at /root/reference/src/search.py:273-275 and :86-87 (sparse_search, :85-99);
+ *                            index built offline by scripts/sparse_index.sh:12-18.
+ *   msr_dense_*    replaces  tevatron FaissFlatSearcher(...).add/search/batch_search
+ *                            called at /root/reference/src/search.py:232,237 and :57,59 (search_queries, :55-63),
+ *                            incl. the fp16 GPU clone at :254-270.
+ *   msr_fuse       replaces  hybrid.fuse  /root/reference/src/hybrid.py:32-53 fed by get_run_dict search.py:66-82
+ *                            (call site search.py:455-461).
+ *   msr_topk_merge           the per-GPU list merge of the doc-sharded layout (FAISS IndexShards precedent,
+ *                            search.py:265-270); inputs are what one NCCL all-gather delivers.
+ *
+ * Conventions: every function returns 0 (MSR_OK) or a negative msr_status; msr_last_error() returns a
+ * thread-local message.  No exceptions cross the boundary.  Handles are opaque, owned by the library, freed
+ * by *_destroy, and immutable after build except for an internal workspace: concurrent searches on ONE
+ * handle must be serialised by the caller (one handle per GPU per stream).  `stream` is a cudaStream_t passed
+ * as void* (NULL = legacy default stream).  Pointers are plain; `where` says whether a call's data pointers
+ * are host (MSR_HOST) or device (MSR_DEVICE) memory.  With MSR_DEVICE the call is asynchronous on `stream`;
+ * with MSR_HOST the library stages through device memory and returns after the results are in the host buffers.
+ * There is NO CPU fallback: every entry point fails with MSR_ERR_CUDA when no sm_100 device is usable.
+ */
+#ifndef MSR_H_
+#define MSR_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    MSR_OK = 0,
+    MSR_ERR_INVALID = -1,   /* bad argument */
+    MSR_ERR_CUDA = -2,      /* CUDA runtime error / no usable device */
+    MSR_ERR_RANGE = -3,     /* value outside the supported exact-arithmetic range (see msr_sparse_search) */
+    MSR_ERR_NOMEM = -4
+} msr_status;
+
+enum { MSR_HOST = 0, MSR_DEVICE = 1 };
+
+#define MSR_MAX_K 4096u            /* largest k / depth any search or merge accepts */
+
+typedef struct msr_sparse_index msr_sparse_index;
+typedef struct msr_dense_index msr_dense_index;
+
+int msr_version(void);
+const char* msr_last_error(void);
+/* number of kernels launched by this library in this process so far (bench.py's gpu_launches) */
+uint64_t msr_kernel_launches(void);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Sparse impact index (kernels (a)+(b)).
+ *
+ * Input = canonical term-major CSR of ONE shard of the collection: postings of term t are
+ * docids[indptr[t] .. indptr[t+1]) strictly ascending LOCAL doc ids in [0,n_docs) with impacts[] >= 1
+ * (tf(t,d) = vector[t], rule S1).  Local doc id d stands for global internal id doc_base + d; internal ids are
+ * ranks of the external docid strings in UTF-8 byte order, so "smaller id wins" is Anserini's tie-break (S8).
+ * n_docs_global / df_global[n_terms] are the collection-wide N and document frequencies used by the query
+ * term filter S5 (keep t iff 0 < df and ln(N/(df+1)) > 0); df_global == NULL means "this shard is the
+ * whole collection".  tile_docs = 0 picks the default doc-range tile (accumulators of one tile live in shared
+ * memory); otherwise 1..53248.
+ * The library re-buckets the postings on the device into its tiled layout and keeps no reference to the
+ * caller's arrays.  nnz must be < 2^32.
+ */
+int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_terms,
+                           const uint64_t* indptr, const uint32_t* docids, const uint16_t* impacts,
+                           uint32_t n_docs_global, const uint32_t* df_global, int32_t doc_base,
+                           uint32_t tile_docs, int where, void* stream, msr_sparse_index** out);
+int msr_sparse_index_destroy(msr_sparse_index* h);
+/* n_docs, n_terms, n_tiles, tile_docs, nnz(lo), nnz(hi), device, bytes-resident(lo), bytes-resident(hi) */
+int msr_sparse_index_info(const msr_sparse_index* h, uint32_t info[9]);
+
+/*
+ * Batched impact search: for query q with terms q_terms[q_indptr[q]..q_indptr[q+1]) and integer weights
+ * q_weights[] (duplicates add, weight 0 ignored, term ids >= n_terms ignored):
+ *     score(q,d) = float32( sum_t float32(w_t * tf(t,d)) )                       (rule S6)
+ * over kept terms (S5); hits are docs with score > 0 (S7), ordered by score desc, internal id asc (S8).
+ * Outputs are [nq,k] row-major: row q = out_counts[q] hits then padding (score 0, doc -1).  out_docs are
+ * GLOBAL internal ids (doc_base added).
+ * Exact-arithmetic range: every weight <= 65535 and sum_t w_t*max_impact(t) < 2^31 per query, otherwise the
+ * query's row is returned empty and the call reports MSR_ERR_RANGE (MSR_HOST) or sets the sticky status
+ * readable with msr_sparse_index_status (MSR_DEVICE).  k <= MSR_MAX_K.
+ */
+int msr_sparse_search(msr_sparse_index* h, uint32_t nq,
+                      const uint64_t* q_indptr, const uint32_t* q_terms, const uint32_t* q_weights,
+                      uint32_t k, float* out_scores, int32_t* out_docs, uint32_t* out_counts,
+                      int where, void* stream);
+/* Synchronises `stream`, returns and clears the sticky device-side status of earlier MSR_DEVICE searches. */
+int msr_sparse_index_status(msr_sparse_index* h, void* stream);
+/*
+ * Algorithmic work of a query batch: *postings = sum_q sum_{t kept} df_shard(t),
+ * *kept_terms = number of kept (query,term) pairs.  Used by bench.py for the roofline numerator.
+ */
+int msr_sparse_query_work(msr_sparse_index* h, uint32_t nq, const uint64_t* q_indptr, const uint32_t* q_terms,
+                          const uint32_t* q_weights, uint64_t* postings, uint64_t* kept_terms,
+                          int where, void* stream);
+
+/*
+ * Per-kernel timing for bench.py's roofline: synchronises `stream`, returns the summed CUDA-event durations (ms)
+ * of the score kernel and of the merge kernel over all launches since the previous call plus their count, then
+ * switches event recording on (enable != 0) or off for later searches.
+ */
+int msr_sparse_profile(msr_sparse_index* h, int enable, double* score_ms, double* merge_ms, uint64_t* launches,
+                       void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Top-k list merge (doc-sharded multi-GPU).
+ * scores/docs are [n_lists, nq, k_in], counts [n_lists, nq] (exactly the layout of an all-gather of per-GPU
+ * results).  Output [nq,k] with the same (score desc, doc asc) order and padding.  Device pointers only.
+ */
+int msr_topk_merge(int device, uint32_t n_lists, uint32_t nq, uint32_t k_in,
+                   const float* scores, const int32_t* docs, const uint32_t* counts,
+                   uint32_t k, float* out_scores, int32_t* out_docs, uint32_t* out_counts, void* stream);
+
+/*
+ * Stand-alone radix-select top-k over dense score rows (kernel (b) on its own): scores [nq, n] row-major
+ * fp32 on the device; output k best per row by (score desc, column asc), columns offset by col_base.
+ * Entries equal to -inf are never returned (counts < k possible).
+ */
+int msr_topk_rows(int device, uint32_t nq, uint32_t n, const float* scores, size_t row_stride,
+                  uint32_t k, int32_t col_base, float* out_scores, int32_t* out_docs, uint32_t* out_counts,
+                  void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Dense flat inner-product index (kernel (c)).
+ * vecs = [n_docs, dim] row-major fp32 (the (reps, lookup) pickle of src/encode.py:386-457 after pickle_load,
+ * search.py:49-52).  The index stores bf16 for the tensor-core pass AND fp32 for the exact re-score.
+ * msr_dense_index_add appends rows (FaissFlatSearcher.add).  Row ids are doc_base + row.
+ */
+int msr_dense_index_create(int device, uint32_t dim, int32_t doc_base, msr_dense_index** out);
+int msr_dense_index_add(msr_dense_index* h, uint32_t n_rows, const float* vecs, int where, void* stream);
+int msr_dense_index_destroy(msr_dense_index* h);
+/* n_docs, dim, device, bytes-resident(lo), bytes-resident(hi) */
+int msr_dense_index_info(const msr_dense_index* h, uint32_t info[5]);
+/*
+ * Exact top-k by inner product: queries [nq, dim] fp32; out_scores fp32 [nq,k] are fp32 dot products
+ * accumulated in a fixed order (|err| <= 1e-6 abs on unit vectors), out_ids int64 [nq,k] (FAISS convention:
+ * -1 / -3.4028235e38 padding when k > n_docs).  Order = score desc, id asc.
+ * mode: 0 = auto, 1 = exact fp32 CUDA-core pass only, 2 = tcgen05 bf16 pass + certified fp32 re-score.
+ */
+int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* queries, uint32_t k,
+                     float* out_scores, int64_t* out_ids, int mode, int where, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Hybrid fusion (kernel (d)) = hybrid.fuse([dense_run, sparse_run], [alpha, 1-alpha]) for a query batch.
+ * Inputs per modality: scores f32 [nq,k_*], docs i32 [nq,k_*] (global internal ids), counts u32 [nq] and
+ * self ids i32 [nq] (the query's own id in the doc id space, or -1): with remove_query != 0 a doc equal to
+ * the self id is dropped AFTER min/max were taken over the full list (get_run_dict, search.py:66-82).
+ * Output row q: the union in the reference's insertion order (dense list order, then sparse-only docs in sparse
+ * list order): out_docs i32 [nq,k_d+k_s], out_scores f64 [nq,k_d+k_s], out_src u8 (1 dense only, 2 sparse only,
+ * 3 both = fuse_statistic's tag, hybrid.py:56-90), out_counts u32 [nq].  w_dense / w_sparse are the reference's
+ * weights [alpha, 1-alpha].  Arithmetic reproduces the reference under NumPy >= 2 bit for bit: float32 for the
+ * dense term and for sums that contain one, float64 for sparse-only docs (rule H3); doc ids must be unique
+ * within a list.  Device pointers only.
+ */
+int msr_fuse(int device, uint32_t nq,
+             uint32_t k_d, const float* d_scores, const int32_t* d_docs, const uint32_t* d_counts,
+             uint32_t k_s, const float* s_scores, const int32_t* s_docs, const uint32_t* s_counts,
+             const int32_t* self_ids, int remove_query, double w_dense, double w_sparse,
+             double* out_scores, int32_t* out_docs, uint8_t* out_src, uint32_t* out_counts, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MSR_H_ */

@@ -1,0 +1,331 @@
+// topk.cu -- kernel (b) stand-alone + list merge.
+//
+//  * topk_merge_kernel: one CTA per query merges n_lists candidate lists (per-tile lists of the sparse scorer,
+//    or the per-GPU lists an NCCL all-gather delivered -- SURVEY.md 8(e)) into the final k by the 64-bit key
+//    (float32 score desc, doc id asc): rounds of "append lists, bitonic-sort in shared memory, keep k".
+//  * topk_rows_kernel: radix-select (11-bit digits on the distance to the row maximum) over a dense fp32 score
+//    row with the same deterministic tie-break; used by the dense path's exact pass and exposed as msr_topk_rows.
+#include "common.cuh"
+
+namespace msr {
+
+constexpr int kMergeThreads = 256;
+
+struct MergeParams {
+    uint32_t nq, n_lists, stride, k, mode;   // mode 0: packed keys [nq][n_lists][stride]; 1: arrays [n_lists][nq][stride]
+    const uint64_t* keys;
+    const float* scores;
+    const int32_t* docs;
+    const uint32_t* cnts;
+    float* out_scores;
+    int32_t* out_docs;
+    uint32_t* out_counts;
+    uint32_t cap;                            // shared-memory capacity in keys (power of two, >= k + stride)
+};
+
+__device__ __forceinline__ uint32_t pow2_ceil(uint32_t x) {
+    uint32_t n = 2;
+    while (n < x) n <<= 1;
+    return n;
+}
+
+__global__ void __launch_bounds__(kMergeThreads)
+topk_merge_kernel(const MergeParams P) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
+    const uint32_t q = blockIdx.x, tid = threadIdx.x;
+    uint32_t fill = 0;
+    for (uint32_t j = 0; j < P.n_lists; ++j) {
+        const size_t li = P.mode == 0 ? (size_t)q * P.n_lists + j : (size_t)j * P.nq + q;
+        const uint32_t c = min(P.cnts[li], P.stride);
+        if (c == 0) continue;
+        if (fill + c > P.cap) {
+            const uint32_t n2 = pow2_ceil(fill);
+            for (uint32_t i = fill + tid; i < n2; i += kMergeThreads) buf[i] = 0;
+            bitonic_sort_desc(buf, n2);
+            fill = min(fill, P.k);
+        }
+        if (P.mode == 0) {
+            const uint64_t* src = P.keys + li * P.stride;
+            for (uint32_t i = tid; i < c; i += kMergeThreads) buf[fill + i] = src[i];
+        } else {
+            const float* ss = P.scores + li * P.stride;
+            const int32_t* dd = P.docs + li * P.stride;
+            for (uint32_t i = tid; i < c; i += kMergeThreads) buf[fill + i] = make_key(ss[i], (uint32_t)dd[i]);
+        }
+        fill += c;
+        __syncthreads();
+    }
+    if (fill > 1) {
+        const uint32_t n2 = pow2_ceil(fill);
+        for (uint32_t i = fill + tid; i < n2; i += kMergeThreads) buf[i] = 0;
+        bitonic_sort_desc(buf, n2);
+    } else {
+        __syncthreads();
+    }
+    const uint32_t n = min(fill, P.k);
+    for (uint32_t r = tid; r < P.k; r += kMergeThreads) {
+        const bool ok = r < n;
+        const uint64_t key = ok ? buf[r] : 0;
+        P.out_scores[(size_t)q * P.k + r] = ok ? key_score(key) : 0.0f;
+        P.out_docs[(size_t)q * P.k + r] = ok ? (int32_t)key_doc(key) : -1;
+    }
+    if (tid == 0) P.out_counts[q] = n;
+}
+
+static int merge_launch(MergeParams P, cudaStream_t s) {
+    uint32_t need = P.k + P.stride;
+    uint64_t total = (uint64_t)P.n_lists * P.stride;
+    uint32_t cap = 2;
+    while (cap < need) cap <<= 1;
+    while (cap < total && cap < 8192) cap <<= 1;
+    if (cap > 8192) { set_error("topk merge: k + k_in = %u exceeds 8192", need); return MSR_ERR_INVALID; }
+    P.cap = cap;
+    const size_t smem = (size_t)cap * 8;
+    static bool attr_set = false;
+    if (!attr_set) {
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(topk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8));
+        attr_set = true;
+    }
+    topk_merge_kernel<<<P.nq, kMergeThreads, smem, s>>>(P);
+    count_launch();
+    MSR_CUDA_CHECK(cudaGetLastError());
+    return MSR_OK;
+}
+
+int topk_merge_keys_launch(uint32_t nq, uint32_t n_lists, uint32_t stride, const uint64_t* keys, const uint32_t* cnts,
+                           uint32_t k, float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s) {
+    MergeParams P{};
+    P.nq = nq; P.n_lists = n_lists; P.stride = stride; P.k = k; P.mode = 0;
+    P.keys = keys; P.cnts = cnts; P.out_scores = out_scores; P.out_docs = out_docs; P.out_counts = out_counts;
+    return merge_launch(P, s);
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// stand-alone row top-k
+// ---------------------------------------------------------------------------------------------------------
+constexpr int kRowThreads = 512;
+constexpr int kRowWarps = kRowThreads / 32;
+constexpr int kRowBins = 2048;
+constexpr int kRowBinBits = 11;
+constexpr int kRowCandMax = 1024;
+
+struct RowsParams {
+    uint32_t nq, n, k;
+    int32_t col_base;
+    const float* scores;
+    size_t row_stride;
+    float* out_scores;
+    int32_t* out_docs;
+    uint32_t* out_counts;
+};
+
+struct RowsSmem {
+    uint32_t hist[kRowBins];
+    uint64_t cand[kRowCandMax];
+    uint32_t wsum[kRowWarps];
+    uint32_t vmax, hits, out_cnt, cand_cnt, sel_b, sel_clt, sel_bcount;
+};
+
+__device__ __forceinline__ uint32_t rows_block_excl_scan(uint32_t v, uint32_t* wsum, uint32_t* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = warp_incl_scan(v, lane);
+    __syncthreads();
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < kRowWarps; ++w) {
+        uint32_t x = wsum[w];
+        if (w < warp) base += x;
+        tot += x;
+    }
+    *total = tot;
+    return base + inc - v;
+}
+
+// key 0 is reserved for "not a candidate" (-inf / NaN are never returned)
+__device__ __forceinline__ uint32_t row_key(float x) { return (x > -INFINITY) ? f2ord(x) : 0u; }
+
+__global__ void __launch_bounds__(kRowThreads)
+topk_rows_kernel(const RowsParams P) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    RowsSmem* S = reinterpret_cast<RowsSmem*>(smem_raw);
+    uint64_t* outk = reinterpret_cast<uint64_t*>(smem_raw + sizeof(RowsSmem));   // pow2_ceil(k) keys
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t q = blockIdx.x;
+    const float* row = P.scores + (size_t)q * P.row_stride;
+    const uint32_t n = P.n;
+    if (tid == 0) { S->vmax = 0; S->hits = 0; S->out_cnt = 0; S->cand_cnt = 0; }
+    __syncthreads();
+    {
+        uint32_t m = 0, h = 0;
+        for (uint32_t i = tid; i < n; i += kRowThreads) {
+            uint32_t kx = row_key(row[i]);
+            m = max(m, kx);
+            h += (kx != 0);
+        }
+        m = warp_reduce_max(m);
+        h = warp_reduce_add(h);
+        if (lane == 0) {
+            if (m) atomicMax(&S->vmax, m);
+            if (h) atomicAdd(&S->hits, h);
+        }
+    }
+    __syncthreads();
+    const uint32_t kmax = S->vmax, hits = S->hits;
+    const uint32_t kq = min(P.k, hits);
+    const uint32_t n2out = pow2_ceil(max(kq, 2u));
+    for (uint32_t i = tid; i < n2out; i += kRowThreads) outk[i] = 0;
+    __syncthreads();
+    if (hits > 0 && hits <= P.k) {
+        for (uint32_t i = tid; i < n; i += kRowThreads) {
+            float x = row[i];
+            if (row_key(x)) outk[atomicAdd(&S->out_cnt, 1u)] = make_key(x, (uint32_t)(P.col_base + (int32_t)i));
+        }
+    } else if (hits > 0) {
+        uint32_t remaining = kq, sh_prev = 32 - __clz(kmax), pref = 0, s = 0, cand_count = 0;
+        for (;;) {
+            s = sh_prev > kRowBinBits ? sh_prev - kRowBinBits : 0;
+            const uint32_t width = sh_prev - s;
+            for (uint32_t i = tid; i < kRowBins; i += kRowThreads) S->hist[i] = 0;
+            __syncthreads();
+            for (uint32_t i = tid; i < n; i += kRowThreads) {
+                uint32_t kx = row_key(row[i]);
+                if (kx) {
+                    uint32_t d = kmax - kx;
+                    uint32_t hi = sh_prev >= 32 ? 0u : (d >> sh_prev);
+                    if (hi == pref) atomicAdd(&S->hist[(d >> s) & ((1u << width) - 1u)], 1u);
+                }
+            }
+            __syncthreads();
+            {
+                uint32_t h4[4], ls = 0;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) { h4[j] = S->hist[tid * 4 + j]; ls += h4[j]; }
+                uint32_t total;
+                uint32_t ex = rows_block_excl_scan(ls, S->wsum, &total);
+#pragma unroll
+                for (int j = 0; j < 4; ++j) {
+                    if (ex < remaining && ex + h4[j] >= remaining) {
+                        S->sel_b = tid * 4 + j; S->sel_clt = ex; S->sel_bcount = h4[j];
+                    }
+                    ex += h4[j];
+                }
+            }
+            __syncthreads();
+            remaining -= S->sel_clt;
+            pref = (width >= 32 ? 0u : (pref << width)) | S->sel_b;
+            sh_prev = s;
+            cand_count = S->sel_bcount;
+            if (cand_count <= (uint32_t)kRowCandMax || s == 0) break;
+        }
+        const uint32_t n_def = kq - remaining;
+        const bool collect = cand_count <= (uint32_t)kRowCandMax;
+        for (uint32_t i = tid; i < n; i += kRowThreads) {
+            float xv = row[i];
+            uint32_t kx = row_key(xv);
+            if (kx) {
+                uint32_t d = kmax - kx;
+                uint32_t x = d >> s;
+                if (x < pref) outk[atomicAdd(&S->out_cnt, 1u)] = make_key(xv, (uint32_t)(P.col_base + (int32_t)i));
+                else if (x == pref && collect) S->cand[atomicAdd(&S->cand_cnt, 1u)] = ~(((uint64_t)d << 32) | i);
+            }
+        }
+        __syncthreads();
+        if (collect) {
+            uint32_t n2 = pow2_ceil(cand_count);
+            for (uint32_t i = cand_count + tid; i < n2; i += kRowThreads) S->cand[i] = 0;
+            bitonic_sort_desc(S->cand, n2);
+            for (uint32_t r = tid; r < remaining; r += kRowThreads) {
+                uint32_t i = (uint32_t)(~S->cand[r]);
+                outk[n_def + r] = make_key(row[i], (uint32_t)(P.col_base + (int32_t)i));
+            }
+        } else {
+            const uint32_t per = ((n + kRowWarps - 1) / kRowWarps + 31) & ~31u;
+            const uint32_t lo = min(n, warp * per), hi = min(n, lo + per);
+            uint32_t c = 0;
+            for (uint32_t base = lo; base < hi; base += 32) {
+                uint32_t i = base + lane;
+                uint32_t kx = i < hi ? row_key(row[i]) : 0;
+                bool f = kx && (kmax - kx) == pref;
+                c += __popc(__ballot_sync(0xffffffffu, f));
+            }
+            __syncthreads();
+            if (lane == 0) S->wsum[warp] = c;
+            __syncthreads();
+            uint32_t run = 0;
+            for (uint32_t w2 = 0; w2 < warp; ++w2) run += S->wsum[w2];
+            for (uint32_t base = lo; base < hi; base += 32) {
+                uint32_t i = base + lane;
+                float xv = i < hi ? row[i] : 0.f;
+                uint32_t kx = i < hi ? row_key(xv) : 0;
+                bool f = kx && (kmax - kx) == pref;
+                uint32_t b = __ballot_sync(0xffffffffu, f);
+                uint32_t r = run + __popc(b & ((1u << lane) - 1u));
+                if (f && r < remaining) outk[n_def + r] = make_key(xv, (uint32_t)(P.col_base + (int32_t)i));
+                run += __popc(b);
+            }
+        }
+    }
+    __syncthreads();
+    bitonic_sort_desc(outk, n2out);
+    for (uint32_t r = tid; r < P.k; r += kRowThreads) {
+        const bool ok = r < kq;
+        const uint64_t key = ok ? outk[r] : 0;
+        P.out_scores[(size_t)q * P.k + r] = ok ? key_score(key) : 0.0f;
+        P.out_docs[(size_t)q * P.k + r] = ok ? (int32_t)key_doc(key) : -1;
+    }
+    if (tid == 0) P.out_counts[q] = kq;
+}
+
+int topk_rows_launch(uint32_t nq, uint32_t n, const float* scores, size_t row_stride, uint32_t k, int32_t col_base,
+                     float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s) {
+    RowsParams P{};
+    P.nq = nq; P.n = n; P.k = k; P.col_base = col_base; P.scores = scores; P.row_stride = row_stride;
+    P.out_scores = out_scores; P.out_docs = out_docs; P.out_counts = out_counts;
+    uint32_t n2 = 2;
+    while (n2 < k) n2 <<= 1;
+    const size_t smem = sizeof(RowsSmem) + (size_t)n2 * 8;
+    static bool attr_set = false;
+    if (!attr_set) {
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(topk_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)(sizeof(RowsSmem) + MSR_MAX_K * 8)));
+        attr_set = true;
+    }
+    topk_rows_kernel<<<nq, kRowThreads, smem, s>>>(P);
+    count_launch();
+    MSR_CUDA_CHECK(cudaGetLastError());
+    return MSR_OK;
+}
+
+}  // namespace msr
+
+using namespace msr;
+
+extern "C" int msr_topk_merge(int device, uint32_t n_lists, uint32_t nq, uint32_t k_in, const float* scores,
+                              const int32_t* docs, const uint32_t* counts, uint32_t k, float* out_scores,
+                              int32_t* out_docs, uint32_t* out_counts, void* stream) {
+    MSR_REQUIRE(n_lists >= 1 && k >= 1 && k_in >= 1, "msr_topk_merge: n_lists, k, k_in must be >= 1");
+    MSR_REQUIRE(k <= MSR_MAX_K && k_in <= MSR_MAX_K, "msr_topk_merge: k/k_in above %u", MSR_MAX_K);
+    if (nq == 0) return MSR_OK;
+    MSR_REQUIRE(scores && docs && counts && out_scores && out_docs && out_counts, "msr_topk_merge: NULL buffer");
+    int rc = use_device(device);
+    if (rc) return rc;
+    MergeParams P{};
+    P.nq = nq; P.n_lists = n_lists; P.stride = k_in; P.k = k; P.mode = 1;
+    P.scores = scores; P.docs = docs; P.cnts = counts;
+    P.out_scores = out_scores; P.out_docs = out_docs; P.out_counts = out_counts;
+    return merge_launch(P, (cudaStream_t)stream);
+}
+
+extern "C" int msr_topk_rows(int device, uint32_t nq, uint32_t n, const float* scores, size_t row_stride, uint32_t k,
+                             int32_t col_base, float* out_scores, int32_t* out_docs, uint32_t* out_counts, void* stream) {
+    MSR_REQUIRE(k >= 1 && k <= MSR_MAX_K, "msr_topk_rows: k=%u outside [1,%u]", k, MSR_MAX_K);
+    if (nq == 0) return MSR_OK;
+    MSR_REQUIRE(scores && out_scores && out_docs && out_counts, "msr_topk_rows: NULL buffer");
+    MSR_REQUIRE(row_stride >= n, "msr_topk_rows: row_stride < n");
+    int rc = use_device(device);
+    if (rc) return rc;
+    return topk_rows_launch(nq, n, scores, row_stride, k, col_base, out_scores, out_docs, out_counts, (cudaStream_t)stream);
+}

@@ -1,0 +1,227 @@
+"""Thin tensor-level wrappers over the C ABI (include/msr.h).  torch is used for device memory and streams only.
+
+Every function here ends in a libmsr.so kernel; nothing falls back to torch math or to the CPU.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import MSR_DEVICE, MSR_HOST, check, current_stream_ptr, ptr
+
+
+def _dev_index(device) -> int:
+    d = torch.device(device)
+    if d.type != "cuda":
+        raise RuntimeError(f"libmsr needs a CUDA (sm_100a) device, got {d}; there is no CPU fallback")
+    return d.index if d.index is not None else torch.cuda.current_device()
+
+
+def kernel_launches() -> int:
+    return int(_lib.load().msr_kernel_launches())
+
+
+class SparseIndex:
+    """Device-resident tiled impact index of one shard (msr_sparse_index_*)."""
+
+    def __init__(self, indptr, docids, impacts, n_docs, *, device="cuda", n_docs_global=None, df_global=None,
+                 doc_base=0, tile_docs=0):
+        """indptr u64/i64 [V+1], docids u32/i32 [nnz], impacts u16/i16 [nnz]: numpy (host) or CUDA tensors."""
+        lib = _lib.load()
+        self.device = _dev_index(device)
+        on_device = isinstance(indptr, torch.Tensor) and indptr.is_cuda
+        if on_device:
+            assert indptr.dtype == torch.int64 and docids.dtype == torch.int32 and impacts.dtype == torch.int16
+            indptr, docids, impacts = indptr.contiguous(), docids.contiguous(), impacts.contiguous()
+            if df_global is not None:
+                df_global = df_global.to(device=indptr.device, dtype=torch.int32).contiguous()
+        else:
+            indptr = np.ascontiguousarray(np.asarray(indptr), dtype=np.uint64)
+            docids = np.ascontiguousarray(np.asarray(docids), dtype=np.uint32)
+            impacts = np.ascontiguousarray(np.asarray(impacts), dtype=np.uint16)
+            if df_global is not None:
+                df_global = np.ascontiguousarray(np.asarray(df_global), dtype=np.uint32)
+        n_terms = int(indptr.shape[0]) - 1
+        self._h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            check(lib.msr_sparse_index_build(self.device, int(n_docs), n_terms, ptr(indptr), ptr(docids), ptr(impacts),
+                                             int(n_docs if n_docs_global is None else n_docs_global), ptr(df_global),
+                                             int(doc_base), int(tile_docs), MSR_DEVICE if on_device else MSR_HOST,
+                                             current_stream_ptr(self.device), ctypes.byref(self._h)))
+        info = (ctypes.c_uint32 * 9)()
+        check(lib.msr_sparse_index_info(self._h, info))
+        self.n_docs, self.n_terms, self.n_tiles, self.tile_docs = info[0], info[1], info[2], info[3]
+        self.nnz = info[4] | (info[5] << 32)
+        self.resident_bytes = info[7] | (info[8] << 32)
+        self.doc_base = int(doc_base)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _lib.load().msr_sparse_index_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def search(self, q_indptr, q_terms, q_weights, k, out=None):
+        """Device path: CUDA tensors (int64 indptr, int32 terms/weights) -> (scores f32, docs i32, counts i32) [nq,k].
+        Asynchronous on the current stream."""
+        nq = q_indptr.numel() - 1
+        dev = torch.device("cuda", self.device)
+        assert q_indptr.is_cuda and q_indptr.dtype == torch.int64
+        assert q_terms.dtype == torch.int32 and q_weights.dtype == torch.int32
+        if out is None:
+            out = (torch.empty((nq, k), dtype=torch.float32, device=dev),
+                   torch.empty((nq, k), dtype=torch.int32, device=dev),
+                   torch.empty((nq,), dtype=torch.int32, device=dev))
+        with torch.cuda.device(self.device):
+            check(_lib.load().msr_sparse_search(self._h, nq, ptr(q_indptr), ptr(q_terms), ptr(q_weights), int(k),
+                                                ptr(out[0]), ptr(out[1]), ptr(out[2]), MSR_DEVICE,
+                                                current_stream_ptr(self.device)))
+        return out
+
+    def status(self):
+        """Synchronise and raise MsrError(MSR_ERR_RANGE) if an earlier device-path search left the exact range."""
+        with torch.cuda.device(self.device):
+            check(_lib.load().msr_sparse_index_status(self._h, current_stream_ptr(self.device)))
+
+    def search_host(self, q_indptr, q_terms, q_weights, k, out=None):
+        """Host path: numpy arrays or pinned CPU tensors in, host arrays out; H2D/D2H inside the call."""
+        if isinstance(q_indptr, torch.Tensor):
+            nq = q_indptr.numel() - 1
+            assert not q_indptr.is_cuda and q_indptr.dtype == torch.int64
+            assert q_terms.dtype == torch.int32 and q_weights.dtype == torch.int32
+        else:
+            q_indptr = np.ascontiguousarray(q_indptr, dtype=np.uint64)
+            q_terms = np.ascontiguousarray(q_terms, dtype=np.uint32)
+            q_weights = np.ascontiguousarray(q_weights, dtype=np.uint32)
+            nq = len(q_indptr) - 1
+        if out is None:
+            out = (np.empty((nq, k), dtype=np.float32), np.empty((nq, k), dtype=np.int32),
+                   np.empty((nq,), dtype=np.uint32))
+        with torch.cuda.device(self.device):
+            check(_lib.load().msr_sparse_search(self._h, nq, ptr(q_indptr), ptr(q_terms), ptr(q_weights), int(k),
+                                                ptr(out[0]), ptr(out[1]), ptr(out[2]), MSR_HOST,
+                                                current_stream_ptr(self.device)))
+        return out
+
+    def profile(self, enable=True):
+        """(score_ms, merge_ms, launches) accumulated since the last call; then switch event timing on/off."""
+        a, b, n = ctypes.c_double(), ctypes.c_double(), ctypes.c_uint64()
+        with torch.cuda.device(self.device):
+            check(_lib.load().msr_sparse_profile(self._h, int(bool(enable)), ctypes.byref(a), ctypes.byref(b),
+                                                 ctypes.byref(n), current_stream_ptr(self.device)))
+        return a.value, b.value, int(n.value)
+
+    def query_work(self, q_indptr, q_terms, q_weights):
+        """(postings touched, kept (query,term) pairs) of a device-resident query batch -- roofline numerator."""
+        nq = q_indptr.numel() - 1
+        p, c = ctypes.c_uint64(), ctypes.c_uint64()
+        with torch.cuda.device(self.device):
+            check(_lib.load().msr_sparse_query_work(self._h, nq, ptr(q_indptr), ptr(q_terms), ptr(q_weights),
+                                                    ctypes.byref(p), ctypes.byref(c), MSR_DEVICE,
+                                                    current_stream_ptr(self.device)))
+        return int(p.value), int(c.value)
+
+
+def topk_merge(scores, docs, counts, k):
+    """[n_lists,nq,k_in] lists (e.g. an all-gather of per-GPU results) -> merged [nq,k]."""
+    n_lists, nq, k_in = scores.shape
+    dev = scores.device
+    out = (torch.empty((nq, k), dtype=torch.float32, device=dev), torch.empty((nq, k), dtype=torch.int32, device=dev),
+           torch.empty((nq,), dtype=torch.int32, device=dev))
+    di = _dev_index(dev)
+    with torch.cuda.device(di):
+        check(_lib.load().msr_topk_merge(di, n_lists, nq, k_in, ptr(scores.contiguous()), ptr(docs.contiguous()),
+                                         ptr(counts.contiguous()), int(k), ptr(out[0]), ptr(out[1]), ptr(out[2]),
+                                         current_stream_ptr(di)))
+    return out
+
+
+def topk_rows(scores, k, col_base=0):
+    """Radix-select top-k of each row of a CUDA fp32 matrix by (score desc, column asc)."""
+    assert scores.is_cuda and scores.dtype == torch.float32 and scores.stride(1) == 1
+    nq, n = scores.shape
+    dev = scores.device
+    out = (torch.empty((nq, k), dtype=torch.float32, device=dev), torch.empty((nq, k), dtype=torch.int32, device=dev),
+           torch.empty((nq,), dtype=torch.int32, device=dev))
+    di = _dev_index(dev)
+    with torch.cuda.device(di):
+        check(_lib.load().msr_topk_rows(di, nq, n, ptr(scores), scores.stride(0), int(k), int(col_base), ptr(out[0]),
+                                        ptr(out[1]), ptr(out[2]), current_stream_ptr(di)))
+    return out
+
+
+class DenseIndex:
+    """Device-resident flat inner-product index (msr_dense_index_*)."""
+
+    def __init__(self, dim, device="cuda", doc_base=0):
+        self.device = _dev_index(device)
+        self.dim = int(dim)
+        self._h = ctypes.c_void_p()
+        check(_lib.load().msr_dense_index_create(self.device, self.dim, int(doc_base), ctypes.byref(self._h)))
+
+    def close(self):
+        if getattr(self, "_h", None):
+            _lib.load().msr_dense_index_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    @property
+    def ntotal(self):
+        info = (ctypes.c_uint32 * 5)()
+        check(_lib.load().msr_dense_index_info(self._h, info))
+        return int(info[0])
+
+    def add(self, vecs):
+        if isinstance(vecs, torch.Tensor) and vecs.is_cuda:
+            vecs = vecs.to(torch.float32).contiguous()
+            where = MSR_DEVICE
+        else:
+            vecs = np.ascontiguousarray(np.asarray(vecs), dtype=np.float32)
+            where = MSR_HOST
+        assert vecs.shape[1] == self.dim
+        with torch.cuda.device(self.device):
+            check(_lib.load().msr_dense_index_add(self._h, int(vecs.shape[0]), ptr(vecs), where,
+                                                  current_stream_ptr(self.device)))
+
+    def search(self, queries, k, mode=0):
+        """numpy in -> numpy out (host path); CUDA tensor in -> CUDA tensors out (device path, asynchronous)."""
+        if isinstance(queries, torch.Tensor) and queries.is_cuda:
+            q = queries.to(torch.float32).contiguous()
+            nq = q.shape[0]
+            out = (torch.empty((nq, k), dtype=torch.float32, device=q.device),
+                   torch.empty((nq, k), dtype=torch.int64, device=q.device))
+            where = MSR_DEVICE
+        else:
+            q = np.ascontiguousarray(np.asarray(queries), dtype=np.float32)
+            nq = q.shape[0]
+            out = (np.empty((nq, k), dtype=np.float32), np.empty((nq, k), dtype=np.int64))
+            where = MSR_HOST
+        assert q.shape[1] == self.dim
+        with torch.cuda.device(self.device):
+            check(_lib.load().msr_dense_search(self._h, nq, ptr(q), int(k), ptr(out[0]), ptr(out[1]), int(mode), where,
+                                               current_stream_ptr(self.device)))
+        return out
+
+
+def fuse_lists(d_scores, d_docs, d_counts, s_scores, s_docs, s_counts, self_ids, remove_query, w_dense, w_sparse):
+    """Kernel (d) on CUDA tensors: returns (scores f64 [nq,kd+ks], docs i32, src u8, counts i32)."""
+    nq, k_d = d_scores.shape
+    k_s = s_scores.shape[1]
+    dev = d_scores.device
+    di = _dev_index(dev)
+    out = (torch.empty((nq, k_d + k_s), dtype=torch.float64, device=dev),
+           torch.empty((nq, k_d + k_s), dtype=torch.int32, device=dev),
+           torch.empty((nq, k_d + k_s), dtype=torch.uint8, device=dev),
+           torch.empty((nq,), dtype=torch.int32, device=dev))
+    with torch.cuda.device(di):
+        check(_lib.load().msr_fuse(di, nq, k_d, ptr(d_scores.contiguous()), ptr(d_docs.contiguous()),
+                                   ptr(d_counts.contiguous()), k_s, ptr(s_scores.contiguous()), ptr(s_docs.contiguous()),
+                                   ptr(s_counts.contiguous()), ptr(self_ids), int(bool(remove_query)), float(w_dense),
+                                   float(w_sparse), ptr(out[0]), ptr(out[1]), ptr(out[2]), ptr(out[3]),
+                                   current_stream_ptr(di)))
+    return out

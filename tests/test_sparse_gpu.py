@@ -1,0 +1,172 @@
+"""GPU parity tests of kernels (a)+(b) against the oracle, through the C ABI.  Bit-exact (integer work)."""
+import numpy as np
+import pytest
+import torch
+
+from helpers import random_csr, random_queries
+
+pytestmark = pytest.mark.gpu
+
+
+def _dev_queries(qi, qt, qw):
+    dev = torch.device("cuda")
+    return (torch.from_numpy(qi.astype(np.int64)).to(dev), torch.from_numpy(qt.astype(np.int32)).to(dev),
+            torch.from_numpy(qw.astype(np.int32)).to(dev))
+
+
+def _search_both(idx, qi, qt, qw, k):
+    """device path and host path must agree with each other."""
+    s, d, c = idx.search(*_dev_queries(qi, qt, qw), k)
+    idx.status()
+    hs, hd, hc = idx.search_host(qi, qt, qw, k)
+    np.testing.assert_array_equal(s.cpu().numpy(), hs)
+    np.testing.assert_array_equal(d.cpu().numpy(), hd)
+    np.testing.assert_array_equal(c.cpu().numpy().astype(np.uint32), hc)
+    return hs, hd, hc
+
+
+def _check(oracle, indptr, docids, impacts, n_docs, qi, qt, qw, k, tile_docs=0, **kw):
+    from mllm_sparse_retrieval_b200.ops import SparseIndex
+    idx = SparseIndex(indptr, docids, impacts, n_docs, tile_docs=tile_docs, **kw)
+    got = _search_both(idx, qi, qt, qw, k)
+    exp = oracle.impact_search_c(indptr, docids, impacts, n_docs, qi, qt, qw, k, threads=4,
+                                 n_docs_global=kw.get("n_docs_global"), df_global=kw.get("df_global"),
+                                 doc_base=kw.get("doc_base", 0))
+    np.testing.assert_array_equal(got[2], exp[2])
+    np.testing.assert_array_equal(got[1], exp[1])
+    np.testing.assert_array_equal(got[0], exp[0])
+    idx.close()
+    return got
+
+
+def test_known_answer_tiny(oracle, lib_built):
+    indptr = np.array([0, 3, 5, 10], dtype=np.uint64)
+    docids = np.array([0, 1, 2, 1, 3, 0, 1, 2, 3, 4], dtype=np.uint32)
+    impacts = np.array([2, 1, 1, 3, 1, 9, 9, 9, 9, 9], dtype=np.uint16)
+    qi = np.array([0, 4, 4, 5], dtype=np.uint64)          # second query is empty
+    qt = np.array([0, 1, 2, 7, 2], dtype=np.uint32)
+    qw = np.array([5, 2, 100, 3, 9], dtype=np.uint32)
+    s, d, c = _check(oracle, indptr, docids, impacts, 6, qi, qt, qw, 10)
+    assert c.tolist() == [4, 0, 0]
+    assert d[0, :4].tolist() == [1, 0, 2, 3] and s[0, :4].tolist() == [11.0, 10.0, 5.0, 2.0]
+
+
+@pytest.mark.parametrize("seed,n_docs,n_terms,nnz,nq,qlen,k,tile", [
+    (1, 200, 64, 16, 20, 8, 10, 0),
+    (2, 1000, 512, 32, 40, (1, 40), 100, 0),          # Flickr-1K shape (reduced vocab)
+    (3, 50, 16, (0, 10), 10, 6, 1000, 0),             # k > hits
+    (4, 3000, 2000, 24, 16, 12, 100, 256),            # 12 tiles
+    (5, 5000, 4096, 128, 32, 128, 100, 0),            # COCO-5K t->i "manual" shape
+    (6, 5000, 4096, 128, 8, 300, 1000, 1024),         # > 256 query terms (two staging passes), depth 1000
+    (7, 26000, 8192, 10, 24, 128, 100, 0),            # COCO i->t shape: 2 default tiles
+    (8, 700, 40, 30, 12, 20, 64, 32),                 # tiny tiles, k > tile size
+])
+def test_random_parity(oracle, lib_built, seed, n_docs, n_terms, nnz, nq, qlen, k, tile):
+    rng = np.random.default_rng(seed)
+    indptr, docids, impacts = random_csr(rng, n_docs, n_terms, nnz)
+    qi, qt, qw = random_queries(rng, nq, n_terms, qlen, dup=(seed % 2 == 0))
+    _check(oracle, indptr, docids, impacts, n_docs, qi, qt, qw, k, tile_docs=tile)
+
+
+def test_massive_ties(oracle, lib_built):
+    """every doc has the same score -> top-k is the k smallest doc ids (S8), through the ordered tie path."""
+    n_docs = 6000
+    indptr = np.array([0, n_docs - 2, n_docs - 2 + 3000], dtype=np.uint64)
+    docids = np.concatenate([np.arange(n_docs - 2), np.arange(0, 6000, 2)]).astype(np.uint32)
+    impacts = np.concatenate([np.full(n_docs - 2, 7), np.full(3000, 1)]).astype(np.uint16)
+    qi = np.array([0, 1, 3], dtype=np.uint64)
+    qt = np.array([0, 0, 1], dtype=np.uint32)
+    qw = np.array([3, 3, 1], dtype=np.uint32)
+    for tile in (0, 2048):
+        s, d, c = _check(oracle, indptr, docids, impacts, n_docs, qi, qt, qw, 100, tile_docs=tile)
+        assert d[0].tolist() == list(range(100))
+        assert d[1].tolist() == list(range(0, 200, 2))
+
+
+def test_score_above_2_24(oracle, lib_built):
+    """S6: per-term float32 rounding and float32 ranking key once sums pass 2^24."""
+    rng = np.random.default_rng(9)
+    n_docs, n_terms = 4000, 50
+    indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 20, max_impact=65535, zipf=False)
+    qi, qt, qw = random_queries(rng, 10, n_terms, 8, max_w=4000, zipf=False)
+    s, d, c = _check(oracle, indptr, docids, impacts, n_docs, qi, qt, qw, 100, tile_docs=512)
+    assert s.max() >= 2 ** 24
+
+
+def test_range_error_is_loud(oracle, lib_built):
+    from mllm_sparse_retrieval_b200._lib import MsrError, MSR_ERR_RANGE
+    from mllm_sparse_retrieval_b200.ops import SparseIndex
+    indptr = np.array([0, 2], dtype=np.uint64)
+    idx = SparseIndex(indptr, np.array([0, 1], np.uint32), np.array([65535, 3], np.uint16), 8)
+    qi = np.array([0, 1], dtype=np.uint64)
+    with pytest.raises(MsrError) as e:
+        idx.search_host(qi, np.array([0], np.uint32), np.array([70000], np.uint32), 5)
+    assert e.value.code == MSR_ERR_RANGE
+    s, d, c = idx.search_host(qi, np.array([0], np.uint32), np.array([2], np.uint32), 5)   # handle still usable
+    assert c.tolist() == [2] and d[0, :2].tolist() == [0, 1]
+
+
+def test_malformed_csr_rejected(lib_built):
+    from mllm_sparse_retrieval_b200._lib import MsrError
+    from mllm_sparse_retrieval_b200.ops import SparseIndex
+    with pytest.raises(MsrError):
+        SparseIndex(np.array([0, 2], np.uint64), np.array([3, 1], np.uint32), np.array([1, 1], np.uint16), 8)
+    with pytest.raises(MsrError):
+        SparseIndex(np.array([0, 1], np.uint64), np.array([9], np.uint32), np.array([1], np.uint16), 8)
+
+
+def test_doc_sharded_merge_invariant(oracle, lib_built):
+    """per-shard search (global df/N) + msr_topk_merge == unsharded, for G = 2, 3, 8."""
+    from mllm_sparse_retrieval_b200.ops import SparseIndex, topk_merge
+    rng = np.random.default_rng(21)
+    n_docs, n_terms, k = 5000, 1000, 100
+    indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 40)
+    qi, qt, qw = random_queries(rng, 25, n_terms, 16)
+    ref = oracle.impact_search_c(indptr, docids, impacts, n_docs, qi, qt, qw, k, threads=4)
+    df = np.diff(indptr.astype(np.int64)).astype(np.uint32)
+    term_of = np.repeat(np.arange(n_terms), df)
+    dq = _dev_queries(qi, qt, qw)
+    for G in (2, 3, 8):
+        bounds = np.linspace(0, n_docs, G + 1).astype(int)
+        outs = []
+        for g in range(G):
+            lo, hi = bounds[g], bounds[g + 1]
+            m = (docids >= lo) & (docids < hi)
+            ip = np.zeros(n_terms + 1, dtype=np.uint64)
+            np.cumsum(np.bincount(term_of[m], minlength=n_terms), out=ip[1:])
+            idx = SparseIndex(ip, docids[m] - lo, impacts[m], hi - lo, n_docs_global=n_docs, df_global=df,
+                              doc_base=int(lo), tile_docs=300)
+            outs.append(idx.search(*dq, k))
+            idx.close()
+        ms, md, mc = topk_merge(torch.stack([o[0] for o in outs]), torch.stack([o[1] for o in outs]),
+                                torch.stack([o[2] for o in outs]), k)
+        np.testing.assert_array_equal(mc.cpu().numpy().astype(np.uint32), ref[2])
+        np.testing.assert_array_equal(md.cpu().numpy(), ref[1])
+        np.testing.assert_array_equal(ms.cpu().numpy(), ref[0])
+
+
+def test_query_work_counts(oracle, lib_built):
+    from mllm_sparse_retrieval_b200.ops import SparseIndex
+    rng = np.random.default_rng(31)
+    n_docs, n_terms = 2000, 300
+    indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 30)
+    qi, qt, qw = random_queries(rng, 17, n_terms, 9)
+    idx = SparseIndex(indptr, docids, impacts, n_docs)
+    p, c = idx.query_work(*_dev_queries(qi, qt, qw))
+    df = np.diff(indptr.astype(np.int64))
+    keep = (df > 0) & (df + 1 < n_docs)
+    assert p == int(df[qt][keep[qt]].sum()) and c == int(keep[qt].sum())
+
+
+def test_synthetic_generator_config_shapes(oracle, lib_built):
+    """Flickr-1K stand-in of SURVEY.md 8(d) config 1 (V reduced for test time), generated on the GPU."""
+    from mllm_sparse_retrieval_b200 import synth
+    from mllm_sparse_retrieval_b200.ops import SparseIndex
+    coll = synth.make_collection(1000, 128, V=8192, seed=1001, device="cuda")
+    qs = synth.make_queries(500, 12, V=8192, seed=1001, device="cuda")
+    idx = SparseIndex(coll.indptr, coll.docids, coll.impacts, coll.n_docs)
+    s, d, c = idx.search(qs.indptr, qs.terms, qs.weights, 100)
+    idx.status()
+    exp = oracle.impact_search_c(*coll.numpy(), coll.n_docs, *qs.numpy(), 100, threads=4)
+    np.testing.assert_array_equal(d.cpu().numpy(), exp[1])
+    np.testing.assert_array_equal(s.cpu().numpy(), exp[0])

@@ -1,0 +1,114 @@
+"""GPU parity of the stand-alone top-k (b), fusion (d) and the exact dense pass (c) against the oracle."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("n,k,kind", [(1000, 10, "normal"), (50000, 100, "normal"), (300000, 1000, "normal"),
+                                      (5000, 100, "ties"), (20000, 64, "const"), (70, 100, "normal"),
+                                      (4096, 4096, "normal"), (9000, 50, "neg")])
+def test_topk_rows(lib_built, n, k, kind):
+    from mllm_sparse_retrieval_b200.ops import topk_rows
+    rng = np.random.default_rng(n + k)
+    nq = 5
+    if kind == "normal":
+        x = rng.standard_normal((nq, n)).astype(np.float32)
+    elif kind == "neg":
+        x = -np.abs(rng.standard_normal((nq, n))).astype(np.float32) - 1
+    elif kind == "ties":
+        x = rng.integers(0, 20, size=(nq, n)).astype(np.float32)
+    else:
+        x = np.full((nq, n), 3.25, dtype=np.float32)
+    x[0, : min(n, 5)] = -np.inf
+    s, d, c = topk_rows(torch.from_numpy(x).cuda(), k, col_base=7)
+    s, d, c = s.cpu().numpy(), d.cpu().numpy(), c.cpu().numpy()
+    for q in range(nq):
+        valid = np.isfinite(x[q]) | (x[q] == np.inf)
+        order = np.lexsort((np.arange(n), -x[q].astype(np.float64)))
+        order = order[valid[order]][:k]
+        assert c[q] == len(order)
+        np.testing.assert_array_equal(d[q, :len(order)], order + 7)
+        np.testing.assert_array_equal(s[q, :len(order)], x[q, order])
+        assert (d[q, len(order):] == -1).all()
+
+
+def _lists_to_runs(oracle, qids, docnames, scores, docs, counts, remove_query, as_f32):
+    batch_scores, batch_rank = [], []
+    for q in range(len(qids)):
+        n = int(counts[q])
+        sc = scores[q, :n]
+        batch_scores.append([np.float32(v) for v in sc] if as_f32 else [float(v) for v in sc])
+        batch_rank.append([docnames[i] for i in docs[q, :n]])
+    return oracle.get_run_dict(qids, batch_scores, batch_rank, remove_query)
+
+
+@pytest.mark.parametrize("remove_query,alpha,kd,ks", [(False, 0.5, 100, 100), (True, 0.3, 1000, 1000), (True, 0.5, 10, 37)])
+def test_fuse_matches_reference_semantics(oracle, lib_built, remove_query, alpha, kd, ks):
+    from mllm_sparse_retrieval_b200.ops import fuse_lists
+    rng = np.random.default_rng(kd + ks)
+    nq, n_docs = 12, 3000
+    docnames = [str(i) for i in range(n_docs)]
+    qids = [str(i * 7) for i in range(nq)]                 # collide with doc ids on purpose
+    d_s = np.zeros((nq, kd), np.float32); d_d = np.full((nq, kd), -1, np.int32); d_c = np.zeros(nq, np.int32)
+    s_s = np.zeros((nq, ks), np.float32); s_d = np.full((nq, ks), -1, np.int32); s_c = np.zeros(nq, np.int32)
+    for q in range(nq):
+        nd = kd if q != 3 else 0                           # one query with an empty dense list
+        ns = ks if q != 5 else max(1, ks // 3)             # one short sparse list
+        pool = rng.permutation(n_docs)[: kd + ks]
+        dd = pool[:nd].copy()
+        sd = np.concatenate([pool[: ns // 2], pool[kd: kd + ns - ns // 2]])[:ns]
+        if q % 2 == 0 and nd:
+            dd[rng.integers(0, nd)] = q * 7                # the query's own id is in the dense list
+        if q % 3 == 0 and ns and (q * 7) not in sd:
+            sd[rng.integers(0, ns)] = q * 7
+        _, ui = np.unique(dd, return_index=True); dd = dd[np.sort(ui)]
+        _, ui = np.unique(sd, return_index=True); sd = sd[np.sort(ui)]
+        nd, ns = len(dd), len(sd)
+        d_d[q, :nd] = dd; d_s[q, :nd] = np.sort(rng.random(nd).astype(np.float32))[::-1]; d_c[q] = nd
+        s_d[q, :ns] = sd; s_s[q, :ns] = np.sort(rng.integers(1, 90000, ns).astype(np.float32))[::-1]; s_c[q] = ns
+    self_ids = np.array([int(x) for x in qids], np.int32)
+    t = lambda a: torch.from_numpy(a).cuda()
+    fs, fd, fsrc, fc = fuse_lists(t(d_s), t(d_d), t(d_c), t(s_s), t(s_d), t(s_c), t(self_ids), remove_query, alpha, 1 - alpha)
+    fs, fd, fsrc, fc = fs.cpu().numpy(), fd.cpu().numpy(), fsrc.cpu().numpy(), fc.cpu().numpy()
+    dense_run = _lists_to_runs(oracle, qids, docnames, d_s, d_d, d_c, remove_query, True)
+    sparse_run = _lists_to_runs(oracle, qids, docnames, s_s, s_d, s_c, remove_query, False)
+    exp = oracle.fuse([dense_run, sparse_run], [alpha, 1 - alpha])
+    for q, qid in enumerate(qids):
+        e = exp[qid]
+        assert fc[q] == len(e)
+        assert [docnames[i] for i in fd[q, :fc[q]]] == list(e.keys())          # insertion order (H1/H4)
+        np.testing.assert_allclose(fs[q, :fc[q]], np.array(list(e.values()), dtype=np.float64), rtol=1e-3, atol=1e-6)
+        for j, doc in enumerate(e.keys()):
+            tag = (1 if doc in dense_run[qid]["docs"] else 0) | (2 if doc in sparse_run[qid]["docs"] else 0)
+            assert fsrc[q, j] == tag
+
+
+@pytest.mark.parametrize("n_docs,dim,nq,k", [(1000, 4096, 7, 10), (5000, 4096, 33, 100), (300, 100, 5, 1000), (2000, 3584, 4, 100)])
+def test_dense_exact_matches_oracle(oracle, lib_built, n_docs, dim, nq, k):
+    from mllm_sparse_retrieval_b200 import synth
+    from mllm_sparse_retrieval_b200.ops import DenseIndex
+    docs, q = synth.make_dense(n_docs, nq, dim=dim, seed=1002)
+    docs, q = docs.numpy(), q.numpy()
+    docs[11] = docs[4]                                      # exact duplicate -> id tie-break
+    idx = DenseIndex(dim)
+    idx.add(docs[: n_docs // 2]); idx.add(docs[n_docs // 2:])   # FaissFlatSearcher.add appends
+    assert idx.ntotal == n_docs
+    s, ids = idx.search(q, k, mode=1)
+    es, eids = oracle.flat_ip_search_numpy(docs, q, k)
+    kk = min(k, n_docs)
+    # ids identical except where the oracle's own neighbours are closer than fp32 resolution
+    S64 = q.astype(np.float64) @ docs.astype(np.float64).T
+    for r in range(nq):
+        if not np.array_equal(ids[r, :kk], eids[r]):
+            bad = np.nonzero(ids[r, :kk] != eids[r])[0]
+            for b in bad:
+                assert abs(S64[r, ids[r, b]] - S64[r, eids[r, b]]) < 2e-6, (r, b)
+    np.testing.assert_allclose(s[:, :kk], np.take_along_axis(S64, ids[:, :kk], 1), rtol=1e-3, atol=1e-6)
+    if k > n_docs:                                          # D5 padding convention
+        assert (ids[:, kk:] == -1).all() and (s[:, kk:] < -3e38).all()
+    # device path agrees with host path
+    s2, ids2 = idx.search(torch.from_numpy(q).cuda(), k, mode=1)
+    np.testing.assert_array_equal(ids2.cpu().numpy(), ids)
+    np.testing.assert_array_equal(s2.cpu().numpy(), s)
