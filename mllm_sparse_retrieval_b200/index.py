@@ -1,0 +1,173 @@
+"""Host side of the sparse index: JSONL collection -> term dictionary + canonical CSR (+ on-disk cache).
+
+Replaces the offline Lucene indexing step of the reference (scripts/sparse_index.sh:12-18:
+``python -m pyserini.index.lucene --collection JsonVectorCollection --impact --pretokenized``) for the files
+that src/encode.py:353-359,426 writes: one JSON object per line, ``{"id": ..., "content": "", "vector": {term: int}}``.
+
+Rules implemented here:
+  S1  tf(t,d) = vector[t]; non-positive weights are never indexed (Anserini repeats the key ``value`` times).
+      The pretokenized pseudo-document is whitespace-analysed, so a key holding whitespace contributes each of its
+      pieces (and an empty key nothing).
+  S2  terms are taken verbatim (no stemming / case folding).
+  S8  internal doc id = rank of the external docid string in UTF-8 byte order, so the kernels' "smaller id wins"
+      equals Anserini's BREAK_SCORE_TIES_BY_DOCID.
+"""
+from __future__ import annotations
+
+import glob
+import json
+import os
+from collections import Counter
+
+import numpy as np
+
+CACHE_DIR = "msr_index"
+CACHE_VERSION = 1
+
+
+class ImpactCollection:
+    """Term dictionary + docid table + canonical term-major CSR on the host."""
+
+    def __init__(self, terms, docids, indptr, post_docs, post_impacts):
+        self.terms = list(terms)                              # term id -> string
+        self.term_to_id = {t: i for i, t in enumerate(self.terms)}
+        self.docids = list(docids)                            # internal id -> external docid string (sorted)
+        self.docid_to_internal = {d: i for i, d in enumerate(self.docids)}
+        self.indptr = np.ascontiguousarray(indptr, dtype=np.uint64)
+        self.post_docs = np.ascontiguousarray(post_docs, dtype=np.uint32)
+        self.post_impacts = np.ascontiguousarray(post_impacts, dtype=np.uint16)
+
+    @property
+    def n_docs(self):
+        return len(self.docids)
+
+    @property
+    def n_terms(self):
+        return len(self.terms)
+
+    @property
+    def df(self):
+        return np.diff(self.indptr.astype(np.int64)).astype(np.uint32)
+
+    # ------------------------------------------------------------------------------------------------------
+    @classmethod
+    def from_vectors(cls, doc_ids, vectors):
+        """doc_ids: iterable of str; vectors: iterable of {term: int} (the JSONL ``vector`` objects)."""
+        doc_ids = [str(d) for d in doc_ids]
+        if len(set(doc_ids)) != len(doc_ids):
+            raise ValueError("duplicate document ids in the collection")
+        order = sorted(range(len(doc_ids)), key=lambda i: doc_ids[i].encode("utf-8"))       # S8
+        internal = np.empty(len(doc_ids), dtype=np.int64)
+        internal[order] = np.arange(len(doc_ids))
+        term_to_id = {}
+        d_list, t_list, w_list = [], [], []
+        for i, vec in enumerate(vectors):
+            tf = Counter()
+            for key, v in vec.items():
+                v = int(v)
+                if v <= 0:
+                    continue                                                               # S1
+                for piece in str(key).split():
+                    tf[piece] += v
+            for term, v in tf.items():
+                if v > 65535:
+                    raise ValueError(f"impact {v} of term {term!r} in doc {doc_ids[i]!r} exceeds 65535")
+                tid = term_to_id.setdefault(term, len(term_to_id))
+                d_list.append(internal[i]); t_list.append(tid); w_list.append(v)
+        n_terms = max(1, len(term_to_id))
+        d = np.asarray(d_list, dtype=np.int64); t = np.asarray(t_list, dtype=np.int64); w = np.asarray(w_list, dtype=np.int64)
+        o = np.lexsort((d, t))
+        d, t, w = d[o], t[o], w[o]
+        indptr = np.zeros(n_terms + 1, dtype=np.uint64)
+        np.cumsum(np.bincount(t, minlength=n_terms), out=indptr[1:])
+        terms = [None] * len(term_to_id)
+        for s, i in term_to_id.items():
+            terms[i] = s
+        if not terms:
+            terms = [""]
+        return cls(terms, [doc_ids[i] for i in order], indptr, d, w)
+
+    @classmethod
+    def from_jsonl_dir(cls, path, use_cache=True):
+        """path = the reference's ``--sparse_index`` directory (holds corpus_*.jsonl; Lucene's own ``index/`` is ignored)."""
+        files = sorted(glob.glob(os.path.join(path, "corpus*.jsonl")))
+        if not files:
+            raise FileNotFoundError(f"no corpus*.jsonl under {path}")
+        stamp = [[os.path.basename(f), os.path.getsize(f), int(os.path.getmtime(f))] for f in files]
+        cdir = os.path.join(path, CACHE_DIR)
+        if use_cache:
+            got = cls._load_cache(cdir, stamp)
+            if got is not None:
+                return got
+        ids, vecs = [], []
+        for fn in files:
+            with open(fn, "r", encoding="utf-8") as f:
+                for line in f:
+                    line = line.strip()
+                    if not line:
+                        continue
+                    obj = json.loads(line)
+                    ids.append(str(obj["id"]))
+                    vecs.append(obj.get("vector") or {})
+        coll = cls.from_vectors(ids, vecs)
+        if use_cache:
+            try:
+                coll._save_cache(cdir, stamp)
+            except OSError:
+                pass                                     # read-only index directory: rebuild next time
+        return coll
+
+    def _save_cache(self, cdir, stamp):
+        os.makedirs(cdir, exist_ok=True)
+        np.save(os.path.join(cdir, "indptr.npy"), self.indptr)
+        np.save(os.path.join(cdir, "docids.npy"), self.post_docs)
+        np.save(os.path.join(cdir, "impacts.npy"), self.post_impacts)
+        with open(os.path.join(cdir, "terms.json"), "w", encoding="utf-8") as f:
+            json.dump(self.terms, f, ensure_ascii=False)
+        with open(os.path.join(cdir, "docids.json"), "w", encoding="utf-8") as f:
+            json.dump(self.docids, f, ensure_ascii=False)
+        with open(os.path.join(cdir, "meta.json"), "w") as f:
+            json.dump({"version": CACHE_VERSION, "source": stamp, "n_docs": self.n_docs, "n_terms": self.n_terms,
+                       "nnz": int(self.indptr[-1])}, f)
+
+    @classmethod
+    def _load_cache(cls, cdir, stamp):
+        try:
+            with open(os.path.join(cdir, "meta.json")) as f:
+                meta = json.load(f)
+            if meta.get("version") != CACHE_VERSION or meta.get("source") != stamp:
+                return None
+            with open(os.path.join(cdir, "terms.json"), encoding="utf-8") as f:
+                terms = json.load(f)
+            with open(os.path.join(cdir, "docids.json"), encoding="utf-8") as f:
+                docids = json.load(f)
+            return cls(terms, docids, np.load(os.path.join(cdir, "indptr.npy")), np.load(os.path.join(cdir, "docids.npy")),
+                       np.load(os.path.join(cdir, "impacts.npy")))
+        except (OSError, ValueError, KeyError):
+            return None
+
+    # ------------------------------------------------------------------------------------------------------
+    def shard(self, lo, hi):
+        """Canonical CSR of the internal-id range [lo,hi) with doc ids rebased to 0 (doc-sharded multi-GPU)."""
+        m = (self.post_docs >= lo) & (self.post_docs < hi)
+        term_of = np.repeat(np.arange(self.n_terms), self.df)
+        indptr = np.zeros(self.n_terms + 1, dtype=np.uint64)
+        np.cumsum(np.bincount(term_of[m], minlength=self.n_terms), out=indptr[1:])
+        return indptr, (self.post_docs[m] - lo).astype(np.uint32), self.post_impacts[m]
+
+    def encode_queries(self, queries):
+        """S4 + dictionary lookup: list of query strings (or {token: weight} maps) -> query CSR (u64, u32, u32).
+
+        A string is encoded as pyserini's TokFreqQueryEncoder does: Counter(text.strip().split()).  Tokens outside
+        the dictionary are dropped here; the df-based half of S5 is applied on the device."""
+        indptr = np.zeros(len(queries) + 1, dtype=np.uint64)
+        terms, weights = [], []
+        for i, q in enumerate(queries):
+            counts = Counter(q.strip().split()) if isinstance(q, str) else q
+            for tok, w in counts.items():
+                tid = self.term_to_id.get(tok)
+                w = int(w)
+                if tid is not None and w > 0:
+                    terms.append(tid); weights.append(w)
+            indptr[i + 1] = len(terms)
+        return indptr, np.asarray(terms, dtype=np.uint32), np.asarray(weights, dtype=np.uint32)
