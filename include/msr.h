@@ -157,13 +157,14 @@ int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* queries, uint
  * list order): out_docs i32 [nq,k_d+k_s], out_scores f64 [nq,k_d+k_s], out_src u8 (1 dense only, 2 sparse only,
  * 3 both = fuse_statistic's tag, hybrid.py:56-90), out_counts u32 [nq].  w_dense / w_sparse are the reference's
  * weights [alpha, 1-alpha].  Arithmetic reproduces the reference under NumPy >= 2 bit for bit: float32 for the
- * dense term and for sums that contain one, float64 for sparse-only docs (rule H3); doc ids must be unique
- * within a list.  Device pointers only.
+ * dense term and for sums that contain one, float64 for sparse-only docs (rule H3).  dense_f32 = 0 switches the
+ * dense term to float64 too (both runs hold Python floats, e.g. runs re-read with read_trec_run).  Doc ids must
+ * be unique within a list.  Device pointers only.
  */
 int msr_fuse(int device, uint32_t nq,
              uint32_t k_d, const float* d_scores, const int32_t* d_docs, const uint32_t* d_counts,
              uint32_t k_s, const float* s_scores, const int32_t* s_docs, const uint32_t* s_counts,
-             const int32_t* self_ids, int remove_query, double w_dense, double w_sparse,
+             const int32_t* self_ids, int remove_query, int dense_f32, double w_dense, double w_sparse,
              double* out_scores, int32_t* out_docs, uint8_t* out_src, uint32_t* out_counts, void* stream);
 
 #ifdef __cplusplus

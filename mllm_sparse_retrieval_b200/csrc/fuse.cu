@@ -23,7 +23,7 @@ struct FuseParams {
     const float* d_scores; const int32_t* d_docs; const uint32_t* d_counts;
     const float* s_scores; const int32_t* s_docs; const uint32_t* s_counts;
     const int32_t* self_ids;
-    int remove_query;
+    int remove_query, dense_f32;
     double w_dense, w_sparse;
     double* out_scores; int32_t* out_docs; uint8_t* out_src; uint32_t* out_counts;
 };
@@ -31,7 +31,6 @@ struct FuseParams {
 struct FuseSmall {
     float dmin, dmax, smin, smax;
     uint32_t wsum[kFuseWarps];
-    uint32_t removed_d;                      // index of the removed dense entry or 0xFFFFFFFF
 };
 
 __device__ __forceinline__ uint32_t hash_doc(uint32_t d) { return d * 2654435761u; }
@@ -88,7 +87,6 @@ fuse_kernel(const FuseParams P) {
     // 2. sparse list -> hash table
     for (uint32_t i = tid; i < P.table; i += kFuseThreads) tkeys[i] = 0xFFFFFFFFu;
     for (uint32_t i = tid; i < ns; i += kFuseThreads) matched[i] = 0;
-    if (tid == 0) S->removed_d = 0xFFFFFFFFu;
     __syncthreads();
     const uint32_t mask = P.table - 1;
     for (uint32_t i = tid; i < ns; i += kFuseThreads) {
@@ -102,10 +100,7 @@ fuse_kernel(const FuseParams P) {
             slot = (slot + 1) & mask;
         }
     }
-    for (uint32_t i = tid; i < nd; i += kFuseThreads)
-        if (dd[i] == self && self >= 0) S->removed_d = i;     // at most one (doc ids are unique within a list)
     __syncthreads();
-    const uint32_t removed_d = S->removed_d;
 
     // normalisation constants, typed as the reference computes them
     const float d_den32 = __fsub_rn(dmax, dmin);
@@ -113,35 +108,49 @@ fuse_kernel(const FuseParams P) {
     const float d_den = d_den_small ? (float)1e-9 : d_den32;
     const float wd32 = (float)P.w_dense;                      // weak Python float * np.float32 -> float32
     const double s_den = fmax(__dsub_rn((double)smax, (double)smin), 1e-9);
+    const double d_den64 = fmax(__dsub_rn((double)dmax, (double)dmin), 1e-9);   // both runs Python floats
 
-    // 3a. dense entries, in dense order
-    for (uint32_t i = tid; i < nd; i += kFuseThreads) {
-        int32_t doc = dd[i];
-        if (i == removed_d || doc < 0) continue;
-        float sc = __fmul_rn(wd32, __fdiv_rn(__fsub_rn(ds[i], dmin), d_den));
-        uint8_t src = 1;
-        uint32_t slot = hash_doc((uint32_t)doc) & mask;
-        for (;;) {
-            uint32_t kx = tkeys[slot];
-            if (kx == 0xFFFFFFFFu) break;
-            if (kx == (uint32_t)doc) {
-                uint32_t j = tvals[slot];
-                matched[j] = 1;
-                double st = __dmul_rn(P.w_sparse, __ddiv_rn(__dsub_rn((double)ss[j], (double)smin), s_den));
-                sc = __fadd_rn(sc, (float)st);                // np.float32 += weak Python float
-                src = 3;
-                break;
+    // 3a. dense entries, in dense order (ordered compaction: entries equal to the self id are dropped)
+    uint32_t run = 0;
+    for (uint32_t base = 0; base < nd; base += kFuseThreads) {
+        const uint32_t i = base + tid;
+        int32_t doc = -1;
+        bool f = false;
+        if (i < nd) { doc = dd[i]; f = doc >= 0 && doc != self; }
+        const uint32_t b = __ballot_sync(0xffffffffu, f);
+        __syncthreads();
+        if (lane == 0) S->wsum[warp] = __popc(b);
+        __syncthreads();
+        uint32_t before = 0, total = 0;
+#pragma unroll
+        for (int w = 0; w < kFuseWarps; ++w) { uint32_t x = S->wsum[w]; if (w < (int)warp) before += x; total += x; }
+        if (f) {
+            float sc = __fmul_rn(wd32, __fdiv_rn(__fsub_rn(ds[i], dmin), d_den));
+            double sc64 = __dmul_rn(P.w_dense, __ddiv_rn(__dsub_rn((double)ds[i], (double)dmin), d_den64));
+            uint8_t src = 1;
+            uint32_t slot = hash_doc((uint32_t)doc) & mask;
+            for (;;) {
+                uint32_t kx = tkeys[slot];
+                if (kx == 0xFFFFFFFFu) break;
+                if (kx == (uint32_t)doc) {
+                    uint32_t j = tvals[slot];
+                    matched[j] = 1;
+                    double st = __dmul_rn(P.w_sparse, __ddiv_rn(__dsub_rn((double)ss[j], (double)smin), s_den));
+                    sc = __fadd_rn(sc, (float)st);            // np.float32 += weak Python float
+                    sc64 = __dadd_rn(sc64, st);
+                    src = 3;
+                    break;
+                }
+                slot = (slot + 1) & mask;
             }
-            slot = (slot + 1) & mask;
+            const uint32_t pos = run + before + __popc(b & ((1u << lane) - 1u));
+            os[pos] = P.dense_f32 ? (double)sc : sc64; od[pos] = doc; osrc[pos] = src;
         }
-        uint32_t pos = i - (removed_d < i ? 1u : 0u);
-        os[pos] = (double)sc; od[pos] = doc; osrc[pos] = src;
+        run += total;
     }
     __syncthreads();
-    const uint32_t n_dense_out = nd - (removed_d != 0xFFFFFFFFu ? 1u : 0u);
 
     // 3b. sparse-only entries, in sparse order (ordered compaction).  Doc ids are unique within a list.
-    uint32_t run = n_dense_out;
     for (uint32_t base = 0; base < ns; base += kFuseThreads) {
         uint32_t i = base + tid;
         bool f = false;
@@ -175,8 +184,8 @@ using namespace msr;
 
 extern "C" int msr_fuse(int device, uint32_t nq, uint32_t k_d, const float* d_scores, const int32_t* d_docs,
                         const uint32_t* d_counts, uint32_t k_s, const float* s_scores, const int32_t* s_docs,
-                        const uint32_t* s_counts, const int32_t* self_ids, int remove_query, double w_dense,
-                        double w_sparse, double* out_scores, int32_t* out_docs, uint8_t* out_src,
+                        const uint32_t* s_counts, const int32_t* self_ids, int remove_query, int dense_f32,
+                        double w_dense, double w_sparse, double* out_scores, int32_t* out_docs, uint8_t* out_src,
                         uint32_t* out_counts, void* stream) {
     MSR_REQUIRE(k_d >= 1 && k_s >= 1 && k_d <= MSR_MAX_K && k_s <= MSR_MAX_K, "msr_fuse: k_d/k_s outside [1,%u]", MSR_MAX_K);
     if (nq == 0) return MSR_OK;
@@ -190,7 +199,7 @@ extern "C" int msr_fuse(int device, uint32_t nq, uint32_t k_d, const float* d_sc
     while (P.table < 2 * k_s) P.table <<= 1;
     P.d_scores = d_scores; P.d_docs = d_docs; P.d_counts = d_counts;
     P.s_scores = s_scores; P.s_docs = s_docs; P.s_counts = s_counts;
-    P.self_ids = self_ids; P.remove_query = remove_query; P.w_dense = w_dense; P.w_sparse = w_sparse;
+    P.self_ids = self_ids; P.remove_query = remove_query; P.dense_f32 = dense_f32; P.w_dense = w_dense; P.w_sparse = w_sparse;
     P.out_scores = out_scores; P.out_docs = out_docs; P.out_src = out_src; P.out_counts = out_counts;
     const size_t smem = sizeof(FuseSmall) + kFuseWarps * 4 + (size_t)P.table * 8 + ((k_s + 15) & ~15u);
     static bool attr_set = false;

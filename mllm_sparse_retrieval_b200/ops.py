@@ -10,7 +10,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from ._lib import MSR_DEVICE, MSR_HOST, check, current_stream_ptr, ptr
+from ._lib import MSR_DEVICE, MSR_HOST, MSR_MAX_K, check, current_stream_ptr, ptr  # noqa: F401
 
 
 def _dev_index(device) -> int:
@@ -208,7 +208,8 @@ class DenseIndex:
         return out
 
 
-def fuse_lists(d_scores, d_docs, d_counts, s_scores, s_docs, s_counts, self_ids, remove_query, w_dense, w_sparse):
+def fuse_lists(d_scores, d_docs, d_counts, s_scores, s_docs, s_counts, self_ids, remove_query, w_dense, w_sparse,
+               dense_f32=True):
     """Kernel (d) on CUDA tensors: returns (scores f64 [nq,kd+ks], docs i32, src u8, counts i32)."""
     nq, k_d = d_scores.shape
     k_s = s_scores.shape[1]
@@ -221,7 +222,7 @@ def fuse_lists(d_scores, d_docs, d_counts, s_scores, s_docs, s_counts, self_ids,
     with torch.cuda.device(di):
         check(_lib.load().msr_fuse(di, nq, k_d, ptr(d_scores.contiguous()), ptr(d_docs.contiguous()),
                                    ptr(d_counts.contiguous()), k_s, ptr(s_scores.contiguous()), ptr(s_docs.contiguous()),
-                                   ptr(s_counts.contiguous()), ptr(self_ids), int(bool(remove_query)), float(w_dense),
+                                   ptr(s_counts.contiguous()), ptr(self_ids), int(bool(remove_query)), int(bool(dense_f32)), float(w_dense),
                                    float(w_sparse), ptr(out[0]), ptr(out[1]), ptr(out[2]), ptr(out[3]),
                                    current_stream_ptr(di)))
     return out

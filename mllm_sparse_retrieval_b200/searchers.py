@@ -1,0 +1,203 @@
+"""Drop-in searcher classes with the call surface the reference uses.
+
+  LuceneImpactSearcher  <- pyserini.search.lucene.LuceneImpactSearcher as used at
+                           /root/reference/src/search.py:273-275 (ctor + set_analyzer) and :86-87 (batch_search)
+  FaissFlatSearcher     <- tevatron.retriever.searcher.FaissFlatSearcher as used at
+                           /root/reference/src/search.py:232,237 (ctor + add), :57,59 (batch_search / search) and
+                           :254-270 (``.index`` re-assignment by the faiss GPU cloner)
+
+Both run on libmsr.so (CUDA, sm_100a) only; constructing either without a usable B200 raises.
+With ``shard=True`` under an initialised torch.distributed process group the collection is doc-sharded over the
+ranks and per-rank top-k lists are merged after one NCCL all-gather; every rank then holds the
+full result for the queries it passed (all ranks must pass the SAME queries in that mode).
+"""
+from __future__ import annotations
+
+import glob
+import os
+
+import numpy as np
+import torch
+
+from . import ops
+from .index import ImpactCollection
+
+
+class Hit:
+    """pyserini hit: the reference reads ``hit.docid`` and ``hit.score`` (search.py:94-97)."""
+    __slots__ = ("docid", "score")
+
+    def __init__(self, docid, score):
+        self.docid = docid
+        self.score = score
+
+    def __repr__(self):
+        return f"Hit(docid={self.docid!r}, score={self.score!r})"
+
+
+class JWhiteSpaceAnalyzer:
+    """Placeholder for pyserini.analysis.JWhiteSpaceAnalyzer (search.py:274): queries are always split on whitespace."""
+
+
+def _dist_info(shard):
+    if shard and torch.distributed.is_available() and torch.distributed.is_initialized():
+        return torch.distributed.get_rank(), torch.distributed.get_world_size()
+    return 0, 1
+
+
+def _find_collection_dir(index_dir):
+    """The reference passes ``<sparse_index>/index`` (Lucene's directory); the JSONL lives one level up."""
+    for cand in (index_dir, os.path.dirname(os.path.normpath(index_dir))):
+        if glob.glob(os.path.join(cand, "corpus*.jsonl")):
+            return cand
+    raise FileNotFoundError(f"no corpus*.jsonl in {index_dir!r} or its parent; "
+                            "point --sparse_index at the directory src/encode.py wrote")
+
+
+class LuceneImpactSearcher:
+    def __init__(self, index_dir, query_encoder=None, min_idf=0, *, device=None, shard=False, tile_docs=0,
+                 collection: ImpactCollection | None = None):
+        if query_encoder is not None:
+            raise NotImplementedError("only query_encoder=None (token-frequency queries) is used by the reference")
+        if min_idf != 0:
+            raise NotImplementedError("min_idf is fixed at 0 (rule S5), as in the reference")
+        self.collection = collection if collection is not None else ImpactCollection.from_jsonl_dir(
+            _find_collection_dir(index_dir))
+        c = self.collection
+        self.num_docs = c.n_docs
+        self.rank, self.world = _dist_info(shard)
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.device = dev
+        if self.world > 1:
+            lo, hi = c.n_docs * self.rank // self.world, c.n_docs * (self.rank + 1) // self.world
+            indptr, docs, imps = c.shard(lo, hi)
+            self.index = ops.SparseIndex(indptr, docs, imps, hi - lo, device=dev, n_docs_global=c.n_docs,
+                                         df_global=c.df, doc_base=lo, tile_docs=tile_docs)
+        else:
+            self.index = ops.SparseIndex(c.indptr, c.post_docs, c.post_impacts, c.n_docs, device=dev, tile_docs=tile_docs)
+
+    def set_analyzer(self, analyzer):
+        return None
+
+    # -- array-level API (used by the CLI, the fusion path and the benchmarks) --------------------------------
+    def search_arrays(self, queries, k):
+        """queries: list of strings / token->count maps.  Returns host arrays (scores f32, docs i32 internal ids, counts)."""
+        qi, qt, qw = self.collection.encode_queries(queries)
+        if self.world == 1:
+            return self.index.search_host(qi, qt, qw, k)
+        dev = self.device
+        t = lambda a, dt: torch.from_numpy(a.astype(dt)).to(dev)
+        s, d, c = self.index.search(t(qi, np.int64), t(qt, np.int32), t(qw, np.int32), k)
+        self.index.status()
+        nq = len(queries)
+        g_s = torch.empty((self.world, nq, k), dtype=torch.float32, device=dev)
+        g_d = torch.empty((self.world, nq, k), dtype=torch.int32, device=dev)
+        g_c = torch.empty((self.world, nq), dtype=torch.int32, device=dev)
+        torch.distributed.all_gather_into_tensor(g_s, s)
+        torch.distributed.all_gather_into_tensor(g_d, d)
+        torch.distributed.all_gather_into_tensor(g_c, c)
+        ms, md, mc = ops.topk_merge(g_s, g_d, g_c, k)
+        return ms.cpu().numpy(), md.cpu().numpy(), mc.cpu().numpy().astype(np.uint32)
+
+    # -- pyserini surface ---------------------------------------------------------------------------------------
+    def batch_search(self, queries, qids, k=10, threads=1, fields=None):
+        """{qid: [hit, ...]} with hit.docid (str) / hit.score (float).  ``threads`` sized the JVM pool (S10); the
+        whole batch is one kernel launch here."""
+        if len(queries) != len(qids):
+            raise ValueError("queries and qids differ in length")
+        s, d, c = self.search_arrays(list(queries), int(k))
+        docids = self.collection.docids
+        out = {}
+        for i, qid in enumerate(qids):
+            n = int(c[i])
+            out[qid] = [Hit(docids[d[i, j]], float(s[i, j])) for j in range(n)]
+        return out
+
+    def search(self, q, k=10, fields=None):
+        return self.batch_search([q], ["q"], k)["q"]
+
+    def close(self):
+        self.index.close()
+
+
+class _FlatIPIndex:
+    """Stands in for the ``faiss.IndexFlatIP`` object behind ``FaissFlatSearcher.index``."""
+
+    def __init__(self, dim, device, doc_base=0):
+        self.d = int(dim)
+        self._ix = ops.DenseIndex(dim, device=device, doc_base=doc_base)
+
+    @property
+    def ntotal(self):
+        return self._ix.ntotal
+
+    def add(self, x):
+        self._ix.add(x)
+
+    def search(self, x, k, mode=0):
+        return self._ix.search(x, k, mode=mode)
+
+
+class FaissFlatSearcher:
+    def __init__(self, init_reps: np.ndarray, *, device=None, shard=False):
+        """Like tevatron: allocates an EMPTY inner-product index of init_reps.shape[1] dimensions (the reference
+        therefore calls ``add(p_reps_0)`` right after, search.py:232-237)."""
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.device = dev
+        self.rank, self.world = _dist_info(shard)
+        self._n_global = 0
+        self.index = _FlatIPIndex(init_reps.shape[1], dev)
+
+    def add(self, p_reps: np.ndarray):
+        p_reps = np.asarray(p_reps)
+        if self.world > 1:
+            # doc-sharded: this rank keeps rows [lo,hi) of the block being added; ids stay global
+            n = p_reps.shape[0]
+            lo, hi = n * self.rank // self.world, n * (self.rank + 1) // self.world
+            if self.index.ntotal == 0:
+                self.index = _FlatIPIndex(p_reps.shape[1], self.device, doc_base=self._n_global + lo)
+            elif self._shard_base_next != self._n_global + lo:
+                raise NotImplementedError("doc-sharded FaissFlatSearcher supports a single add() (the reference "
+                                          "loads one corpus pickle, search.py:228-237)")
+            self.index.add(p_reps[lo:hi])
+            self._shard_base_next = self._n_global + hi
+            self._n_global += n
+        else:
+            self.index.add(p_reps)
+            self._n_global += p_reps.shape[0]
+
+    def search(self, q_reps: np.ndarray, k: int):
+        q_reps = np.asarray(q_reps, dtype=np.float32)
+        if self.world == 1:
+            return self.index.search(q_reps, k)
+        dev = self.device
+        kk = min(int(k), ops.MSR_MAX_K)
+        s, ids = self.index.search(torch.from_numpy(q_reps).to(dev), kk)
+        nq = q_reps.shape[0]
+        cnt = (ids >= 0).sum(1).to(torch.int32)
+        g_s = torch.empty((self.world, nq, kk), dtype=torch.float32, device=dev)
+        g_d = torch.empty((self.world, nq, kk), dtype=torch.int32, device=dev)
+        g_c = torch.empty((self.world, nq), dtype=torch.int32, device=dev)
+        torch.distributed.all_gather_into_tensor(g_s, s.contiguous())
+        torch.distributed.all_gather_into_tensor(g_d, ids.to(torch.int32).contiguous())
+        torch.distributed.all_gather_into_tensor(g_c, cnt)
+        ms, md, mc = ops.topk_merge(g_s, g_d, g_c, kk)
+        ms, md, mc = ms.cpu().numpy(), md.cpu().numpy().astype(np.int64), mc.cpu().numpy()
+        pad = np.arange(kk)[None, :] >= mc[:, None]
+        ms[pad] = -3.4028234663852886e38
+        md[pad] = -1
+        return ms, md
+
+    def batch_search(self, q_reps: np.ndarray, k: int, batch_size: int, quiet: bool = False):
+        """tevatron loops over ``batch_size`` chunks and concatenates; chunking does not change any result."""
+        q_reps = np.asarray(q_reps, dtype=np.float32)
+        n = q_reps.shape[0]
+        if batch_size <= 0 or n <= batch_size:
+            return self.search(q_reps, k)
+        scores, ids = [], []
+        # chunk at a multiple of batch_size that keeps the launches large
+        step = max(batch_size, (4096 // batch_size) * batch_size)
+        for lo in range(0, n, step):
+            s, i = self.search(q_reps[lo:lo + step], k)
+            scores.append(s); ids.append(i)
+        return np.concatenate(scores, 0), np.concatenate(ids, 0)

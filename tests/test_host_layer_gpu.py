@@ -1,0 +1,160 @@
+"""GPU tests of the reference-facing Python surface: LuceneImpactSearcher / FaissFlatSearcher / hybrid.fuse."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "reference_glue.json")
+
+
+@pytest.fixture(scope="module")
+def golden():
+    with open(GOLDEN) as f:
+        return json.load(f)
+
+
+def untyped(tv):
+    tag, v = tv
+    return np.float32(v) if tag == "f32" else (float(v) if tag == "f64" else int(v))
+
+
+def test_fuse_dict_api_bit_exact_vs_reference(golden, lib_built):
+    from mllm_sparse_retrieval_b200.hybrid import fuse, fuse_statistic, get_run_dict
+    for case in golden["fuse"]:
+        qids = case["qids"]
+        dense = get_run_dict(qids, [[np.float32(x) for x in d["scores"]] for d in case["dense"]],
+                             [d["docs"] for d in case["dense"]], case["remove_query"])
+        sparse = get_run_dict(qids, [[float(x) for x in s["scores"]] for s in case["sparse"]],
+                              [s["docs"] for s in case["sparse"]], case["remove_query"])
+        w = [case["alpha"], 1 - case["alpha"]]
+        fused = fuse([dense, sparse], w)
+        for qid in qids:
+            exp = case["fused"][qid]
+            got = list(fused[qid].items())
+            assert [d for d, _ in got] == [d for d, _ in exp]
+            for (_, gv), (_, ev) in zip(got, exp):
+                e = untyped(ev)
+                assert type(gv) is type(e)
+                assert gv == e, (qid, gv, e)
+        stat = fuse_statistic([dense, sparse], w)
+        for qid in qids:
+            assert [(d, r.type) for d, r in stat[qid].items()] == [tuple(x) for x in case["fused_tags"][qid]]
+
+
+def _write_collection(tmp_path, rng, n_docs, vocab, nnz):
+    d = tmp_path / "sparse_output"
+    (d / "index").mkdir(parents=True)                      # Lucene's directory: present but ignored
+    ids = [str(x) for x in rng.permutation(n_docs * 3)[:n_docs]]
+    vecs = []
+    with open(d / "corpus_0.jsonl", "w") as f:
+        for i in ids:
+            toks = rng.choice(len(vocab), size=nnz, replace=False)
+            vec = {vocab[t]: int(rng.integers(0, 300)) for t in toks}      # some zero weights (never indexed)
+            vecs.append(vec)
+            f.write(json.dumps({"id": i, "content": "", "vector": vec}) + "\n")
+    return d, ids, vecs
+
+
+def test_lucene_impact_searcher_dropin(oracle, lib_built, tmp_path):
+    from mllm_sparse_retrieval_b200.searchers import JWhiteSpaceAnalyzer, LuceneImpactSearcher
+    rng = np.random.default_rng(3)
+    vocab = [f"tok{i}" for i in range(400)] + ["ġcat", "▁tree", "dog"]
+    d, ids, vecs = _write_collection(tmp_path, rng, 700, vocab, 24)
+    s = LuceneImpactSearcher(os.path.join(str(d), "index"), None)          # as search.py:273 passes it
+    s.set_analyzer(JWhiteSpaceAnalyzer())
+    assert s.num_docs == 700
+    topics, qids = [], []
+    for q in range(20):
+        toks = rng.choice(len(vocab), size=10, replace=False)
+        text = ""
+        for t in toks:
+            text += (" " + vocab[t]) * int(rng.integers(0, 40))
+        topics.append((text + " unknown_token unknown_token").strip())
+        qids.append(f"q{q}")
+    topics.append(""); qids.append("empty")
+    res = s.batch_search(topics, qids, 50, threads=16)
+    # oracle on the same collection, through its own restatement of S1/S4/S8
+    order = sorted(range(len(ids)), key=lambda i: ids[i].encode())
+    internal = {ids[i]: r for r, i in enumerate(order)}
+    terms = {}
+    trip = []
+    for i, vec in zip(ids, vecs):
+        for tok, w in vec.items():
+            if w > 0:
+                trip.append((terms.setdefault(tok, len(terms)), internal[i], w))
+    trip.sort()
+    a = np.array(trip, dtype=np.int64)
+    indptr = np.zeros(len(terms) + 1, dtype=np.uint64)
+    np.cumsum(np.bincount(a[:, 0], minlength=len(terms)), out=indptr[1:])
+    qi, qt, qw = [0], [], []
+    for text in topics:
+        for tok, c in oracle.query_string_to_counts(text).items():
+            if tok in terms:
+                qt.append(terms[tok]); qw.append(c)
+        qi.append(len(qt))
+    es, ed, ec = oracle.impact_search_c(indptr, a[:, 1], a[:, 2], 700, np.array(qi, np.uint64), np.array(qt, np.uint32),
+                                        np.array(qw, np.uint32), 50)
+    sorted_ids = [ids[i] for i in order]
+    for r, qid in enumerate(qids):
+        hits = res[qid]
+        assert len(hits) == ec[r]
+        assert [h.docid for h in hits] == [sorted_ids[x] for x in ed[r, :ec[r]]]
+        assert [h.score for h in hits] == [float(x) for x in es[r, :ec[r]]]
+        assert all(isinstance(h.score, float) and isinstance(h.docid, str) for h in hits)
+    assert res["empty"] == []
+
+
+def test_faiss_flat_searcher_dropin(oracle, lib_built):
+    from mllm_sparse_retrieval_b200 import synth
+    from mllm_sparse_retrieval_b200.searchers import FaissFlatSearcher
+    docs, q = synth.make_dense(1500, 9, dim=256, seed=5)
+    docs, q = docs.numpy(), q.numpy()
+    r = FaissFlatSearcher(docs)
+    assert r.index.ntotal == 0                              # tevatron allocates only; the reference adds next
+    r.add(docs)
+    assert r.index.ntotal == 1500
+    s1, i1 = r.search(q, 20)
+    s2, i2 = r.batch_search(q, 20, 2, True)
+    np.testing.assert_array_equal(i1, i2)
+    np.testing.assert_array_equal(s1, s2)
+    assert s1.dtype == np.float32 and i1.dtype == np.int64
+    es, ei = oracle.flat_ip_search_numpy(docs, q, 20)
+    np.testing.assert_array_equal(i1, ei)
+    np.testing.assert_allclose(s1, es, rtol=1e-3, atol=1e-6)
+
+
+def test_end_to_end_hybrid_like_search_py(oracle, lib_built, tmp_path):
+    """The reference's own loop shape: sparse_search + search_queries + get_run_dict + fuse (search.py:55-99,455-461)."""
+    from mllm_sparse_retrieval_b200.hybrid import fuse, get_run_dict
+    from mllm_sparse_retrieval_b200.searchers import FaissFlatSearcher, LuceneImpactSearcher
+    from mllm_sparse_retrieval_b200 import synth
+    rng = np.random.default_rng(8)
+    vocab = [f"w{i}" for i in range(300)]
+    d, ids, vecs = _write_collection(tmp_path, rng, 400, vocab, 30)
+    sparse = LuceneImpactSearcher(os.path.join(str(d), "index"), None)
+    reps, qreps = synth.make_dense(400, 6, dim=128, seed=9)
+    dense = FaissFlatSearcher(reps.numpy()); dense.add(reps.numpy())
+    look_up = ids
+    batch_ids = [ids[3], ids[10], "nohit", ids[7], "x1", "x2"]
+    topics = [" ".join(rng.choice(vocab, size=15)) for _ in batch_ids]
+    depth = 100
+    # sparse_search (search.py:85-99)
+    results = sparse.batch_search(topics, batch_ids, depth, threads=16)
+    sparse_scores = [[h.score for h in results[i]] for i in batch_ids]
+    sparse_rank = [[h.docid for h in results[i]] for i in batch_ids]
+    # search_queries (search.py:55-63)
+    all_scores, all_idx = dense.batch_search(qreps.numpy(), depth, 2, True)
+    psg = np.array([[str(look_up[x]) for x in row] for row in all_idx])
+    dense_run = get_run_dict(batch_ids, all_scores, psg, True)
+    sparse_run = get_run_dict(batch_ids, sparse_scores, sparse_rank, True)
+    fused = fuse([dense_run, sparse_run], [0.5, 0.5])
+    exp = oracle.fuse([oracle.get_run_dict(batch_ids, all_scores, psg, True),
+                       oracle.get_run_dict(batch_ids, sparse_scores, sparse_rank, True)], [0.5, 0.5])
+    for qid in batch_ids:
+        assert list(fused[qid].keys()) == list(exp[qid].keys())
+        for doc in exp[qid]:
+            assert fused[qid][doc] == exp[qid][doc] and type(fused[qid][doc]) is type(exp[qid][doc])
+        assert qid not in fused[qid]
