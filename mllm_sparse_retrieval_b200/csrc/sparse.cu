@@ -5,9 +5,16 @@
 //
 // HBM layout (built once by msr_sparse_index_build):
 //   * the doc id space of the shard is cut into n_tiles contiguous tiles of tile_docs docs (<= 65536);
-//   * postings are bucketed by (tile, term) and packed into ONE u32 each: (impact << 16) | (doc - tile_lo),
-//     ascending doc inside a bucket.  4 B/posting physical against the canonical 6 B (u32 docid + u16 impact)
-//     that SURVEY.md 8(d) fixes as the algorithmic figure;
+//   * postings are bucketed by (tile, term) and packed into ONE u32 each: (impact << 16) | (doc - tile_lo).
+//     4 B/posting physical against the canonical 6 B (u32 docid + u16 impact) that SURVEY.md 8(d) fixes as the
+//     algorithmic figure;
+//   * buckets of at most kSmallBucket postings keep ascending doc order.  Larger buckets are laid out
+//     BANK-CONFLICT-FREE: the bucket is cut into G = max(ceil(n/32), max postings per shared-memory bank)
+//     groups of 32 slots, postings are dealt round-robin (bank-major) over the groups so that no group holds
+//     two docs of the same bank (doc & 31), and the free slots of a group are filled with impact-0 postings on
+//     the group's unused banks.  One warp-wide shared-memory atomic per group then costs one wavefront
+//     instead of the ~3.5 a random 32-doc group costs.  Integer adds commute, so the order inside a bucket
+//     never changes a score;
 //   * seg_ptr[tile * n_terms + term] = first posting of the bucket (u32, one flat array, +1 sentinel);
 //   * term_keep[term] = rule S5 with collection-wide df / N;  term_maximp[term] = max impact (range checks).
 //
@@ -20,22 +27,19 @@
 // (topk.cu) produces the final sorted list.
 #include <cub/device/device_scan.cuh>
 
+#include <stdlib.h>
+
 #include <vector>
 
 #include "common.cuh"
+#include "sparse_kernel.cuh"
 
 namespace msr {
 
-constexpr int kThreads = 512;
-constexpr int kWarps = kThreads / 32;
-constexpr int kSegMax = 256;      // query terms staged per pass
-constexpr int kUnroll = 8;        // loads in flight per lane
-constexpr int kChunk = 32 * kUnroll;
-constexpr int kBins = 2048;
-constexpr int kBinBits = 11;
-constexpr int kCandMax = 1024;
 constexpr uint32_t kDefaultTileDocs = 24576;   // 96 KB of accumulators -> 2 CTAs per SM
 constexpr uint32_t kMaxTileDocs = 53248;       // 208 KB of accumulators + staging = the 227 KB opt-in limit
+constexpr uint32_t kSmallBucket = 96;          // buckets above this size get the bank-conflict-free layout
+constexpr int kBuildWarps = 8;                 // warps per CTA of the bucket layout kernels
 
 int topk_merge_keys_launch(uint32_t nq, uint32_t n_lists, uint32_t stride, const uint64_t* keys,
                            const uint32_t* cnts, uint32_t k, float* out_scores, int32_t* out_docs,
@@ -47,9 +51,9 @@ struct msr_sparse_index {
     int device = 0;
     uint32_t n_docs = 0, n_terms = 0, tile_docs = 0, n_tiles = 0, n_docs_global = 0;
     int32_t doc_base = 0;
-    uint64_t nnz = 0;
+    uint64_t nnz = 0, n_slots = 0;    // real postings / posting slots incl. the padding of conflict-free buckets
     uint32_t* seg_ptr = nullptr;      // [n_tiles*n_terms + 1]
-    uint32_t* postings = nullptr;     // [nnz]
+    uint32_t* postings = nullptr;     // [n_slots]
     uint8_t* term_keep = nullptr;     // [n_terms]
     uint16_t* term_maximp = nullptr;  // [n_terms]
     uint32_t* df_local = nullptr;     // [n_terms]
@@ -58,6 +62,7 @@ struct msr_sparse_index {
     msr::Workspace ws;
     size_t resident_bytes = 0;
     // optional per-kernel timing (msr_sparse_profile): events bracket every score / merge launch on the stream
+    bool use_theta = true;            // cross-tile threshold sharing (MSR_SPARSE_NO_THETA=1 in the environment disables)
     bool profiling = false;
     std::vector<cudaEvent_t> ev;      // triples: before score, after score, after merge
     size_t ev_used = 0;
@@ -113,6 +118,92 @@ __global__ void build_scatter_kernel(const uint64_t* __restrict__ indptr, const 
     }
 }
 
+__global__ void sum_u32_kernel(const uint32_t* __restrict__ x, size_t n, unsigned long long* __restrict__ out) {
+    unsigned long long a = 0;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) a += x[i];
+    for (int o = 16; o > 0; o >>= 1) a += __shfl_xor_sync(0xffffffffu, a, o);
+    if ((threadIdx.x & 31) == 0 && a) atomicAdd(out, a);
+}
+
+// Per-bank posting counts of one large bucket (lane b returns the count of bank b); hist = 32 u32 of this warp.
+__device__ __forceinline__ uint32_t bucket_bank_counts(const uint32_t* __restrict__ stage, uint32_t n, uint32_t* hist,
+                                                       uint32_t lane) {
+    hist[lane] = 0;
+    __syncwarp();
+    for (uint32_t i = lane; i < n; i += 32) atomicAdd(&hist[stage[i] & 31u], 1u);
+    __syncwarp();
+    return hist[lane];
+}
+
+// Pass 1 of the bucket layout: slots each bucket occupies (n for small buckets, 32*G for large ones).
+__global__ void __launch_bounds__(kBuildWarps * 32)
+build_plan_kernel(const uint32_t* __restrict__ seg0, const uint32_t* __restrict__ stage, size_t n_buckets,
+                  uint32_t* __restrict__ slots) {
+    __shared__ uint32_t hist[kBuildWarps][32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (size_t b = (size_t)blockIdx.x * kBuildWarps + warp; b < n_buckets; b += (size_t)gridDim.x * kBuildWarps) {
+        const uint32_t lo = seg0[b], n = seg0[b + 1] - lo;
+        if (n <= kSmallBucket) {
+            if (lane == 0) slots[b] = n;
+            continue;
+        }
+        uint32_t c = bucket_bank_counts(stage + lo, n, hist[warp], lane);
+        const uint32_t g0 = (n + 31) / 32, G = max(g0, warp_reduce_max(c));
+        if (lane == 0) slots[b] = G <= 2 * g0 ? G * 32 : n;     // skewed banks: keep doc order, no padding
+        __syncwarp();
+    }
+}
+
+// Pass 2: write the final posting array.  Large buckets: posting number s (bank-major order) goes to group s % G,
+// slot s / G; the unused slots of a group get impact-0 postings on the group's free banks.
+__global__ void __launch_bounds__(kBuildWarps * 32)
+build_layout_kernel(const uint32_t* __restrict__ seg0, const uint32_t* __restrict__ stage, size_t n_buckets,
+                    const uint32_t* __restrict__ seg_ptr, uint32_t* __restrict__ postings) {
+    __shared__ uint32_t hist[kBuildWarps][32];
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t lt = (1u << lane) - 1u;
+    for (size_t b = (size_t)blockIdx.x * kBuildWarps + warp; b < n_buckets; b += (size_t)gridDim.x * kBuildWarps) {
+        const uint32_t lo = seg0[b], n = seg0[b + 1] - lo;
+        uint32_t* out = postings + seg_ptr[b];
+        if (n <= kSmallBucket) {
+            for (uint32_t i = lane; i < n; i += 32) out[i] = stage[lo + i];
+            continue;
+        }
+        uint32_t c = bucket_bank_counts(stage + lo, n, hist[warp], lane);
+        const uint32_t g0 = (n + 31) / 32, G = max(g0, warp_reduce_max(c));
+        __syncwarp();
+        if (G > 2 * g0) {
+            for (uint32_t i = lane; i < n; i += 32) out[i] = stage[lo + i];
+            continue;
+        }
+        hist[warp][lane] = warp_incl_scan(c, lane) - c;          // first sequence number of each bank
+        __syncwarp();
+        for (uint32_t i = 0; i < n; i += 32) {
+            const uint32_t idx = i + lane;
+            const bool act = idx < n;
+            const uint32_t v = act ? stage[lo + idx] : 0u;
+            const uint32_t bank = v & 31u;
+            const uint32_t m = __match_any_sync(0xffffffffu, act ? bank : 32u + lane);
+            const uint32_t r = __popc(m & lt);
+            uint32_t s = 0;
+            if (act) s = hist[warp][bank] + r;
+            __syncwarp();
+            if (act && r == 0) hist[warp][bank] += __popc(m);
+            __syncwarp();
+            if (act) out[(s % G) * 32 + s / G] = v;
+        }
+        __syncwarp();
+        for (uint32_t g = 0; g < G; ++g) {
+            const bool real = lane * G + g < n;
+            const uint32_t v = real ? out[g * 32 + lane] : 0u;
+            const uint32_t used = __reduce_or_sync(0xffffffffu, real ? (1u << (v & 31u)) : 0u);
+            const uint32_t pads = __ballot_sync(0xffffffffu, !real);
+            if (!real) out[g * 32 + lane] = __fns(~used, 0, __popc(pads & lt) + 1);
+        }
+        __syncwarp();
+    }
+}
+
 __global__ void build_term_meta_kernel(const uint64_t* __restrict__ indptr, const uint32_t* __restrict__ df_global,
                                        const uint32_t* __restrict__ maximp32, uint32_t n_terms, uint32_t n_docs_global,
                                        uint8_t* __restrict__ keep, uint16_t* __restrict__ maximp, uint32_t* __restrict__ df_local) {
@@ -124,289 +215,6 @@ __global__ void build_term_meta_kernel(const uint64_t* __restrict__ indptr, cons
     keep[t] = (df > 0 && df + 1 < (uint64_t)n_docs_global) ? 1 : 0;
     maximp[t] = (uint16_t)maximp32[t];
     df_local[t] = dfl;
-}
-
-// ---------------------------------------------------------------------------------------------------------
-// search kernel
-// ---------------------------------------------------------------------------------------------------------
-struct SearchParams {
-    const uint32_t* seg_ptr;
-    const uint32_t* postings;
-    const uint8_t* term_keep;
-    const uint16_t* term_maximp;
-    uint32_t n_docs, n_terms, tile_docs, n_tiles;
-    int32_t doc_base;
-    const uint64_t* q_indptr;
-    const uint32_t* q_terms;
-    const uint32_t* q_weights;
-    uint32_t q_lo, nq, k, k_stride;
-    uint64_t* cand_keys;   // [nq][n_tiles][k_stride]
-    uint32_t* cand_cnt;    // [nq][n_tiles]
-    uint32_t* status;
-};
-
-__device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t* p) {
-    uint32_t v;
-    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
-    return v;
-}
-
-struct SegStage {                      // streaming phase view of the union region
-    uint32_t start[kSegMax];
-    uint32_t len[kSegMax];
-    uint32_t w[kSegMax];               // bit 31 = "product may reach 2^24: round per term" (S6)
-    uint32_t pref[kSegMax + 1];        // exclusive prefix of chunk counts
-};
-struct SelStage {                      // epilogue view of the union region
-    uint32_t hist[kBins];
-    uint64_t cand[kCandMax];
-};
-union StageUnion {
-    SegStage seg;
-    SelStage sel;
-};
-struct SmallState {
-    unsigned long long bound;
-    uint32_t wmax, vmax, hits, out_cnt, cand_cnt, sel_b, sel_clt, sel_bcount;
-    uint32_t wsum[kWarps];
-};
-
-// exclusive scan of one value per thread over the CTA (kThreads threads); returns exclusive prefix, *total = sum
-__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* wsum, uint32_t* total) {
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    uint32_t inc = warp_incl_scan(v, lane);
-    __syncthreads();                       // wsum may still be read from a previous call
-    if (lane == 31) wsum[warp] = inc;
-    __syncthreads();
-    uint32_t base = 0, tot = 0;
-#pragma unroll
-    for (int w = 0; w < kWarps; ++w) {
-        uint32_t x = wsum[w];
-        if (w < warp) base += x;
-        tot += x;
-    }
-    *total = tot;
-    return base + inc - v;
-}
-
-__global__ void __launch_bounds__(kThreads, 2)
-sparse_score_topk_kernel(const SearchParams P) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    StageUnion* U = reinterpret_cast<StageUnion*>(smem_raw);
-    SmallState* S = reinterpret_cast<SmallState*>(smem_raw + sizeof(StageUnion));
-    uint32_t* acc = reinterpret_cast<uint32_t*>(smem_raw + sizeof(StageUnion) + sizeof(SmallState));
-
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t q = blockIdx.x % P.nq;
-    const uint32_t tile = blockIdx.x / P.nq;
-    const uint32_t tile_lo = tile * P.tile_docs;
-    const uint32_t tl = min(P.tile_docs, P.n_docs - tile_lo);
-    const uint64_t qs = P.q_indptr[P.q_lo + q], qe = P.q_indptr[P.q_lo + q + 1];
-    const uint32_t* seg_row = P.seg_ptr + (size_t)tile * P.n_terms;
-    uint64_t* keys_out = P.cand_keys + ((size_t)q * P.n_tiles + tile) * P.k_stride;
-    uint32_t* cnt_out = P.cand_cnt + (size_t)q * P.n_tiles + tile;
-
-    for (uint32_t i = tid; i < tl; i += kThreads) acc[i] = 0;
-    if (tid == 0) {
-        S->bound = 0; S->wmax = 0; S->vmax = 0; S->hits = 0; S->out_cnt = 0; S->cand_cnt = 0;
-    }
-    __syncthreads();
-
-    // ---- exact-arithmetic range check over the whole query (see msr.h) ----
-    {
-        unsigned long long b = 0;
-        uint32_t wm = 0;
-        for (uint64_t j = qs + tid; j < qe; j += kThreads) {
-            uint32_t t = P.q_terms[j], w = P.q_weights[j];
-            if (t < P.n_terms && w && P.term_keep[t]) {
-                b += (unsigned long long)w * P.term_maximp[t];
-                wm = max(wm, w);
-            }
-        }
-        if (b) atomicAdd(&S->bound, b);
-        if (wm) atomicMax(&S->wmax, wm);
-    }
-    __syncthreads();
-    if (S->bound >= (1ull << 31) || S->wmax > 65535u) {
-        if (tid == 0) { atomicOr(P.status, 1u); *cnt_out = 0; }
-        return;
-    }
-
-    // ---- phase 1: stream the query's buckets of this tile, accumulate integer impacts ----
-    for (uint64_t batch = qs; batch < qe; batch += kSegMax) {
-        __syncthreads();   // previous batch fully consumed
-        uint32_t nchunks = 0;
-        if (tid < kSegMax) {
-            uint32_t len = 0, start = 0, w = 0;
-            uint64_t j = batch + tid;
-            if (j < qe) {
-                uint32_t t = P.q_terms[j];
-                w = P.q_weights[j];
-                if (t < P.n_terms && w && P.term_keep[t]) {
-                    start = seg_row[t];
-                    len = seg_row[t + 1] - start;
-                    if ((uint64_t)w * P.term_maximp[t] >= (1u << 24)) w |= 0x80000000u;
-                }
-            }
-            U->seg.start[tid] = start;
-            U->seg.len[tid] = len;
-            U->seg.w[tid] = w;
-            nchunks = (len + kChunk - 1) / kChunk;
-        }
-        uint32_t total;
-        uint32_t ex = block_excl_scan(nchunks, S->wsum, &total);
-        if (tid < kSegMax) U->seg.pref[tid] = ex;
-        if (tid == 0) U->seg.pref[kSegMax] = total;
-        __syncthreads();
-
-        uint32_t seg = 0;
-        for (uint32_t g = warp; g < total; g += kWarps) {
-            while (U->seg.pref[seg + 1] <= g) ++seg;          // monotone in g; empty buckets are skipped
-            const uint32_t off = (g - U->seg.pref[seg]) * kChunk;
-            const uint32_t n = min((uint32_t)kChunk, U->seg.len[seg] - off);
-            const uint32_t* src = P.postings + U->seg.start[seg] + off + lane;
-            const uint32_t wraw = U->seg.w[seg];
-            const uint32_t w = wraw & 0x7FFFFFFFu;
-            uint32_t v[kUnroll];
-#pragma unroll
-            for (int u = 0; u < kUnroll; ++u) v[u] = (u * 32 + lane < n) ? ld_stream_u32(src + u * 32) : 0u;
-            if (!(wraw >> 31)) {
-#pragma unroll
-                for (int u = 0; u < kUnroll; ++u)
-                    if (u * 32 + lane < n) atomicAdd(&acc[v[u] & 0xFFFFu], (v[u] >> 16) * w);
-            } else {                                            // S6: float32(boost*freq) per term
-#pragma unroll
-                for (int u = 0; u < kUnroll; ++u)
-                    if (u * 32 + lane < n) atomicAdd(&acc[v[u] & 0xFFFFu], (uint32_t)__uint2float_rn((v[u] >> 16) * w));
-            }
-        }
-    }
-    __syncthreads();
-
-    // ---- phase 2: top-k of the tile by (float32(score) desc, doc asc) ----
-    {
-        uint32_t m = 0, h = 0;
-        for (uint32_t i = tid; i < tl; i += kThreads) {
-            uint32_t a = acc[i];
-            m = max(m, a);
-            h += (a != 0);
-        }
-        m = warp_reduce_max(m);
-        h = warp_reduce_add(h);
-        if (lane == 0) {
-            if (m) atomicMax(&S->vmax, m);
-            if (h) atomicAdd(&S->hits, h);
-        }
-    }
-    __syncthreads();
-    const uint32_t vmax = S->vmax, hits = S->hits;
-    const uint32_t kq = min(P.k, tl);
-    const uint32_t gdoc0 = (uint32_t)P.doc_base + tile_lo;
-    if (hits == 0) {
-        if (tid == 0) *cnt_out = 0;
-        return;
-    }
-    if (hits <= kq) {                                           // S7: fewer hits than k -> all of them
-        for (uint32_t i = tid; i < tl; i += kThreads) {
-            uint32_t a = acc[i];
-            if (a) keys_out[atomicAdd(&S->out_cnt, 1u)] = make_key(__uint2float_rn(a), gdoc0 + i);
-        }
-        if (tid == 0) *cnt_out = hits;
-        return;
-    }
-    // selection key: integers below 2^24 are their own float32 image; above, rank by the rounded float (S6)
-    const bool use_f = vmax >= (1u << 24);
-#define MSR_SELKEY(a) (use_f ? __float_as_uint(__uint2float_rn(a)) : (a))
-    const uint32_t kmax = MSR_SELKEY(vmax);
-    uint32_t remaining = kq, sh_prev = 32 - __clz(kmax), pref = 0, s = 0, cand_count = 0;
-    for (;;) {
-        s = sh_prev > kBinBits ? sh_prev - kBinBits : 0;
-        const uint32_t width = sh_prev - s;
-        for (uint32_t i = tid; i < kBins; i += kThreads) U->sel.hist[i] = 0;
-        __syncthreads();
-        for (uint32_t i = tid; i < tl; i += kThreads) {
-            uint32_t a = acc[i];
-            if (a) {
-                uint32_t d = kmax - MSR_SELKEY(a);
-                uint32_t hi = sh_prev >= 32 ? 0u : (d >> sh_prev);
-                if (hi == pref) atomicAdd(&U->sel.hist[(d >> s) & ((1u << width) - 1u)], 1u);
-            }
-        }
-        __syncthreads();
-        {
-            uint32_t h4[4], ls = 0;
-#pragma unroll
-            for (int j = 0; j < 4; ++j) { h4[j] = U->sel.hist[tid * 4 + j]; ls += h4[j]; }
-            uint32_t total;
-            uint32_t ex = block_excl_scan(ls, S->wsum, &total);
-#pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                if (ex < remaining && ex + h4[j] >= remaining) {
-                    S->sel_b = tid * 4 + j; S->sel_clt = ex; S->sel_bcount = h4[j];
-                }
-                ex += h4[j];
-            }
-        }
-        __syncthreads();
-        remaining -= S->sel_clt;
-        pref = (width >= 32 ? 0u : (pref << width)) | S->sel_b;
-        sh_prev = s;
-        cand_count = S->sel_bcount;
-        if (cand_count <= (uint32_t)kCandMax || s == 0) break;
-    }
-    const uint32_t n_def = kq - remaining;                      // docs strictly better than the candidate bin
-    const bool collect = cand_count <= (uint32_t)kCandMax;
-    for (uint32_t i = tid; i < tl; i += kThreads) {
-        uint32_t a = acc[i];
-        if (a) {
-            uint32_t d = kmax - MSR_SELKEY(a);
-            uint32_t x = d >> s;
-            if (x < pref) {
-                keys_out[atomicAdd(&S->out_cnt, 1u)] = make_key(__uint2float_rn(a), gdoc0 + i);
-            } else if (x == pref && collect) {
-                // descending sort of ~((d<<32)|i)  ==  ascending (d, i)  ==  best first
-                U->sel.cand[atomicAdd(&S->cand_cnt, 1u)] = ~(((uint64_t)d << 32) | i);
-            }
-        }
-    }
-    __syncthreads();
-    if (collect) {
-        uint32_t n2 = 2;
-        while (n2 < cand_count) n2 <<= 1;
-        for (uint32_t i = cand_count + tid; i < n2; i += kThreads) U->sel.cand[i] = 0;
-        bitonic_sort_desc(U->sel.cand, n2);
-        for (uint32_t r = tid; r < remaining; r += kThreads) {
-            uint32_t i = (uint32_t)(~U->sel.cand[r]);
-            keys_out[n_def + r] = make_key(__uint2float_rn(acc[i]), gdoc0 + i);
-        }
-    } else {
-        // more than kCandMax docs tie exactly at the threshold key: take the `remaining` smallest doc ids (S8)
-        const uint32_t per = ((tl + kWarps - 1) / kWarps + 31) & ~31u;
-        const uint32_t lo = warp * per, hi = min(tl, lo + per);
-        uint32_t c = 0;
-        for (uint32_t base = lo; base < hi; base += 32) {
-            uint32_t i = base + lane;
-            uint32_t a = i < hi ? acc[i] : 0;
-            bool f = a && (kmax - MSR_SELKEY(a)) == pref;
-            c += __popc(__ballot_sync(0xffffffffu, f));
-        }
-        __syncthreads();
-        if (lane == 0) S->wsum[warp] = c;
-        __syncthreads();
-        uint32_t run = 0;
-        for (uint32_t w2 = 0; w2 < warp; ++w2) run += S->wsum[w2];
-        for (uint32_t base = lo; base < hi; base += 32) {
-            uint32_t i = base + lane;
-            uint32_t a = i < hi ? acc[i] : 0;
-            bool f = a && (kmax - MSR_SELKEY(a)) == pref;
-            uint32_t b = __ballot_sync(0xffffffffu, f);
-            uint32_t r = run + __popc(b & ((1u << lane) - 1u));
-            if (f && r < remaining) keys_out[n_def + r] = make_key(__uint2float_rn(a), gdoc0 + i);
-            run += __popc(b);
-        }
-    }
-#undef MSR_SELKEY
-    if (tid == 0) *cnt_out = kq;
 }
 
 __global__ void query_work_kernel(const uint8_t* __restrict__ keep, const uint32_t* __restrict__ df_local,
@@ -494,6 +302,7 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
     if (!h) { set_error("msr_sparse_index_build: out of host memory"); return MSR_ERR_NOMEM; }
     h->device = device; h->n_docs = n_docs; h->n_terms = n_terms; h->tile_docs = tile_docs; h->n_tiles = n_tiles;
     h->n_docs_global = n_docs_global; h->doc_base = doc_base; h->nnz = nnz;
+    { const char* e = getenv("MSR_SPARSE_NO_THETA"); h->use_theta = !(e && e[0] == '1'); }
     const size_t n_seg = (size_t)n_tiles * n_terms + 1;
     DevBuf b_cnt, b_max32, b_bad, b_tmp;
     cudaError_t e = cudaSuccess;
@@ -503,14 +312,15 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
         return (int)MSR_ERR_CUDA;
     };
     if ((e = cudaMalloc(&h->seg_ptr, n_seg * 4)) != cudaSuccess) return fail("alloc seg_ptr");
-    if ((e = cudaMalloc(&h->postings, (nnz ? nnz : 1) * 4)) != cudaSuccess) return fail("alloc postings");
     if ((e = cudaMalloc(&h->term_keep, n_terms)) != cudaSuccess) return fail("alloc term_keep");
     if ((e = cudaMalloc(&h->term_maximp, (size_t)n_terms * 2)) != cudaSuccess) return fail("alloc term_maximp");
     if ((e = cudaMalloc(&h->df_local, (size_t)n_terms * 4)) != cudaSuccess) return fail("alloc df_local");
     if ((e = cudaMalloc(&h->status, 4)) != cudaSuccess) return fail("alloc status");
     if ((e = cudaMalloc(&h->work, 16)) != cudaSuccess) return fail("alloc work");
-    h->resident_bytes = n_seg * 4 + (nnz ? nnz : 1) * 4 + n_terms * 7ull + 20;
+    DevBuf b_seg0, b_stage;
     if ((e = b_cnt.alloc(n_seg * 4)) != cudaSuccess) return fail("alloc cnt");
+    if ((e = b_seg0.alloc(n_seg * 4)) != cudaSuccess) return fail("alloc seg0");
+    if ((e = b_stage.alloc((nnz ? nnz : 1) * 4)) != cudaSuccess) return fail("alloc stage");
     if ((e = b_max32.alloc((size_t)n_terms * 4)) != cudaSuccess) return fail("alloc maximp32");
     if ((e = b_bad.alloc(4)) != cudaSuccess) return fail("alloc bad");
     cudaMemsetAsync(b_cnt.p, 0, n_seg * 4, s);
@@ -518,6 +328,7 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
     cudaMemsetAsync(b_bad.p, 0, 4, s);
     cudaMemsetAsync(h->status, 0, 4, s);
 
+    // 1. validate + count postings per (tile, term) bucket
     const int bt = 256;
     const int grid = (int)std::min<uint64_t>((nnz + bt - 1) / bt, 148ull * 32);
     if (nnz) {
@@ -525,28 +336,58 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
                                                b_cnt.as<uint32_t>(), b_max32.as<uint32_t>(), b_bad.as<uint32_t>());
         count_launch();
     }
-    size_t tmp_bytes = 0;
-    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, b_cnt.as<uint32_t>(), h->seg_ptr, n_seg, s);
-    if ((e = b_tmp.alloc(tmp_bytes)) != cudaSuccess) return fail("alloc scan temp");
-    if ((e = cub::DeviceScan::ExclusiveSum(b_tmp.p, tmp_bytes, b_cnt.as<uint32_t>(), h->seg_ptr, n_seg, s)) != cudaSuccess)
-        return fail("bucket scan");
-    if (nnz) {
-        build_scatter_kernel<<<grid, bt, 0, s>>>(d_indptr, d_docids, d_impacts, nnz, n_terms, tile_docs, h->seg_ptr, h->postings);
-        count_launch();
-    }
-    build_term_meta_kernel<<<(n_terms + bt - 1) / bt, bt, 0, s>>>(d_indptr, d_df, b_max32.as<uint32_t>(), n_terms,
-                                                                  n_docs_global, h->term_keep, h->term_maximp, h->df_local);
-    count_launch();
     uint32_t bad = 0;
     if ((e = cudaMemcpyAsync(&bad, b_bad.p, 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail("read flags");
-    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail("build kernels");
-    if ((e = cudaGetLastError()) != cudaSuccess) return fail("build kernels (launch)");
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail("count kernel");
     if (bad) {
         set_error("msr_sparse_index_build: malformed CSR (%s%s)", (bad & 1) ? "docid out of range or impact 0; " : "",
                   (bad & 2) ? "docids not strictly ascending within a term" : "");
         msr_sparse_index_destroy(h);
         return MSR_ERR_INVALID;
     }
+    // 2. bucket the postings in doc order into a staging array
+    uint32_t* seg0 = b_seg0.as<uint32_t>();
+    uint32_t* stage = b_stage.as<uint32_t>();
+    size_t tmp_bytes = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, b_cnt.as<uint32_t>(), seg0, n_seg, s);
+    if ((e = b_tmp.alloc(tmp_bytes)) != cudaSuccess) return fail("alloc scan temp");
+    if ((e = cub::DeviceScan::ExclusiveSum(b_tmp.p, tmp_bytes, b_cnt.as<uint32_t>(), seg0, n_seg, s)) != cudaSuccess)
+        return fail("bucket scan");
+    if (nnz) {
+        build_scatter_kernel<<<grid, bt, 0, s>>>(d_indptr, d_docids, d_impacts, nnz, n_terms, tile_docs, seg0, stage);
+        count_launch();
+    }
+    // 3. final layout: slots per bucket (large buckets are padded to whole conflict-free groups), scan, write
+    const size_t n_buckets = n_seg - 1;
+    const int lgrid = (int)std::min<size_t>((n_buckets + kBuildWarps - 1) / kBuildWarps, 148 * 16);
+    uint32_t* slots = b_cnt.as<uint32_t>();          // reuse: counts are no longer needed
+    build_plan_kernel<<<lgrid, kBuildWarps * 32, 0, s>>>(seg0, stage, n_buckets, slots);
+    count_launch();
+    cudaMemsetAsync(slots + n_buckets, 0, 4, s);
+    if ((e = cub::DeviceScan::ExclusiveSum(b_tmp.p, tmp_bytes, slots, h->seg_ptr, n_seg, s)) != cudaSuccess)
+        return fail("slot scan");
+    // total slots in 64 bits: the u32 prefix sum above must not have wrapped
+    unsigned long long n_slots64 = 0;
+    cudaMemsetAsync(h->work, 0, 16, s);
+    sum_u32_kernel<<<148 * 4, 256, 0, s>>>(slots, n_buckets, (unsigned long long*)h->work);
+    count_launch();
+    if ((e = cudaMemcpyAsync(&n_slots64, h->work, 8, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail("read slots");
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail("plan kernel");
+    if (n_slots64 >= (1ull << 32)) {
+        set_error("msr_sparse_index_build: %llu posting slots after padding >= 2^32 (shard the collection)", n_slots64);
+        msr_sparse_index_destroy(h);
+        return MSR_ERR_INVALID;
+    }
+    h->n_slots = n_slots64;
+    if ((e = cudaMalloc(&h->postings, (h->n_slots ? h->n_slots : 1) * 4)) != cudaSuccess) return fail("alloc postings");
+    h->resident_bytes = n_seg * 4 + (h->n_slots ? h->n_slots : 1) * 4 + n_terms * 7ull + 20;
+    build_layout_kernel<<<lgrid, kBuildWarps * 32, 0, s>>>(seg0, stage, n_buckets, h->seg_ptr, h->postings);
+    count_launch();
+    build_term_meta_kernel<<<(n_terms + bt - 1) / bt, bt, 0, s>>>(d_indptr, d_df, b_max32.as<uint32_t>(), n_terms,
+                                                                  n_docs_global, h->term_keep, h->term_maximp, h->df_local);
+    count_launch();
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail("build kernels");
+    if ((e = cudaGetLastError()) != cudaSuccess) return fail("build kernels (launch)");
     e = cudaFuncSetAttribute(sparse_score_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)search_smem_bytes(kMaxTileDocs));
     if (e != cudaSuccess) return fail("opt-in shared memory");
@@ -636,7 +477,10 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     if (where == MSR_HOST) nnz_q = q_indptr[nq];
     size_t off_keys = 0;
     size_t off_cnt = align_up(off_keys + (size_t)qc * h->n_tiles * k_stride * 8, 256);
-    size_t off_end = align_up(off_cnt + (size_t)qc * h->n_tiles * 4, 256);
+    size_t off_ok = align_up(off_cnt + (size_t)qc * h->n_tiles * 4, 256);
+    size_t off_theta = align_up(off_ok + nq, 256);
+    size_t off_tlist = align_up(off_theta + (size_t)qc * 8, 256);
+    size_t off_end = align_up(off_tlist + (size_t)qc * k * 8, 256);
     size_t off_qi = off_end, off_qt = 0, off_qw = 0, off_os = 0, off_od = 0, off_oc = 0;
     if (where == MSR_HOST) {
         MSR_REQUIRE(nnz_q == 0 || (q_terms && q_weights), "msr_sparse_search: NULL query arrays");
@@ -665,12 +509,19 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
         d_os = (float*)(base + off_os); d_od = (int32_t*)(base + off_od); d_oc = (uint32_t*)(base + off_oc);
     }
 
+    uint8_t* d_ok = (uint8_t*)(base + off_ok);
+    query_prep_kernel<<<(nq + 7) / 8, 256, 0, s>>>(h->term_keep, h->term_maximp, h->n_terms, nq, d_qi, d_qt, d_qw, d_ok, h->status);
+    count_launch();
+    MSR_CUDA_CHECK(cudaGetLastError());
+
     SearchParams P;
     P.seg_ptr = h->seg_ptr; P.postings = h->postings; P.term_keep = h->term_keep; P.term_maximp = h->term_maximp;
     P.n_docs = h->n_docs; P.n_terms = h->n_terms; P.tile_docs = h->tile_docs; P.n_tiles = h->n_tiles;
-    P.doc_base = h->doc_base; P.q_indptr = d_qi; P.q_terms = d_qt; P.q_weights = d_qw;
+    P.doc_base = h->doc_base; P.q_indptr = d_qi; P.q_terms = d_qt; P.q_weights = d_qw; P.q_ok = d_ok;
     P.k = k; P.k_stride = k_stride;
-    P.cand_keys = (uint64_t*)(base + off_keys); P.cand_cnt = (uint32_t*)(base + off_cnt); P.status = h->status;
+    P.cand_keys = (uint64_t*)(base + off_keys); P.cand_cnt = (uint32_t*)(base + off_cnt);
+    P.theta = (unsigned long long*)(base + off_theta); P.tlist = (uint64_t*)(base + off_tlist);
+    P.use_theta = (h->n_tiles > 1 && h->use_theta) ? 1u : 0u;
     const size_t smem = search_smem_bytes(h->tile_docs);
     for (uint32_t q0 = 0; q0 < nq; q0 += qc) {
         const uint32_t n = std::min(qc, nq - q0);
@@ -684,6 +535,8 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
             h->ev_used += 3;
             MSR_CUDA_CHECK(cudaEventRecord(evs[0], s));
         }
+        if (P.use_theta)      // theta[] and tlist[] are contiguous up to alignment: one clear
+            MSR_CUDA_CHECK(cudaMemsetAsync(base + off_theta, 0, off_tlist - off_theta + (size_t)n * k * 8, s));
         sparse_score_topk_kernel<<<n * h->n_tiles, kThreads, smem, s>>>(P);
         count_launch();
         MSR_CUDA_CHECK(cudaGetLastError());

@@ -1,0 +1,452 @@
+// sparse_kernel.cuh -- device code of the sparse impact search (included by sparse.cu only).
+//
+//   query_prep_kernel         once per query batch: S5 term filter, S6 per-term rounding flag, exact-range check.
+//   sparse_score_topk_kernel  one CTA per (query, doc tile): stream the query's posting buckets of the tile,
+//                             accumulate integer impacts in shared memory, select the tile's candidates.
+//
+// Candidate selection uses a per-query THRESHOLD shared between the tiles of a query through global memory:
+//   theta[q]    64-bit ranking key; invariant: at least k distinct docs of the shard have key >= theta[q].
+//   tlist[q][k] keys of k such docs (any mix of real doc keys; readers de-duplicate).
+// The first tile of a query (grid order is tile-major, so it finishes long before the others start) radix-selects
+// its exact top-k and publishes it.  Every later tile emits only the docs whose key reaches theta -- one pass over
+// the accumulators -- then merges them with tlist, re-publishes the best k and raises theta (atomicMax).  Any doc of
+// the final top-k has key >= the true k-th key >= theta, so it is always emitted: the result is exact and
+// independent of timing; only the amount of surplus candidates varies.  A tile that finds no theta yet, or more
+// candidates than its output slots, falls back to the exact radix select.  8-byte stores are single transactions,
+// so a reader racing a writer sees old or new keys, each a real doc: no locks, nothing waits on another CTA.
+#pragma once
+#include "common.cuh"
+
+namespace msr {
+
+constexpr int kThreads = 512;
+constexpr int kWarps = kThreads / 32;
+constexpr int kSegMax = 256;      // query terms staged per pass
+constexpr int kUnroll = 8;        // loads in flight per lane
+constexpr int kChunk = 32 * kUnroll;
+constexpr int kBins = 2048;
+constexpr int kBinBits = 11;
+constexpr int kCandMax = 1024;
+constexpr int kUnionMax = 2048;   // keys the threshold merge can sort (own candidates + k)
+
+struct SearchParams {
+    const uint32_t* seg_ptr;
+    const uint32_t* postings;
+    uint32_t n_docs, n_terms, tile_docs, n_tiles;
+    int32_t doc_base;
+    const uint64_t* q_indptr;
+    const uint32_t* q_terms;
+    const uint32_t* q_weights;
+    const uint8_t* term_keep;
+    const uint16_t* term_maximp;
+    const uint8_t* q_ok;          // [nq_total] 1 = inside the exact-arithmetic range
+    uint32_t q_lo, nq, k, k_stride;
+    uint64_t* cand_keys;          // [nq][n_tiles][k_stride]
+    uint32_t* cand_cnt;           // [nq][n_tiles]
+    unsigned long long* theta;    // [nq]
+    uint64_t* tlist;              // [nq][k]
+    uint32_t use_theta;
+};
+
+// One warp per query: exact-arithmetic range check over the kept terms (see msr.h), done once instead of per tile.
+__global__ void query_prep_kernel(const uint8_t* __restrict__ keep, const uint16_t* __restrict__ maximp, uint32_t n_terms,
+                                  uint32_t nq, const uint64_t* __restrict__ q_indptr, const uint32_t* __restrict__ q_terms,
+                                  const uint32_t* __restrict__ q_weights, uint8_t* __restrict__ q_ok,
+                                  uint32_t* __restrict__ status) {
+    const uint32_t q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (q >= nq) return;
+    const uint64_t qs = q_indptr[q], qe = q_indptr[q + 1];
+    unsigned long long bound = 0;
+    uint32_t wmax = 0;
+    for (uint64_t j = qs + lane; j < qe; j += 32) {
+        const uint32_t t = q_terms[j];
+        const uint32_t w = q_weights[j];
+        if (t < n_terms && w && keep[t]) {
+            bound += (unsigned long long)w * maximp[t];
+            wmax = max(wmax, w);
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) {
+        bound += __shfl_xor_sync(0xffffffffu, bound, o);
+        wmax = max(wmax, __shfl_xor_sync(0xffffffffu, wmax, o));
+    }
+    if (lane == 0) {
+        const bool ok = bound < (1ull << 31) && wmax <= 65535u;
+        q_ok[q] = ok ? 1 : 0;
+        if (!ok) atomicOr(status, 1u);
+    }
+}
+
+__device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t* p) {
+    uint32_t v;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ void red_shared_add(uint32_t saddr, uint32_t val) {
+    asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(saddr), "r"(val) : "memory");
+}
+
+struct SegStage {                      // streaming phase view of the union region
+    uint32_t start[kSegMax];
+    uint32_t len[kSegMax];
+    uint32_t w[kSegMax];
+    uint32_t pref[kSegMax + 1];        // exclusive prefix of chunk counts
+};
+struct SelStage {                      // radix-select view
+    uint32_t hist[kBins];
+    uint64_t cand[kCandMax];
+};
+union StageUnion {
+    SegStage seg;
+    SelStage sel;
+    uint64_t keys[kUnionMax];          // threshold-merge view
+};
+struct SmallState {
+    uint32_t vmax, hits, out_cnt, cand_cnt, sel_b, sel_clt, sel_bcount, pad;
+    uint32_t wsum[kWarps];
+};
+
+// exclusive scan of one value per thread over the CTA (kThreads threads); returns exclusive prefix, *total = sum
+__device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* wsum, uint32_t* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    uint32_t inc = warp_incl_scan(v, lane);
+    __syncthreads();                       // wsum may still be read from a previous call
+    if (lane == 31) wsum[warp] = inc;
+    __syncthreads();
+    uint32_t base = 0, tot = 0;
+#pragma unroll
+    for (int w = 0; w < kWarps; ++w) {
+        uint32_t x = wsum[w];
+        if (w < warp) base += x;
+        tot += x;
+    }
+    *total = tot;
+    return base + inc - v;
+}
+
+// one chunk of <= kChunk posting slots of one bucket, lane-predicated (bucket tails, small buckets, S6 terms)
+__device__ __forceinline__ void score_chunk_generic(const uint32_t* src, uint32_t n, uint32_t wraw, uint32_t lane,
+                                                    uint32_t acc_s) {
+    const uint32_t w = wraw & 0x7FFFFFFFu;
+    uint32_t v[kUnroll];
+#pragma unroll
+    for (int u = 0; u < kUnroll; ++u) v[u] = (u * 32 + lane < n) ? ld_stream_u32(src + u * 32) : 0u;
+    if (!(wraw >> 31)) {
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+            if (u * 32 + lane < n) red_shared_add(acc_s + (v[u] & 0xFFFFu) * 4u, (v[u] >> 16) * w);
+    } else {                                                    // S6: float32(boost*freq) per term
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+            if (u * 32 + lane < n) red_shared_add(acc_s + (v[u] & 0xFFFFu) * 4u, (uint32_t)__uint2float_rn((v[u] >> 16) * w));
+    }
+}
+
+__global__ void __launch_bounds__(kThreads, 2)
+sparse_score_topk_kernel(const SearchParams P) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    StageUnion* U = reinterpret_cast<StageUnion*>(smem_raw);
+    SmallState* S = reinterpret_cast<SmallState*>(smem_raw + sizeof(StageUnion));
+    uint32_t* acc = reinterpret_cast<uint32_t*>(smem_raw + sizeof(StageUnion) + sizeof(SmallState));
+    const uint32_t acc_s = (uint32_t)__cvta_generic_to_shared(acc);
+
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t q = blockIdx.x % P.nq;
+    const uint32_t tile = blockIdx.x / P.nq;
+    const uint32_t tile_lo = tile * P.tile_docs;
+    const uint32_t tl = min(P.tile_docs, P.n_docs - tile_lo);
+    const uint64_t qs = P.q_indptr[P.q_lo + q], qe = P.q_indptr[P.q_lo + q + 1];
+    const uint32_t* seg_row = P.seg_ptr + (size_t)tile * P.n_terms;
+    uint64_t* keys_out = P.cand_keys + ((size_t)q * P.n_tiles + tile) * P.k_stride;
+    uint32_t* cnt_out = P.cand_cnt + (size_t)q * P.n_tiles + tile;
+
+    if (!P.q_ok[P.q_lo + q]) {                                  // outside the exact range: empty row (see msr.h)
+        if (tid == 0) *cnt_out = 0;
+        return;
+    }
+    for (uint32_t i = tid; i < tl; i += kThreads) acc[i] = 0;
+    if (tid == 0) { S->vmax = 0; S->hits = 0; S->out_cnt = 0; S->cand_cnt = 0; }
+
+    // ---- phase 1: stream the query's buckets of this tile, accumulate integer impacts ----
+    for (uint64_t batch = qs; batch < qe; batch += kSegMax) {
+        __syncthreads();   // previous batch fully consumed (first pass: accumulators zeroed)
+        uint32_t nchunks = 0;
+        if (tid < kSegMax) {
+            uint32_t len = 0, start = 0, w = 0;
+            const uint64_t j = batch + tid;
+            if (j < qe) {
+                const uint32_t t = P.q_terms[j];
+                w = P.q_weights[j];
+                if (t < P.n_terms && w && P.term_keep[t]) {
+                    start = seg_row[t];
+                    len = seg_row[t + 1] - start;
+                    // S6: float32(boost*freq) rounds once a product can reach 2^24 -> flag the term (bit 31)
+                    if ((uint64_t)w * P.term_maximp[t] >= (1u << 24)) w |= 0x80000000u;
+                } else {
+                    w = 0;
+                }
+            }
+            U->seg.start[tid] = start;
+            U->seg.len[tid] = len;
+            U->seg.w[tid] = w;
+            nchunks = (len + kChunk - 1) / kChunk;
+        }
+        uint32_t total;
+        const uint32_t ex = block_excl_scan(nchunks, S->wsum, &total);
+        if (tid < kSegMax) U->seg.pref[tid] = ex;
+        if (tid == 0) U->seg.pref[kSegMax] = total;
+        __syncthreads();
+
+        // each warp takes a contiguous range of chunk numbers, so it mostly walks inside one bucket
+        uint32_t g = (uint32_t)(((uint64_t)total * warp) / kWarps);
+        const uint32_t g1 = (uint32_t)(((uint64_t)total * (warp + 1)) / kWarps);
+        if (g >= g1) continue;
+        uint32_t seg;
+        {                                                       // last seg with pref[seg] <= g
+            uint32_t lo = 0, hi = kSegMax;
+            while (hi - lo > 1) {
+                const uint32_t mid = (lo + hi) >> 1;
+                if (U->seg.pref[mid] <= g) lo = mid; else hi = mid;
+            }
+            seg = lo;
+        }
+        while (g < g1) {
+            const uint32_t sb = U->seg.pref[seg], se = U->seg.pref[seg + 1];
+            if (se <= g) { ++seg; continue; }                   // empty buckets
+            const uint32_t len = U->seg.len[seg], wraw = U->seg.w[seg];
+            const uint32_t c0 = g - sb, c1 = min(se, g1) - sb;  // chunks [c0,c1) of this bucket are ours
+            const uint32_t* src = P.postings + U->seg.start[seg] + (size_t)c0 * kChunk + lane;
+            uint32_t left = len - c0 * kChunk;                  // slots from chunk c0 to the bucket's end
+            uint32_t nc = c1 - c0;
+            g = sb + c1;
+            ++seg;
+            if (!(wraw >> 31)) {
+                const uint32_t w = wraw;
+                uint32_t nfull = min(nc, left / kChunk);
+                if (nfull) {
+                    uint32_t v[kUnroll];
+#pragma unroll
+                    for (int u = 0; u < kUnroll; ++u) v[u] = ld_stream_u32(src + u * 32);
+                    for (uint32_t c = 1; c < nfull; ++c) {      // software pipeline: next chunk's loads in flight
+                        uint32_t nx[kUnroll];
+                        src += kChunk;
+#pragma unroll
+                        for (int u = 0; u < kUnroll; ++u) nx[u] = ld_stream_u32(src + u * 32);
+#pragma unroll
+                        for (int u = 0; u < kUnroll; ++u) red_shared_add(acc_s + (v[u] & 0xFFFFu) * 4u, (v[u] >> 16) * w);
+#pragma unroll
+                        for (int u = 0; u < kUnroll; ++u) v[u] = nx[u];
+                    }
+#pragma unroll
+                    for (int u = 0; u < kUnroll; ++u) red_shared_add(acc_s + (v[u] & 0xFFFFu) * 4u, (v[u] >> 16) * w);
+                    src += kChunk;
+                    left -= nfull * kChunk;
+                    nc -= nfull;
+                }
+            }
+            for (; nc; --nc) {
+                const uint32_t n = min((uint32_t)kChunk, left);
+                score_chunk_generic(src, n, wraw, lane, acc_s);
+                src += kChunk;
+                left -= n;
+            }
+        }
+    }
+    __syncthreads();
+
+    // ---- phase 2: candidates of the tile by (float32(score) desc, doc asc) ----
+    const uint32_t kq = min(P.k, tl);
+    const uint32_t gdoc0 = (uint32_t)P.doc_base + tile_lo;
+    unsigned long long* theta_p = P.theta + q;
+    uint64_t* tlist = P.tlist + (size_t)q * P.k;
+
+    // 2a. threshold mode: one pass, emit the docs whose key reaches theta
+    const unsigned long long theta = P.use_theta ? *(volatile unsigned long long*)theta_p : 0ull;
+    if (theta) {
+        const float tf = key_score(theta);                      // an integer-valued float32 in (0, 2^31)
+        uint32_t amin = (uint32_t)tf;                           // smallest integer score whose float32 image is >= tf
+        while (amin > 1 && __uint2float_rn(amin - 1) >= tf) --amin;
+        const uint32_t cap = min(P.k_stride, (uint32_t)kUnionMax);
+        for (uint32_t i = tid; i < tl; i += kThreads) {
+            const uint32_t a = acc[i];
+            if (a >= amin) {
+                const uint64_t key = make_key(__uint2float_rn(a), gdoc0 + i);
+                if (key >= theta) {
+                    const uint32_t pos = atomicAdd(&S->cand_cnt, 1u);
+                    if (pos < cap) U->keys[pos] = key;
+                }
+            }
+        }
+        __syncthreads();
+        const uint32_t c = S->cand_cnt;
+        if (c <= cap) {
+            for (uint32_t i = tid; i < c; i += kThreads) keys_out[i] = U->keys[i];
+            if (tid == 0) *cnt_out = c;
+            if (c == 0 || c + P.k > (uint32_t)kUnionMax) return;
+            // merge with the published list: best k distinct keys of (own candidates U tlist) -> new list, new theta
+            for (uint32_t r = tid; r < P.k; r += kThreads) U->keys[c + r] = ((volatile const uint64_t*)tlist)[r];
+            const uint32_t n = c + P.k;
+            uint32_t n2 = 2;
+            while (n2 < n) n2 <<= 1;
+            for (uint32_t i = n + tid; i < n2; i += kThreads) U->keys[i] = 0;
+            bitonic_sort_desc(U->keys, n2);
+            uint64_t e[4];
+            uint32_t f[4], ls = 0;
+            uint64_t prev = (tid > 0 && 4 * tid - 1 < n2) ? U->keys[4 * tid - 1] : ~0ull;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const uint32_t idx = 4 * tid + j;
+                e[j] = idx < n2 ? U->keys[idx] : 0ull;
+                f[j] = (e[j] != 0ull && e[j] != prev) ? 1u : 0u;
+                prev = e[j];
+                ls += f[j];
+            }
+            uint32_t total;
+            uint32_t ex = block_excl_scan(ls, S->wsum, &total);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (f[j]) {
+                    if (ex < P.k) {
+                        tlist[ex] = e[j];
+                        if (ex == P.k - 1) atomicMax(theta_p, (unsigned long long)e[j]);
+                    }
+                    ++ex;
+                }
+            }
+            return;
+        }
+        __syncthreads();                                        // more candidates than slots: exact select below
+        if (tid == 0) S->cand_cnt = 0;
+    }
+
+    // 2b. exact radix select of the tile's top-k
+    {
+        uint32_t m = 0, h = 0;
+        for (uint32_t i = tid; i < tl; i += kThreads) {
+            uint32_t a = acc[i];
+            m = max(m, a);
+            h += (a != 0);
+        }
+        m = warp_reduce_max(m);
+        h = warp_reduce_add(h);
+        if (lane == 0) {
+            if (m) atomicMax(&S->vmax, m);
+            if (h) atomicAdd(&S->hits, h);
+        }
+    }
+    __syncthreads();
+    const uint32_t vmax = S->vmax, hits = S->hits;
+    if (hits == 0) {
+        if (tid == 0) *cnt_out = 0;
+        return;
+    }
+    if (hits <= kq) {                                           // S7: fewer hits than k -> all of them
+        for (uint32_t i = tid; i < tl; i += kThreads) {
+            uint32_t a = acc[i];
+            if (a) keys_out[atomicAdd(&S->out_cnt, 1u)] = make_key(__uint2float_rn(a), gdoc0 + i);
+        }
+        if (tid == 0) *cnt_out = hits;
+        return;
+    }
+    // selection key: integers below 2^24 are their own float32 image; above, rank by the rounded float (S6)
+    const bool use_f = vmax >= (1u << 24);
+#define MSR_SELKEY(a) (use_f ? __float_as_uint(__uint2float_rn(a)) : (a))
+    const uint32_t kmax = MSR_SELKEY(vmax);
+    uint32_t remaining = kq, sh_prev = 32 - __clz(kmax), pref = 0, s = 0, cand_count = 0;
+    for (;;) {
+        s = sh_prev > kBinBits ? sh_prev - kBinBits : 0;
+        const uint32_t width = sh_prev - s;
+        for (uint32_t i = tid; i < kBins; i += kThreads) U->sel.hist[i] = 0;
+        __syncthreads();
+        for (uint32_t i = tid; i < tl; i += kThreads) {
+            uint32_t a = acc[i];
+            if (a) {
+                uint32_t d = kmax - MSR_SELKEY(a);
+                uint32_t hi = sh_prev >= 32 ? 0u : (d >> sh_prev);
+                if (hi == pref) atomicAdd(&U->sel.hist[(d >> s) & ((1u << width) - 1u)], 1u);
+            }
+        }
+        __syncthreads();
+        {
+            uint32_t h4[4], ls = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { h4[j] = U->sel.hist[tid * 4 + j]; ls += h4[j]; }
+            uint32_t total;
+            uint32_t ex = block_excl_scan(ls, S->wsum, &total);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (ex < remaining && ex + h4[j] >= remaining) {
+                    S->sel_b = tid * 4 + j; S->sel_clt = ex; S->sel_bcount = h4[j];
+                }
+                ex += h4[j];
+            }
+        }
+        __syncthreads();
+        remaining -= S->sel_clt;
+        pref = (width >= 32 ? 0u : (pref << width)) | S->sel_b;
+        sh_prev = s;
+        cand_count = S->sel_bcount;
+        if (cand_count <= (uint32_t)kCandMax || s == 0) break;
+    }
+    const uint32_t n_def = kq - remaining;                      // docs strictly better than the candidate bin
+    const bool collect = cand_count <= (uint32_t)kCandMax;
+    for (uint32_t i = tid; i < tl; i += kThreads) {
+        uint32_t a = acc[i];
+        if (a) {
+            uint32_t d = kmax - MSR_SELKEY(a);
+            uint32_t x = d >> s;
+            if (x < pref) {
+                keys_out[atomicAdd(&S->out_cnt, 1u)] = make_key(__uint2float_rn(a), gdoc0 + i);
+            } else if (x == pref && collect) {
+                // descending sort of ~((d<<32)|i)  ==  ascending (d, i)  ==  best first
+                U->sel.cand[atomicAdd(&S->cand_cnt, 1u)] = ~(((uint64_t)d << 32) | i);
+            }
+        }
+    }
+    __syncthreads();
+    if (collect) {
+        uint32_t n2 = 2;
+        while (n2 < cand_count) n2 <<= 1;
+        for (uint32_t i = cand_count + tid; i < n2; i += kThreads) U->sel.cand[i] = 0;
+        bitonic_sort_desc(U->sel.cand, n2);
+        for (uint32_t r = tid; r < remaining; r += kThreads) {
+            uint32_t i = (uint32_t)(~U->sel.cand[r]);
+            keys_out[n_def + r] = make_key(__uint2float_rn(acc[i]), gdoc0 + i);
+        }
+    } else {
+        // more than kCandMax docs tie exactly at the threshold key: take the `remaining` smallest doc ids (S8)
+        const uint32_t per = ((tl + kWarps - 1) / kWarps + 31) & ~31u;
+        const uint32_t lo = warp * per, hi = min(tl, lo + per);
+        uint32_t c = 0;
+        for (uint32_t base = lo; base < hi; base += 32) {
+            uint32_t i = base + lane;
+            uint32_t a = i < hi ? acc[i] : 0;
+            bool f = a && (kmax - MSR_SELKEY(a)) == pref;
+            c += __popc(__ballot_sync(0xffffffffu, f));
+        }
+        __syncthreads();
+        if (lane == 0) S->wsum[warp] = c;
+        __syncthreads();
+        uint32_t run = 0;
+        for (uint32_t w2 = 0; w2 < warp; ++w2) run += S->wsum[w2];
+        for (uint32_t base = lo; base < hi; base += 32) {
+            uint32_t i = base + lane;
+            uint32_t a = i < hi ? acc[i] : 0;
+            bool f = a && (kmax - MSR_SELKEY(a)) == pref;
+            uint32_t b = __ballot_sync(0xffffffffu, f);
+            uint32_t r = run + __popc(b & ((1u << lane) - 1u));
+            if (f && r < remaining) keys_out[n_def + r] = make_key(__uint2float_rn(a), gdoc0 + i);
+            run += __popc(b);
+        }
+    }
+#undef MSR_SELKEY
+    if (tid == 0) *cnt_out = kq;
+    // publish this tile's exact top-k as the query's threshold list (keys_out[k-1] is its smallest key)
+    if (P.use_theta && kq == P.k) {
+        __syncthreads();
+        for (uint32_t r = tid; r < P.k; r += kThreads) tlist[r] = keys_out[r];
+        if (tid == 0) atomicMax(theta_p, (unsigned long long)keys_out[P.k - 1]);
+    }
+}
+
+}  // namespace msr
