@@ -27,6 +27,7 @@
 // (topk.cu) produces the final sorted list.
 #include <cub/device/device_scan.cuh>
 
+#include <math.h>
 #include <stdlib.h>
 
 #include <vector>
@@ -39,6 +40,7 @@ namespace msr {
 constexpr uint32_t kDefaultTileDocs = 24576;   // 96 KB of accumulators -> 2 CTAs per SM
 constexpr uint32_t kMaxTileDocs = 53248;       // 208 KB of accumulators + staging = the 227 KB opt-in limit
 constexpr uint32_t kSmallBucket = 96;          // buckets above this size get the bank-conflict-free layout
+constexpr float kDenseFraction = 0.25f;        // terms present in >= this fraction of the shard's docs are stored as rows
 constexpr int kBuildWarps = 8;                 // warps per CTA of the bucket layout kernels
 
 int topk_merge_keys_launch(uint32_t nq, uint32_t n_lists, uint32_t stride, const uint64_t* keys,
@@ -55,7 +57,11 @@ struct msr_sparse_index {
     uint32_t* seg_ptr = nullptr;      // [n_tiles*n_terms + 1]
     uint32_t* postings = nullptr;     // [n_slots]
     uint8_t* term_keep = nullptr;     // [n_terms]
-    uint16_t* term_maximp = nullptr;  // [n_terms]
+    uint32_t* term_maximp = nullptr;  // [n_terms]
+    uint32_t* dense_id = nullptr;     // [n_terms] row of a dense term in dense_rows, kNotDense otherwise
+    uint16_t* dense_rows = nullptr;   // [n_dense][dense_stride] impact of the term in every doc of the shard (0 = absent)
+    uint32_t n_dense = 0;
+    size_t dense_stride = 0;
     uint32_t* df_local = nullptr;     // [n_terms]
     uint32_t* status = nullptr;       // sticky device status word
     uint64_t* work = nullptr;         // [2] scratch for msr_sparse_query_work
@@ -83,27 +89,33 @@ __device__ __forceinline__ uint32_t term_of_posting(const uint64_t* __restrict__
     return lo;
 }
 
+// Validates the CSR, records max impact per term, writes the postings of DENSE terms into their impact rows and
+// counts the postings of the other terms per (tile, term) bucket.
 __global__ void build_count_kernel(const uint64_t* __restrict__ indptr, const uint32_t* __restrict__ docids,
                                    const uint16_t* __restrict__ impacts, uint64_t nnz, uint32_t n_terms,
-                                   uint32_t n_docs, uint32_t tile_docs, uint32_t* __restrict__ cnt,
-                                   uint32_t* __restrict__ maximp32, uint32_t* __restrict__ bad) {
+                                   uint32_t n_docs, uint32_t tile_docs, const uint32_t* __restrict__ dense_id,
+                                   uint16_t* __restrict__ dense_rows, size_t dense_stride, uint32_t* __restrict__ cnt,
+                                   uint32_t* __restrict__ maximp, uint32_t* __restrict__ bad) {
     for (uint64_t p = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; p < nnz; p += (uint64_t)gridDim.x * blockDim.x) {
         uint32_t t = term_of_posting(indptr, n_terms, p);
         uint32_t d = docids[p];
         uint32_t imp = impacts[p];
         if (d >= n_docs || imp == 0) { atomicOr(bad, 1u); continue; }
         if (p > indptr[t] && docids[p - 1] >= d) atomicOr(bad, 2u);
-        atomicAdd(&cnt[(size_t)(d / tile_docs) * n_terms + t], 1u);
-        atomicMax(&maximp32[t], imp);
+        const uint32_t di = dense_id[t];
+        if (di != kNotDense) dense_rows[(size_t)di * dense_stride + d] = (uint16_t)imp;
+        else atomicAdd(&cnt[(size_t)(d / tile_docs) * n_terms + t], 1u);
+        atomicMax(&maximp[t], imp);
     }
 }
 
 __global__ void build_scatter_kernel(const uint64_t* __restrict__ indptr, const uint32_t* __restrict__ docids,
                                      const uint16_t* __restrict__ impacts, uint64_t nnz, uint32_t n_terms,
-                                     uint32_t tile_docs, const uint32_t* __restrict__ seg_ptr,
-                                     uint32_t* __restrict__ postings) {
+                                     uint32_t tile_docs, const uint32_t* __restrict__ dense_id,
+                                     const uint32_t* __restrict__ seg_ptr, uint32_t* __restrict__ postings) {
     for (uint64_t p = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; p < nnz; p += (uint64_t)gridDim.x * blockDim.x) {
         uint32_t t = term_of_posting(indptr, n_terms, p);
+        if (dense_id[t] != kNotDense) continue;
         uint32_t d = docids[p];
         uint32_t tile = d / tile_docs;
         uint32_t tile_lo = tile * tile_docs;
@@ -204,17 +216,26 @@ build_layout_kernel(const uint32_t* __restrict__ seg0, const uint32_t* __restric
     }
 }
 
+// keep (rule S5), local df and the dense flag of every term (dense: df_local >= dense_min postings in this shard)
 __global__ void build_term_meta_kernel(const uint64_t* __restrict__ indptr, const uint32_t* __restrict__ df_global,
-                                       const uint32_t* __restrict__ maximp32, uint32_t n_terms, uint32_t n_docs_global,
-                                       uint8_t* __restrict__ keep, uint16_t* __restrict__ maximp, uint32_t* __restrict__ df_local) {
+                                       uint32_t n_terms, uint32_t n_docs_global, uint32_t dense_min,
+                                       uint8_t* __restrict__ keep, uint32_t* __restrict__ df_local,
+                                       uint32_t* __restrict__ dense_flag) {
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    if (t >= n_terms) return;
+    if (t > n_terms) return;
+    if (t == n_terms) { dense_flag[t] = 0; return; }              // sentinel slot of the scan
     uint32_t dfl = (uint32_t)(indptr[t + 1] - indptr[t]);
     uint64_t df = df_global ? df_global[t] : dfl;
     // S5: in the dictionary and ln(N/(df+1)) > 0  <=>  0 < df and df + 1 < N
     keep[t] = (df > 0 && df + 1 < (uint64_t)n_docs_global) ? 1 : 0;
-    maximp[t] = (uint16_t)maximp32[t];
     df_local[t] = dfl;
+    dense_flag[t] = dfl >= dense_min ? 1u : 0u;
+}
+
+// dense_id[t] = row number of a dense term (exclusive scan of the flags), kNotDense otherwise
+__global__ void build_dense_id_kernel(const uint32_t* __restrict__ dense_flag, uint32_t n_terms, uint32_t* __restrict__ dense_id) {
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < n_terms) dense_id[t] = dense_flag[t] ? dense_id[t] : kNotDense;
 }
 
 __global__ void query_work_kernel(const uint8_t* __restrict__ keep, const uint32_t* __restrict__ df_local,
@@ -233,7 +254,7 @@ __global__ void query_work_kernel(const uint8_t* __restrict__ keep, const uint32
 }
 
 static size_t search_smem_bytes(uint32_t tile_docs) {
-    return sizeof(StageUnion) + sizeof(SmallState) + (size_t)tile_docs * 4;
+    return sizeof(StageUnion) + sizeof(SmallState) + (size_t)((tile_docs + 7) & ~7u) * 4;
 }
 
 }  // namespace msr
@@ -304,7 +325,7 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
     h->n_docs_global = n_docs_global; h->doc_base = doc_base; h->nnz = nnz;
     { const char* e = getenv("MSR_SPARSE_NO_THETA"); h->use_theta = !(e && e[0] == '1'); }
     const size_t n_seg = (size_t)n_tiles * n_terms + 1;
-    DevBuf b_cnt, b_max32, b_bad, b_tmp;
+    DevBuf b_cnt, b_bad, b_tmp;
     cudaError_t e = cudaSuccess;
     auto fail = [&](const char* what) {
         set_error("msr_sparse_index_build: %s: %s", what, cudaGetErrorString(e));
@@ -313,27 +334,54 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
     };
     if ((e = cudaMalloc(&h->seg_ptr, n_seg * 4)) != cudaSuccess) return fail("alloc seg_ptr");
     if ((e = cudaMalloc(&h->term_keep, n_terms)) != cudaSuccess) return fail("alloc term_keep");
-    if ((e = cudaMalloc(&h->term_maximp, (size_t)n_terms * 2)) != cudaSuccess) return fail("alloc term_maximp");
+    if ((e = cudaMalloc(&h->term_maximp, (size_t)n_terms * 4)) != cudaSuccess) return fail("alloc term_maximp");
     if ((e = cudaMalloc(&h->df_local, (size_t)n_terms * 4)) != cudaSuccess) return fail("alloc df_local");
+    if ((e = cudaMalloc(&h->dense_id, (size_t)(n_terms + 1) * 4)) != cudaSuccess) return fail("alloc dense_id");
     if ((e = cudaMalloc(&h->status, 4)) != cudaSuccess) return fail("alloc status");
     if ((e = cudaMalloc(&h->work, 16)) != cudaSuccess) return fail("alloc work");
-    DevBuf b_seg0, b_stage;
+    DevBuf b_seg0, b_stage, b_flag;
     if ((e = b_cnt.alloc(n_seg * 4)) != cudaSuccess) return fail("alloc cnt");
     if ((e = b_seg0.alloc(n_seg * 4)) != cudaSuccess) return fail("alloc seg0");
-    if ((e = b_stage.alloc((nnz ? nnz : 1) * 4)) != cudaSuccess) return fail("alloc stage");
-    if ((e = b_max32.alloc((size_t)n_terms * 4)) != cudaSuccess) return fail("alloc maximp32");
+    if ((e = b_flag.alloc((size_t)(n_terms + 1) * 4)) != cudaSuccess) return fail("alloc dense flags");
     if ((e = b_bad.alloc(4)) != cudaSuccess) return fail("alloc bad");
     cudaMemsetAsync(b_cnt.p, 0, n_seg * 4, s);
-    cudaMemsetAsync(b_max32.p, 0, (size_t)n_terms * 4, s);
+    cudaMemsetAsync(h->term_maximp, 0, (size_t)n_terms * 4, s);
     cudaMemsetAsync(b_bad.p, 0, 4, s);
     cudaMemsetAsync(h->status, 0, 4, s);
 
-    // 1. validate + count postings per (tile, term) bucket
+    // 0. per-term metadata; terms present in >= kDenseFraction of the shard's docs become dense impact rows
     const int bt = 256;
+    size_t tmp_bytes = 0, tmp2 = 0;
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, b_cnt.as<uint32_t>(), b_seg0.as<uint32_t>(), n_seg, s);
+    cub::DeviceScan::ExclusiveSum(nullptr, tmp2, b_flag.as<uint32_t>(), h->dense_id, n_terms + 1, s);
+    tmp_bytes = std::max(tmp_bytes, tmp2);
+    if ((e = b_tmp.alloc(tmp_bytes)) != cudaSuccess) return fail("alloc scan temp");
+    uint32_t dense_min = 0xFFFFFFFFu;                               // dense rows need 16-byte aligned tile starts
+    { const char* ev = getenv("MSR_SPARSE_NO_DENSE");
+      if (tile_docs % 8 == 0 && !(ev && ev[0] == '1'))
+          dense_min = std::max<uint32_t>(32u, (uint32_t)std::ceil((double)kDenseFraction * n_docs)); }
+    build_term_meta_kernel<<<(n_terms + 1 + bt - 1) / bt, bt, 0, s>>>(d_indptr, d_df, n_terms, n_docs_global, dense_min,
+                                                                      h->term_keep, h->df_local, b_flag.as<uint32_t>());
+    count_launch();
+    if ((e = cub::DeviceScan::ExclusiveSum(b_tmp.p, tmp_bytes, b_flag.as<uint32_t>(), h->dense_id, n_terms + 1, s)) != cudaSuccess)
+        return fail("dense scan");
+    if ((e = cudaMemcpyAsync(&h->n_dense, h->dense_id + n_terms, 4, cudaMemcpyDeviceToHost, s)) != cudaSuccess) return fail("read n_dense");
+    build_dense_id_kernel<<<(n_terms + bt - 1) / bt, bt, 0, s>>>(b_flag.as<uint32_t>(), n_terms, h->dense_id);
+    count_launch();
+    if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail("term metadata");
+    h->dense_stride = ((size_t)n_tiles * tile_docs + 7) / 8 * 8;
+    if (h->n_dense) {
+        if ((e = cudaMalloc(&h->dense_rows, (size_t)h->n_dense * h->dense_stride * 2)) != cudaSuccess) return fail("alloc dense rows");
+        cudaMemsetAsync(h->dense_rows, 0, (size_t)h->n_dense * h->dense_stride * 2, s);
+    }
+    if ((e = b_stage.alloc((nnz ? nnz : 1) * 4)) != cudaSuccess) return fail("alloc stage");
+
+    // 1. validate, fill the dense rows, count the other postings per (tile, term) bucket
     const int grid = (int)std::min<uint64_t>((nnz + bt - 1) / bt, 148ull * 32);
     if (nnz) {
-        build_count_kernel<<<grid, bt, 0, s>>>(d_indptr, d_docids, d_impacts, nnz, n_terms, n_docs, tile_docs,
-                                               b_cnt.as<uint32_t>(), b_max32.as<uint32_t>(), b_bad.as<uint32_t>());
+        build_count_kernel<<<grid, bt, 0, s>>>(d_indptr, d_docids, d_impacts, nnz, n_terms, n_docs, tile_docs, h->dense_id,
+                                               h->dense_rows, h->dense_stride, b_cnt.as<uint32_t>(), h->term_maximp,
+                                               b_bad.as<uint32_t>());
         count_launch();
     }
     uint32_t bad = 0;
@@ -348,13 +396,10 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
     // 2. bucket the postings in doc order into a staging array
     uint32_t* seg0 = b_seg0.as<uint32_t>();
     uint32_t* stage = b_stage.as<uint32_t>();
-    size_t tmp_bytes = 0;
-    cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, b_cnt.as<uint32_t>(), seg0, n_seg, s);
-    if ((e = b_tmp.alloc(tmp_bytes)) != cudaSuccess) return fail("alloc scan temp");
     if ((e = cub::DeviceScan::ExclusiveSum(b_tmp.p, tmp_bytes, b_cnt.as<uint32_t>(), seg0, n_seg, s)) != cudaSuccess)
         return fail("bucket scan");
     if (nnz) {
-        build_scatter_kernel<<<grid, bt, 0, s>>>(d_indptr, d_docids, d_impacts, nnz, n_terms, tile_docs, seg0, stage);
+        build_scatter_kernel<<<grid, bt, 0, s>>>(d_indptr, d_docids, d_impacts, nnz, n_terms, tile_docs, h->dense_id, seg0, stage);
         count_launch();
     }
     // 3. final layout: slots per bucket (large buckets are padded to whole conflict-free groups), scan, write
@@ -380,11 +425,9 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
     }
     h->n_slots = n_slots64;
     if ((e = cudaMalloc(&h->postings, (h->n_slots ? h->n_slots : 1) * 4)) != cudaSuccess) return fail("alloc postings");
-    h->resident_bytes = n_seg * 4 + (h->n_slots ? h->n_slots : 1) * 4 + n_terms * 7ull + 20;
+    h->resident_bytes = n_seg * 4 + (h->n_slots ? h->n_slots : 1) * 4 + n_terms * 13ull + 20 +
+                        (size_t)h->n_dense * h->dense_stride * 2;
     build_layout_kernel<<<lgrid, kBuildWarps * 32, 0, s>>>(seg0, stage, n_buckets, h->seg_ptr, h->postings);
-    count_launch();
-    build_term_meta_kernel<<<(n_terms + bt - 1) / bt, bt, 0, s>>>(d_indptr, d_df, b_max32.as<uint32_t>(), n_terms,
-                                                                  n_docs_global, h->term_keep, h->term_maximp, h->df_local);
     count_launch();
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail("build kernels");
     if ((e = cudaGetLastError()) != cudaSuccess) return fail("build kernels (launch)");
@@ -399,7 +442,7 @@ extern "C" int msr_sparse_index_destroy(msr_sparse_index* h) {
     if (!h) return MSR_OK;
     cudaSetDevice(h->device);
     cudaFree(h->seg_ptr); cudaFree(h->postings); cudaFree(h->term_keep); cudaFree(h->term_maximp);
-    cudaFree(h->df_local); cudaFree(h->status); cudaFree(h->work);
+    cudaFree(h->df_local); cudaFree(h->status); cudaFree(h->work); cudaFree(h->dense_id); cudaFree(h->dense_rows);
     h->ws.release();
     for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
     delete h;
@@ -518,6 +561,7 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     P.seg_ptr = h->seg_ptr; P.postings = h->postings; P.term_keep = h->term_keep; P.term_maximp = h->term_maximp;
     P.n_docs = h->n_docs; P.n_terms = h->n_terms; P.tile_docs = h->tile_docs; P.n_tiles = h->n_tiles;
     P.doc_base = h->doc_base; P.q_indptr = d_qi; P.q_terms = d_qt; P.q_weights = d_qw; P.q_ok = d_ok;
+    P.dense_id = h->dense_id; P.dense_rows = h->dense_rows; P.dense_stride = h->dense_stride;
     P.k = k; P.k_stride = k_stride;
     P.cand_keys = (uint64_t*)(base + off_keys); P.cand_cnt = (uint32_t*)(base + off_cnt);
     P.theta = (unsigned long long*)(base + off_theta); P.tlist = (uint64_t*)(base + off_tlist);

@@ -27,6 +27,7 @@ constexpr int kChunk = 32 * kUnroll;
 constexpr int kBins = 2048;
 constexpr int kBinBits = 11;
 constexpr int kCandMax = 1024;
+constexpr uint32_t kNotDense = 0xFFFFFFFFu;   // dense_id of a term that is stored as posting buckets
 constexpr int kUnionMax = 2048;   // keys the threshold merge can sort (own candidates + k)
 
 struct SearchParams {
@@ -38,7 +39,10 @@ struct SearchParams {
     const uint32_t* q_terms;
     const uint32_t* q_weights;
     const uint8_t* term_keep;
-    const uint16_t* term_maximp;
+    const uint32_t* term_maximp;
+    const uint32_t* dense_id;     // [n_terms]
+    const uint16_t* dense_rows;   // [n_dense][dense_stride]
+    size_t dense_stride;
     const uint8_t* q_ok;          // [nq_total] 1 = inside the exact-arithmetic range
     uint32_t q_lo, nq, k, k_stride;
     uint64_t* cand_keys;          // [nq][n_tiles][k_stride]
@@ -49,7 +53,7 @@ struct SearchParams {
 };
 
 // One warp per query: exact-arithmetic range check over the kept terms (see msr.h), done once instead of per tile.
-__global__ void query_prep_kernel(const uint8_t* __restrict__ keep, const uint16_t* __restrict__ maximp, uint32_t n_terms,
+__global__ void query_prep_kernel(const uint8_t* __restrict__ keep, const uint32_t* __restrict__ maximp, uint32_t n_terms,
                                   uint32_t nq, const uint64_t* __restrict__ q_indptr, const uint32_t* __restrict__ q_terms,
                                   const uint32_t* __restrict__ q_weights, uint8_t* __restrict__ q_ok,
                                   uint32_t* __restrict__ status) {
@@ -91,6 +95,8 @@ struct SegStage {                      // streaming phase view of the union regi
     uint32_t len[kSegMax];
     uint32_t w[kSegMax];
     uint32_t pref[kSegMax + 1];        // exclusive prefix of chunk counts
+    uint32_t drow[kSegMax];            // dense terms of the batch: row number, weight
+    uint32_t dw[kSegMax];
 };
 struct SelStage {                      // radix-select view
     uint32_t hist[kBins];
@@ -102,9 +108,16 @@ union StageUnion {
     uint64_t keys[kUnionMax];          // threshold-merge view
 };
 struct SmallState {
-    uint32_t vmax, hits, out_cnt, cand_cnt, sel_b, sel_clt, sel_bcount, pad;
+    uint32_t vmax, hits, out_cnt, cand_cnt, sel_b, sel_clt, sel_bcount, n_dense;
     uint32_t wsum[kWarps];
 };
+static_assert(sizeof(SmallState) % 16 == 0 && sizeof(StageUnion) % 16 == 0, "accumulators must stay 16-byte aligned");
+
+__device__ __forceinline__ uint4 ld_stream_v4(const void* p) {
+    uint4 v;
+    asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+    return v;
+}
 
 // exclusive scan of one value per thread over the CTA (kThreads threads); returns exclusive prefix, *total = sum
 __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* wsum, uint32_t* total) {
@@ -164,12 +177,16 @@ sparse_score_topk_kernel(const SearchParams P) {
         if (tid == 0) *cnt_out = 0;
         return;
     }
-    for (uint32_t i = tid; i < tl; i += kThreads) acc[i] = 0;
     if (tid == 0) { S->vmax = 0; S->hits = 0; S->out_cnt = 0; S->cand_cnt = 0; }
 
-    // ---- phase 1: stream the query's buckets of this tile, accumulate integer impacts ----
-    for (uint64_t batch = qs; batch < qe; batch += kSegMax) {
-        __syncthreads();   // previous batch fully consumed (first pass: accumulators zeroed)
+    // ---- phase 1: accumulate integer impacts of the tile's docs in shared memory ----
+    // Dense terms (impact rows) are added doc-parallel with plain stores -- the first batch thereby also zeroes the
+    // accumulators -- then the other terms' posting buckets are scattered with shared-memory atomics.
+    uint64_t batch = qs;
+    do {
+        __syncthreads();   // previous batch fully consumed
+        if (tid == 0) S->n_dense = 0;
+        __syncthreads();
         uint32_t nchunks = 0;
         if (tid < kSegMax) {
             uint32_t len = 0, start = 0, w = 0;
@@ -178,10 +195,17 @@ sparse_score_topk_kernel(const SearchParams P) {
                 const uint32_t t = P.q_terms[j];
                 w = P.q_weights[j];
                 if (t < P.n_terms && w && P.term_keep[t]) {
-                    start = seg_row[t];
-                    len = seg_row[t + 1] - start;
                     // S6: float32(boost*freq) rounds once a product can reach 2^24 -> flag the term (bit 31)
                     if ((uint64_t)w * P.term_maximp[t] >= (1u << 24)) w |= 0x80000000u;
+                    const uint32_t di = P.dense_id[t];
+                    if (di != kNotDense) {
+                        const uint32_t pos = atomicAdd(&S->n_dense, 1u);
+                        U->seg.drow[pos] = di;
+                        U->seg.dw[pos] = w;
+                    } else {
+                        start = seg_row[t];
+                        len = seg_row[t + 1] - start;
+                    }
                 } else {
                     w = 0;
                 }
@@ -190,6 +214,37 @@ sparse_score_topk_kernel(const SearchParams P) {
             U->seg.len[tid] = len;
             U->seg.w[tid] = w;
             nchunks = (len + kChunk - 1) / kChunk;
+        }
+        __syncthreads();
+        {
+            const uint32_t nd = S->n_dense;
+            const bool first = batch == qs;
+            if (first || nd) {
+                const uint32_t nslots = (tl + 7) >> 3;          // 8 docs per thread and step
+                for (uint32_t slot = tid; slot < nslots; slot += kThreads) {
+                    uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+                    uint4* ap = reinterpret_cast<uint4*>(acc + 8 * slot);
+                    if (!first) { a0 = ap[0]; a1 = ap[1]; }
+                    const uint16_t* col = P.dense_rows + tile_lo + 8 * slot;
+#pragma unroll 4
+                    for (uint32_t d = 0; d < nd; ++d) {
+                        const uint4 v = ld_stream_v4(col + (size_t)U->seg.drow[d] * P.dense_stride);
+                        const uint32_t wraw = U->seg.dw[d], w = wraw & 0x7FFFFFFFu;
+                        if (!(wraw >> 31)) {
+                            a0.x += (v.x & 0xFFFFu) * w; a0.y += (v.x >> 16) * w;
+                            a0.z += (v.y & 0xFFFFu) * w; a0.w += (v.y >> 16) * w;
+                            a1.x += (v.z & 0xFFFFu) * w; a1.y += (v.z >> 16) * w;
+                            a1.z += (v.w & 0xFFFFu) * w; a1.w += (v.w >> 16) * w;
+                        } else {
+                            a0.x += (uint32_t)__uint2float_rn((v.x & 0xFFFFu) * w); a0.y += (uint32_t)__uint2float_rn((v.x >> 16) * w);
+                            a0.z += (uint32_t)__uint2float_rn((v.y & 0xFFFFu) * w); a0.w += (uint32_t)__uint2float_rn((v.y >> 16) * w);
+                            a1.x += (uint32_t)__uint2float_rn((v.z & 0xFFFFu) * w); a1.y += (uint32_t)__uint2float_rn((v.z >> 16) * w);
+                            a1.z += (uint32_t)__uint2float_rn((v.w & 0xFFFFu) * w); a1.w += (uint32_t)__uint2float_rn((v.w >> 16) * w);
+                        }
+                    }
+                    ap[0] = a0; ap[1] = a1;
+                }
+            }
         }
         uint32_t total;
         const uint32_t ex = block_excl_scan(nchunks, S->wsum, &total);
@@ -200,7 +255,7 @@ sparse_score_topk_kernel(const SearchParams P) {
         // each warp takes a contiguous range of chunk numbers, so it mostly walks inside one bucket
         uint32_t g = (uint32_t)(((uint64_t)total * warp) / kWarps);
         const uint32_t g1 = (uint32_t)(((uint64_t)total * (warp + 1)) / kWarps);
-        if (g >= g1) continue;
+        if (g >= g1) continue;                                  // (the do-while condition is evaluated)
         uint32_t seg;
         {                                                       // last seg with pref[seg] <= g
             uint32_t lo = 0, hi = kSegMax;
@@ -251,7 +306,7 @@ sparse_score_topk_kernel(const SearchParams P) {
                 left -= n;
             }
         }
-    }
+    } while ((batch += kSegMax) < qe);
     __syncthreads();
 
     // ---- phase 2: candidates of the tile by (float32(score) desc, doc asc) ----
@@ -282,10 +337,33 @@ sparse_score_topk_kernel(const SearchParams P) {
         if (c <= cap) {
             for (uint32_t i = tid; i < c; i += kThreads) keys_out[i] = U->keys[i];
             if (tid == 0) *cnt_out = c;
-            if (c == 0 || c + P.k > (uint32_t)kUnionMax) return;
-            // merge with the published list: best k distinct keys of (own candidates U tlist) -> new list, new theta
+            // merge with the published list: best k distinct keys of (own candidates U tlist) -> new list, new theta.
+            // Skipped while the tile adds little (theta would hardly move) or the union does not fit.
+            if (c < max(1u, P.k >> 3) || c + P.k > (uint32_t)kUnionMax) return;
             for (uint32_t r = tid; r < P.k; r += kThreads) U->keys[c + r] = ((volatile const uint64_t*)tlist)[r];
             const uint32_t n = c + P.k;
+            if (n <= (uint32_t)kThreads) {
+                // rank by counting: one key per thread against all n (broadcast reads).  Own candidates and list
+                // entries come from different tiles, so equal keys only appear when two tiles of the query raced
+                // on the list; that case takes the sorting path below.
+                __syncthreads();
+                const uint64_t mine = tid < n ? U->keys[tid] : 0ull;
+                uint32_t gt = 0, dup = 0;
+                if (mine) {
+                    for (uint32_t j = 0; j < n; ++j) {
+                        const uint64_t kj = U->keys[j];
+                        gt += kj > mine;
+                        dup |= (kj == mine) & (j < tid);
+                    }
+                }
+                if (!__syncthreads_or((int)dup)) {
+                    if (mine && gt < P.k) {
+                        tlist[gt] = mine;
+                        if (gt == P.k - 1) atomicMax(theta_p, (unsigned long long)mine);
+                    }
+                    return;
+                }
+            }
             uint32_t n2 = 2;
             while (n2 < n) n2 <<= 1;
             for (uint32_t i = n + tid; i < n2; i += kThreads) U->keys[i] = 0;

@@ -170,3 +170,47 @@ def test_synthetic_generator_config_shapes(oracle, lib_built):
     exp = oracle.impact_search_c(*coll.numpy(), coll.n_docs, *qs.numpy(), 100, threads=4)
     np.testing.assert_array_equal(d.cpu().numpy(), exp[1])
     np.testing.assert_array_equal(s.cpu().numpy(), exp[0])
+
+
+@pytest.mark.parametrize("k,tile,qlen", [(10, 512, 16), (100, 512, 16), (100, 1000, 40), (700, 1024, 24)])
+def test_threshold_sharing_large_batch(oracle, lib_built, k, tile, qlen):
+    """Enough queries that the tiles of one query run far apart in time: later tiles then select by the per-query
+    threshold published by earlier ones (sparse_kernel.cuh) and merge their candidates into the shared list."""
+    rng = np.random.default_rng(77 + k)
+    n_docs, n_terms = 6000, 1500
+    indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 40)
+    qi, qt, qw = random_queries(rng, 1200, n_terms, qlen)
+    _check(oracle, indptr, docids, impacts, n_docs, qi, qt, qw, k, tile_docs=tile)
+
+
+def test_threshold_overflow_falls_back(oracle, lib_built):
+    """All docs tie: every later tile finds more candidates at the threshold than it has slots for."""
+    n_docs = 8192
+    indptr = np.array([0, n_docs - 2], dtype=np.uint64)
+    docids = np.arange(n_docs - 2, dtype=np.uint32)
+    impacts = np.full(n_docs - 2, 5, dtype=np.uint16)
+    nq = 900
+    qi = np.arange(nq + 1, dtype=np.uint64)
+    qt = np.zeros(nq, dtype=np.uint32)
+    qw = (1 + np.arange(nq) % 7).astype(np.uint32)
+    s, d, c = _check(oracle, indptr, docids, impacts, n_docs, qi, qt, qw, 50, tile_docs=512)
+    assert d[0].tolist() == list(range(50))
+
+
+@pytest.mark.parametrize("env", ["MSR_SPARSE_NO_THETA", "MSR_SPARSE_NO_DENSE"])
+def test_layout_switches_do_not_change_results(oracle, lib_built, monkeypatch, env):
+    """Dense impact rows and threshold sharing are pure optimisations: switching either off changes nothing."""
+    monkeypatch.setenv(env, "1")
+    rng = np.random.default_rng(5)
+    n_docs, n_terms = 5000, 800
+    indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 48, max_impact=65535)
+    qi, qt, qw = random_queries(rng, 600, n_terms, 12, max_w=1500)
+    s, d, c = _check(oracle, indptr, docids, impacts, n_docs, qi, qt, qw, 100, tile_docs=640)
+    assert s.max() >= 2 ** 24          # S6 rounding exercised on the posting path too
+
+
+def test_tile_size_not_multiple_of_8(oracle, lib_built):
+    rng = np.random.default_rng(6)
+    indptr, docids, impacts = random_csr(rng, 3001, 300, 30)
+    qi, qt, qw = random_queries(rng, 400, 300, 10)
+    _check(oracle, indptr, docids, impacts, 3001, qi, qt, qw, 20, tile_docs=501)
