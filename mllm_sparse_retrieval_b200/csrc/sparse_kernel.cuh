@@ -95,8 +95,10 @@ struct SegStage {                      // streaming phase view of the union regi
     uint32_t len[kSegMax];
     uint32_t w[kSegMax];
     uint32_t pref[kSegMax + 1];        // exclusive prefix of chunk counts
-    uint32_t drow[kSegMax];            // dense terms of the batch: row number, weight
-    uint32_t dw[kSegMax];
+    // dense terms of the batch: row start in 16-byte units and weight.  Plain terms fill the arrays from the front,
+    // terms that need the per-term float32 rounding of S6 from the back.
+    alignas(16) uint32_t drow[kSegMax];
+    alignas(16) uint32_t dw[kSegMax];
 };
 struct SelStage {                      // radix-select view
     uint32_t hist[kBins];
@@ -109,6 +111,7 @@ union StageUnion {
 };
 struct SmallState {
     uint32_t vmax, hits, out_cnt, cand_cnt, sel_b, sel_clt, sel_bcount, n_dense;
+    uint32_t n_dense_f, pad[3];
     uint32_t wsum[kWarps];
 };
 static_assert(sizeof(SmallState) % 16 == 0 && sizeof(StageUnion) % 16 == 0, "accumulators must stay 16-byte aligned");
@@ -117,6 +120,14 @@ __device__ __forceinline__ uint4 ld_stream_v4(const void* p) {
     uint4 v;
     asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
     return v;
+}
+
+// a[0..7] += w * (8 u16 impacts packed in v)
+__device__ __forceinline__ void dense_fma8(uint32_t (&a)[8], const uint4 v, const uint32_t w) {
+    a[0] += (v.x & 0xFFFFu) * w; a[1] += (v.x >> 16) * w;
+    a[2] += (v.y & 0xFFFFu) * w; a[3] += (v.y >> 16) * w;
+    a[4] += (v.z & 0xFFFFu) * w; a[5] += (v.z >> 16) * w;
+    a[6] += (v.w & 0xFFFFu) * w; a[7] += (v.w >> 16) * w;
 }
 
 // exclusive scan of one value per thread over the CTA (kThreads threads); returns exclusive prefix, *total = sum
@@ -185,7 +196,7 @@ sparse_score_topk_kernel(const SearchParams P) {
     uint64_t batch = qs;
     do {
         __syncthreads();   // previous batch fully consumed
-        if (tid == 0) S->n_dense = 0;
+        if (tid == 0) { S->n_dense = 0; S->n_dense_f = 0; }
         __syncthreads();
         uint32_t nchunks = 0;
         if (tid < kSegMax) {
@@ -199,9 +210,9 @@ sparse_score_topk_kernel(const SearchParams P) {
                     if ((uint64_t)w * P.term_maximp[t] >= (1u << 24)) w |= 0x80000000u;
                     const uint32_t di = P.dense_id[t];
                     if (di != kNotDense) {
-                        const uint32_t pos = atomicAdd(&S->n_dense, 1u);
-                        U->seg.drow[pos] = di;
-                        U->seg.dw[pos] = w;
+                        const uint32_t pos = (w >> 31) ? kSegMax - 1 - atomicAdd(&S->n_dense_f, 1u) : atomicAdd(&S->n_dense, 1u);
+                        U->seg.drow[pos] = di * (uint32_t)(P.dense_stride >> 3);
+                        U->seg.dw[pos] = w & 0x7FFFFFFFu;
                     } else {
                         start = seg_row[t];
                         len = seg_row[t + 1] - start;
@@ -217,32 +228,51 @@ sparse_score_topk_kernel(const SearchParams P) {
         }
         __syncthreads();
         {
-            const uint32_t nd = S->n_dense;
+            const uint32_t nd = S->n_dense, ndf = S->n_dense_f;
             const bool first = batch == qs;
-            if (first || nd) {
+            if (first || nd || ndf) {
                 const uint32_t nslots = (tl + 7) >> 3;          // 8 docs per thread and step
+                const uint4* rows = reinterpret_cast<const uint4*>(P.dense_rows + tile_lo);
                 for (uint32_t slot = tid; slot < nslots; slot += kThreads) {
-                    uint4 a0 = make_uint4(0, 0, 0, 0), a1 = a0;
+                    uint32_t a[8];
                     uint4* ap = reinterpret_cast<uint4*>(acc + 8 * slot);
-                    if (!first) { a0 = ap[0]; a1 = ap[1]; }
-                    const uint16_t* col = P.dense_rows + tile_lo + 8 * slot;
-#pragma unroll 4
-                    for (uint32_t d = 0; d < nd; ++d) {
-                        const uint4 v = ld_stream_v4(col + (size_t)U->seg.drow[d] * P.dense_stride);
-                        const uint32_t wraw = U->seg.dw[d], w = wraw & 0x7FFFFFFFu;
-                        if (!(wraw >> 31)) {
-                            a0.x += (v.x & 0xFFFFu) * w; a0.y += (v.x >> 16) * w;
-                            a0.z += (v.y & 0xFFFFu) * w; a0.w += (v.y >> 16) * w;
-                            a1.x += (v.z & 0xFFFFu) * w; a1.y += (v.z >> 16) * w;
-                            a1.z += (v.w & 0xFFFFu) * w; a1.w += (v.w >> 16) * w;
-                        } else {
-                            a0.x += (uint32_t)__uint2float_rn((v.x & 0xFFFFu) * w); a0.y += (uint32_t)__uint2float_rn((v.x >> 16) * w);
-                            a0.z += (uint32_t)__uint2float_rn((v.y & 0xFFFFu) * w); a0.w += (uint32_t)__uint2float_rn((v.y >> 16) * w);
-                            a1.x += (uint32_t)__uint2float_rn((v.z & 0xFFFFu) * w); a1.y += (uint32_t)__uint2float_rn((v.z >> 16) * w);
-                            a1.z += (uint32_t)__uint2float_rn((v.w & 0xFFFFu) * w); a1.w += (uint32_t)__uint2float_rn((v.w >> 16) * w);
+                    if (first) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) a[i] = 0;
+                    } else {
+                        const uint4 x = ap[0], y = ap[1];
+                        a[0] = x.x; a[1] = x.y; a[2] = x.z; a[3] = x.w; a[4] = y.x; a[5] = y.y; a[6] = y.z; a[7] = y.w;
+                    }
+                    const uint4* col = rows + slot;
+                    uint32_t d = 0;
+                    for (; d + 4 <= nd; d += 4) {               // 4 independent 16-byte loads in flight per thread
+                        const uint4 r = *reinterpret_cast<const uint4*>(&U->seg.drow[d]);
+                        const uint4 w = *reinterpret_cast<const uint4*>(&U->seg.dw[d]);
+                        const uint4 v0 = ld_stream_v4(col + r.x), v1 = ld_stream_v4(col + r.y);
+                        const uint4 v2 = ld_stream_v4(col + r.z), v3 = ld_stream_v4(col + r.w);
+                        dense_fma8(a, v0, w.x); dense_fma8(a, v1, w.y); dense_fma8(a, v2, w.z); dense_fma8(a, v3, w.w);
+                    }
+                    if (d < nd) {
+                        const uint32_t m = nd - d;              // 1..3 left
+                        const uint4 v0 = ld_stream_v4(col + U->seg.drow[d]);
+                        const uint4 v1 = ld_stream_v4(col + U->seg.drow[m > 1 ? d + 1 : d]);
+                        const uint4 v2 = ld_stream_v4(col + U->seg.drow[m > 2 ? d + 2 : d]);
+                        dense_fma8(a, v0, U->seg.dw[d]);
+                        dense_fma8(a, v1, m > 1 ? U->seg.dw[d + 1] : 0u);
+                        dense_fma8(a, v2, m > 2 ? U->seg.dw[d + 2] : 0u);
+                    }
+                    for (uint32_t f = 0; f < ndf; ++f) {        // S6: float32(boost*freq) per term
+                        const uint4 v = ld_stream_v4(col + U->seg.drow[kSegMax - 1 - f]);
+                        const uint32_t w = U->seg.dw[kSegMax - 1 - f];
+                        const uint32_t e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) {
+                            a[2 * i] += (uint32_t)__uint2float_rn((e[i] & 0xFFFFu) * w);
+                            a[2 * i + 1] += (uint32_t)__uint2float_rn((e[i] >> 16) * w);
                         }
                     }
-                    ap[0] = a0; ap[1] = a1;
+                    ap[0] = make_uint4(a[0], a[1], a[2], a[3]);
+                    ap[1] = make_uint4(a[4], a[5], a[6], a[7]);
                 }
             }
         }
