@@ -370,6 +370,14 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
     count_launch();
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail("term metadata");
     h->dense_stride = ((size_t)n_tiles * tile_docs + 7) / 8 * 8;
+    if ((uint64_t)h->n_dense * h->dense_stride * 2 >= (1ull << 32)) {
+        // the kernel addresses dense rows with 32-bit byte offsets: keep every term as posting buckets instead
+        build_term_meta_kernel<<<(n_terms + 1 + bt - 1) / bt, bt, 0, s>>>(d_indptr, d_df, n_terms, n_docs_global, 0xFFFFFFFFu,
+                                                                          h->term_keep, h->df_local, b_flag.as<uint32_t>());
+        build_dense_id_kernel<<<(n_terms + bt - 1) / bt, bt, 0, s>>>(b_flag.as<uint32_t>(), n_terms, h->dense_id);
+        count_launch(2);
+        h->n_dense = 0;
+    }
     if (h->n_dense) {
         if ((e = cudaMalloc(&h->dense_rows, (size_t)h->n_dense * h->dense_stride * 2)) != cudaSuccess) return fail("alloc dense rows");
         cudaMemsetAsync(h->dense_rows, 0, (size_t)h->n_dense * h->dense_stride * 2, s);
@@ -562,6 +570,7 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     P.n_docs = h->n_docs; P.n_terms = h->n_terms; P.tile_docs = h->tile_docs; P.n_tiles = h->n_tiles;
     P.doc_base = h->doc_base; P.q_indptr = d_qi; P.q_terms = d_qt; P.q_weights = d_qw; P.q_ok = d_ok;
     P.dense_id = h->dense_id; P.dense_rows = h->dense_rows; P.dense_stride = h->dense_stride;
+    P.dense_row_bytes = (uint32_t)(h->dense_stride * 2);
     P.k = k; P.k_stride = k_stride;
     P.cand_keys = (uint64_t*)(base + off_keys); P.cand_cnt = (uint32_t*)(base + off_cnt);
     P.theta = (unsigned long long*)(base + off_theta); P.tlist = (uint64_t*)(base + off_tlist);

@@ -43,6 +43,7 @@ struct SearchParams {
     const uint32_t* dense_id;     // [n_terms]
     const uint16_t* dense_rows;   // [n_dense][dense_stride]
     size_t dense_stride;
+    uint32_t dense_row_bytes;     // dense_stride * 2 (all rows together stay below 4 GiB)
     const uint8_t* q_ok;          // [nq_total] 1 = inside the exact-arithmetic range
     uint32_t q_lo, nq, k, k_stride;
     uint64_t* cand_keys;          // [nq][n_tiles][k_stride]
@@ -205,17 +206,23 @@ sparse_score_topk_kernel(const SearchParams P) {
             if (j < qe) {
                 const uint32_t t = P.q_terms[j];
                 w = P.q_weights[j];
-                if (t < P.n_terms && w && P.term_keep[t]) {
-                    // S6: float32(boost*freq) rounds once a product can reach 2^24 -> flag the term (bit 31)
-                    if ((uint64_t)w * P.term_maximp[t] >= (1u << 24)) w |= 0x80000000u;
-                    const uint32_t di = P.dense_id[t];
-                    if (di != kNotDense) {
-                        const uint32_t pos = (w >> 31) ? kSegMax - 1 - atomicAdd(&S->n_dense_f, 1u) : atomicAdd(&S->n_dense, 1u);
-                        U->seg.drow[pos] = di * (uint32_t)(P.dense_stride >> 3);
-                        U->seg.dw[pos] = w & 0x7FFFFFFFu;
+                if (t < P.n_terms && w) {
+                    // independent gathers first (one round trip), decisions after
+                    const uint32_t keep = P.term_keep[t], mi = P.term_maximp[t], di = P.dense_id[t];
+                    const uint32_t s0 = seg_row[t], s1 = seg_row[t + 1];
+                    if (keep) {
+                        // S6: float32(boost*freq) rounds once a product can reach 2^24 -> flag the term (bit 31)
+                        if ((uint64_t)w * mi >= (1u << 24)) w |= 0x80000000u;
+                        if (di != kNotDense) {
+                            const uint32_t pos = (w >> 31) ? kSegMax - 1 - atomicAdd(&S->n_dense_f, 1u) : atomicAdd(&S->n_dense, 1u);
+                            U->seg.drow[pos] = di * P.dense_row_bytes;
+                            U->seg.dw[pos] = w & 0x7FFFFFFFu;
+                        } else {
+                            start = s0;
+                            len = s1 - s0;
+                        }
                     } else {
-                        start = seg_row[t];
-                        len = seg_row[t + 1] - start;
+                        w = 0;
                     }
                 } else {
                     w = 0;
@@ -232,7 +239,7 @@ sparse_score_topk_kernel(const SearchParams P) {
             const bool first = batch == qs;
             if (first || nd || ndf) {
                 const uint32_t nslots = (tl + 7) >> 3;          // 8 docs per thread and step
-                const uint4* rows = reinterpret_cast<const uint4*>(P.dense_rows + tile_lo);
+                const char* rows = reinterpret_cast<const char*>(P.dense_rows + tile_lo);
                 for (uint32_t slot = tid; slot < nslots; slot += kThreads) {
                     uint32_t a[8];
                     uint4* ap = reinterpret_cast<uint4*>(acc + 8 * slot);
@@ -243,26 +250,25 @@ sparse_score_topk_kernel(const SearchParams P) {
                         const uint4 x = ap[0], y = ap[1];
                         a[0] = x.x; a[1] = x.y; a[2] = x.z; a[3] = x.w; a[4] = y.x; a[5] = y.y; a[6] = y.z; a[7] = y.w;
                     }
-                    const uint4* col = rows + slot;
+                    const uint32_t so = slot * 16u;             // row offsets are 32-bit byte offsets (checked at build)
                     uint32_t d = 0;
                     for (; d + 4 <= nd; d += 4) {               // 4 independent 16-byte loads in flight per thread
                         const uint4 r = *reinterpret_cast<const uint4*>(&U->seg.drow[d]);
                         const uint4 w = *reinterpret_cast<const uint4*>(&U->seg.dw[d]);
-                        const uint4 v0 = ld_stream_v4(col + r.x), v1 = ld_stream_v4(col + r.y);
-                        const uint4 v2 = ld_stream_v4(col + r.z), v3 = ld_stream_v4(col + r.w);
+                        const uint4 v0 = ld_stream_v4(rows + (r.x + so)), v1 = ld_stream_v4(rows + (r.y + so));
+                        const uint4 v2 = ld_stream_v4(rows + (r.z + so)), v3 = ld_stream_v4(rows + (r.w + so));
                         dense_fma8(a, v0, w.x); dense_fma8(a, v1, w.y); dense_fma8(a, v2, w.z); dense_fma8(a, v3, w.w);
                     }
-                    if (d < nd) {
-                        const uint32_t m = nd - d;              // 1..3 left
-                        const uint4 v0 = ld_stream_v4(col + U->seg.drow[d]);
-                        const uint4 v1 = ld_stream_v4(col + U->seg.drow[m > 1 ? d + 1 : d]);
-                        const uint4 v2 = ld_stream_v4(col + U->seg.drow[m > 2 ? d + 2 : d]);
-                        dense_fma8(a, v0, U->seg.dw[d]);
-                        dense_fma8(a, v1, m > 1 ? U->seg.dw[d + 1] : 0u);
-                        dense_fma8(a, v2, m > 2 ? U->seg.dw[d + 2] : 0u);
+                    if (nd & 2) {
+                        const uint2 r = *reinterpret_cast<const uint2*>(&U->seg.drow[d]);
+                        const uint2 w = *reinterpret_cast<const uint2*>(&U->seg.dw[d]);
+                        const uint4 v0 = ld_stream_v4(rows + (r.x + so)), v1 = ld_stream_v4(rows + (r.y + so));
+                        dense_fma8(a, v0, w.x); dense_fma8(a, v1, w.y);
+                        d += 2;
                     }
+                    if (nd & 1) dense_fma8(a, ld_stream_v4(rows + (U->seg.drow[d] + so)), U->seg.dw[d]);
                     for (uint32_t f = 0; f < ndf; ++f) {        // S6: float32(boost*freq) per term
-                        const uint4 v = ld_stream_v4(col + U->seg.drow[kSegMax - 1 - f]);
+                        const uint4 v = ld_stream_v4(rows + (U->seg.drow[kSegMax - 1 - f] + so));
                         const uint32_t w = U->seg.dw[kSegMax - 1 - f];
                         const uint32_t e[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
@@ -352,13 +358,21 @@ sparse_score_topk_kernel(const SearchParams P) {
         uint32_t amin = (uint32_t)tf;                           // smallest integer score whose float32 image is >= tf
         while (amin > 1 && __uint2float_rn(amin - 1) >= tf) --amin;
         const uint32_t cap = min(P.k_stride, (uint32_t)kUnionMax);
-        for (uint32_t i = tid; i < tl; i += kThreads) {
-            const uint32_t a = acc[i];
-            if (a >= amin) {
-                const uint64_t key = make_key(__uint2float_rn(a), gdoc0 + i);
-                if (key >= theta) {
-                    const uint32_t pos = atomicAdd(&S->cand_cnt, 1u);
-                    if (pos < cap) U->keys[pos] = key;
+        const uint32_t nvec = (tl + 3) >> 2;                     // 4 docs per thread and step (slots past tl hold 0)
+        for (uint32_t j = tid; j < nvec; j += kThreads) {
+            const uint4 x = reinterpret_cast<const uint4*>(acc)[j];
+            if (max(max(x.x, x.y), max(x.z, x.w)) >= amin) {
+                const uint32_t e[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                for (int u = 0; u < 4; ++u) {
+                    const uint32_t i = 4 * j + u;
+                    if (e[u] >= amin && i < tl) {
+                        const uint64_t key = make_key(__uint2float_rn(e[u]), gdoc0 + i);
+                        if (key >= theta) {
+                            const uint32_t pos = atomicAdd(&S->cand_cnt, 1u);
+                            if (pos < cap) U->keys[pos] = key;
+                        }
+                    }
                 }
             }
         }
