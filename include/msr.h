@@ -148,6 +148,14 @@ int msr_dense_index_info(const msr_dense_index* h, uint32_t info[5]);
 int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* queries, uint32_t k,
                      float* out_scores, int64_t* out_ids, int mode, int where, void* stream);
 
+/*
+ * The tensor-core pass of mode 2 on its own (tests, benchmarks, profiling): out_scores[q*ld + d] =
+ * sum_h bf16(queries[q,h]) * bf16(vecs[d,h]) accumulated in fp32 by tcgen05.mma.  Device pointers only; ld >= n_docs,
+ * ld % 4 == 0, dim % 8 == 0.  Asynchronous on `stream`.
+ */
+int msr_dense_tc_scores(msr_dense_index* h, uint32_t nq, const float* queries, float* out_scores, size_t ld,
+                        void* stream);
+
 /* ---------------------------------------------------------------------------------------------------------
  * Hybrid fusion (kernel (d)) = hybrid.fuse([dense_run, sparse_run], [alpha, 1-alpha]) for a query batch.
  * Inputs per modality: scores f32 [nq,k_*], docs i32 [nq,k_*] (global internal ids), counts u32 [nq] and

@@ -13,6 +13,7 @@
 #include <cuda_bf16.h>
 
 #include "common.cuh"
+#include "dense_tc.cuh"
 
 namespace msr {
 int topk_rows_launch(uint32_t nq, uint32_t n, const float* scores, size_t row_stride, uint32_t k, int32_t col_base,
@@ -278,4 +279,26 @@ extern "C" int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* qu
         MSR_CUDA_CHECK(cudaStreamSynchronize(s));
     }
     return MSR_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------------------
+// tensor-core pass on its own (tests, bench.py --dense, ncu): scores[nq, n_docs] = bf16(Q) . bf16(X)^T, fp32 out
+// ---------------------------------------------------------------------------------------------------------
+extern "C" int msr_dense_tc_scores(msr_dense_index* h, uint32_t nq, const float* queries, float* out_scores, size_t ld,
+                                   void* stream) {
+    MSR_REQUIRE(h && queries && out_scores, "msr_dense_tc_scores: NULL argument");
+    MSR_REQUIRE(h->n_docs > 0 && nq > 0, "msr_dense_tc_scores: empty index or query block");
+    MSR_REQUIRE(h->dim % 8 == 0, "msr_dense_tc_scores: dim %u is not a multiple of 8 (TMA row pitch)", h->dim);
+    MSR_REQUIRE(ld >= h->n_docs && ld % 4 == 0, "msr_dense_tc_scores: ld must be >= n_docs and a multiple of 4");
+    int rc = use_device(h->device);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    MSR_CUDA_CHECK(h->ws.reserve(align_up((size_t)nq * h->dim * 2, 256), s));
+    __nv_bfloat16* q16 = (__nv_bfloat16*)h->ws.p;
+    const size_t n = (size_t)nq * h->dim;
+    tc::to_bf16_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 148 * 16), 256, 0, s>>>(queries, q16, n);
+    count_launch();
+    MSR_CUDA_CHECK(cudaGetLastError());
+    return tc::dense_tc_scores_launch(q16, nq, h->v16, h->n_docs, h->dim, out_scores, ld, s);
 }

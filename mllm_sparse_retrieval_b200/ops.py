@@ -188,6 +188,17 @@ class DenseIndex:
             check(_lib.load().msr_dense_index_add(self._h, int(vecs.shape[0]), ptr(vecs), where,
                                                   current_stream_ptr(self.device)))
 
+    def tc_scores(self, queries):
+        """Tensor-core pass alone: CUDA fp32 queries [nq,dim] -> approximate scores fp32 [nq, n_docs] (bf16 inputs)."""
+        q = queries.to(torch.float32).contiguous()
+        n = self.ntotal
+        ld = (n + 3) // 4 * 4
+        out = torch.empty((q.shape[0], ld), dtype=torch.float32, device=q.device)
+        with torch.cuda.device(self.device):
+            check(_lib.load().msr_dense_tc_scores(self._h, int(q.shape[0]), ptr(q), ptr(out), ld,
+                                                  current_stream_ptr(self.device)))
+        return out[:, :n]
+
     def search(self, queries, k, mode=0):
         """numpy in -> numpy out (host path); CUDA tensor in -> CUDA tensors out (device path, asynchronous)."""
         if isinstance(queries, torch.Tensor) and queries.is_cuda:
