@@ -144,6 +144,11 @@ int msr_dense_index_info(const msr_dense_index* h, uint32_t info[5]);
  * accumulated in a fixed order (|err| <= 1e-6 abs on unit vectors), out_ids int64 [nq,k] (FAISS convention:
  * -1 / -3.4028235e38 padding when k > n_docs).  Order = score desc, id asc.
  * mode: 0 = auto, 1 = exact fp32 CUDA-core pass only, 2 = tcgen05 bf16 pass + certified fp32 re-score.
+ * Mode 2: approximate scores of all docs on the tensor cores, the 4k best (at least 256) re-scored in fp32 with the
+ * accumulation order of mode 1, and a per-query certificate that no other doc can reach the exact k-th score
+ * (bf16 rounding of both sides bounded by Cauchy-Schwarz from stored norms); uncertified queries are re-run by
+ * mode 1.  Both modes therefore return identical ids and bit-identical scores.  Mode 2 (and auto with nq >= 16)
+ * synchronises `stream` inside the call even with MSR_DEVICE.  Needs dim % 8 == 0 (auto falls back to mode 1).
  */
 int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* queries, uint32_t k,
                      float* out_scores, int64_t* out_ids, int mode, int where, void* stream);
@@ -153,6 +158,8 @@ int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* queries, uint
  * sum_h bf16(queries[q,h]) * bf16(vecs[d,h]) accumulated in fp32 by tcgen05.mma.  Device pointers only; ld >= n_docs,
  * ld % 4 == 0, dim % 8 == 0.  Asynchronous on `stream`.
  */
+/* Queries of the last mode-2 (or auto) search on this handle whose certificate failed and that were re-run exactly. */
+int msr_dense_last_fallback(const msr_dense_index* h, uint32_t* n);
 int msr_dense_tc_scores(msr_dense_index* h, uint32_t nq, const float* queries, float* out_scores, size_t ld,
                         void* stream);
 

@@ -188,6 +188,13 @@ class DenseIndex:
             check(_lib.load().msr_dense_index_add(self._h, int(vecs.shape[0]), ptr(vecs), where,
                                                   current_stream_ptr(self.device)))
 
+    @property
+    def last_fallback(self):
+        """Queries of the last tensor-core search whose certificate failed (re-run by the exact pass)."""
+        n = ctypes.c_uint32()
+        check(_lib.load().msr_dense_last_fallback(self._h, ctypes.byref(n)))
+        return int(n.value)
+
     def tc_scores(self, queries):
         """Tensor-core pass alone: CUDA fp32 queries [nq,dim] -> approximate scores fp32 [nq, n_docs] (bf16 inputs)."""
         q = queries.to(torch.float32).contiguous()

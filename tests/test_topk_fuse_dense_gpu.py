@@ -112,3 +112,64 @@ def test_dense_exact_matches_oracle(oracle, lib_built, n_docs, dim, nq, k):
     s2, ids2 = idx.search(torch.from_numpy(q).cuda(), k, mode=1)
     np.testing.assert_array_equal(ids2.cpu().numpy(), ids)
     np.testing.assert_array_equal(s2.cpu().numpy(), s)
+
+
+@pytest.mark.parametrize("n_docs,dim,nq,k", [(5000, 4096, 200, 100), (25000, 1024, 300, 100), (777, 256, 130, 1000),
+                                              (3000, 3584, 64, 10), (2048, 64, 129, 5)])
+def test_dense_tensor_core_mode_equals_exact_mode(oracle, lib_built, n_docs, dim, nq, k):
+    """Mode 2 (tcgen05 bf16 pass + fp32 re-score + certificate) returns the ids AND the bit pattern of the scores of
+    mode 1; both match the float64 oracle (ids identical up to fp32-resolution ties, scores within 1e-3 relative)."""
+    from mllm_sparse_retrieval_b200 import synth
+    from mllm_sparse_retrieval_b200.ops import DenseIndex
+    docs, q = synth.make_dense(n_docs, nq, dim=dim, seed=1002, device="cuda")
+    docs[11] = docs[4]
+    idx = DenseIndex(dim)
+    idx.add(docs)
+    s1, i1 = idx.search(q, k, mode=1)
+    s2, i2 = idx.search(q, k, mode=2)
+    n_fb = idx.last_fallback
+    s0, i0 = idx.search(q, k, mode=0)                        # auto picks the tensor-core path at this batch size
+    torch.testing.assert_close(i2, i1, rtol=0, atol=0)
+    torch.testing.assert_close(s2, s1, rtol=0, atol=0)
+    torch.testing.assert_close(i0, i1, rtol=0, atol=0)
+    assert n_fb <= nq // 4, f"{n_fb} of {nq} queries failed the certificate"
+    kk = min(k, n_docs)
+    es, eids = oracle.flat_ip_search_numpy(docs.cpu().numpy(), q.cpu().numpy(), kk)
+    assert (i2[:, :kk].cpu().numpy() == eids).mean() > 0.999
+    np.testing.assert_allclose(s2[:, :kk].cpu().numpy(), es, rtol=1e-3, atol=2e-6)
+    # host path of the C ABI
+    hs, hi = idx.search(q.cpu().numpy(), k, mode=2)
+    np.testing.assert_array_equal(hi, i1.cpu().numpy())
+
+
+def test_dense_certificate_falls_back_on_near_ties(oracle, lib_built):
+    """Thousands of near-duplicate docs: bf16 cannot separate them, the certificate must fail and the exact pass
+    must take over -- results still equal mode 1."""
+    from mllm_sparse_retrieval_b200.ops import DenseIndex
+    g = torch.Generator(device="cuda"); g.manual_seed(5)
+    dim, n_docs, nq, k = 512, 6000, 48, 50
+    base = torch.randn(dim, generator=g, device="cuda")
+    docs = base[None, :] + 1e-4 * torch.randn(n_docs, dim, generator=g, device="cuda")
+    docs = docs / docs.norm(dim=1, keepdim=True)
+    q = base[None, :] + 0.05 * torch.randn(nq, dim, generator=g, device="cuda")
+    q = q / q.norm(dim=1, keepdim=True)
+    idx = DenseIndex(dim)
+    idx.add(docs)
+    s1, i1 = idx.search(q, k, mode=1)
+    s2, i2 = idx.search(q, k, mode=2)
+    assert idx.last_fallback == nq
+    torch.testing.assert_close(i2, i1, rtol=0, atol=0)
+    torch.testing.assert_close(s2, s1, rtol=0, atol=0)
+
+
+def test_tensor_core_scores_match_bf16_matmul(lib_built):
+    """The tcgen05 pass alone against a torch fp32 matmul of the bf16-rounded operands (tolerance: fp32 accumulation)."""
+    from mllm_sparse_retrieval_b200.ops import DenseIndex
+    g = torch.Generator(device="cuda"); g.manual_seed(3)
+    for n, nq, dim in [(256, 128, 64), (1000, 37, 128), (4099, 257, 4096)]:
+        x = torch.randn(n, dim, generator=g, device="cuda"); x = x / x.norm(dim=1, keepdim=True)
+        q = torch.randn(nq, dim, generator=g, device="cuda"); q = q / q.norm(dim=1, keepdim=True)
+        idx = DenseIndex(dim); idx.add(x)
+        got = idx.tc_scores(q)
+        ref = q.bfloat16().float() @ x.bfloat16().float().T
+        torch.testing.assert_close(got, ref, rtol=0, atol=2e-6)
