@@ -49,6 +49,14 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--check", type=int, default=32, help="queries verified against the oracle after the run")
+    ap.add_argument("--workload", default="sparse", choices=["sparse", "dense", "hybrid"],
+                    help="sparse = the headline metric (default); dense / hybrid = the other kernels of the path (bench_extra.py)")
+    ap.add_argument("--dense-docs", type=int, default=25000)
+    ap.add_argument("--dense-nq", type=int, default=5000)
+    ap.add_argument("--dense-dim", type=int, default=4096)
+    ap.add_argument("--hybrid-nq", type=int, default=25000)
+    ap.add_argument("--depth", type=int, default=1000)
+    ap.add_argument("--alpha", type=float, default=0.5)
     return ap.parse_args()
 
 
@@ -349,6 +357,11 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if a.impl == "reference":
         run_reference(a, rank, world)
+        return
+    if a.workload != "sparse":
+        if rank == 0:
+            import bench_extra
+            (bench_extra.run_dense if a.workload == "dense" else bench_extra.run_hybrid)(a, ROOT, ClockSampler)
         return
     if world > 1:
         import torch

@@ -206,18 +206,27 @@ class DenseIndex:
                                                   current_stream_ptr(self.device)))
         return out[:, :n]
 
-    def search(self, queries, k, mode=0):
-        """numpy in -> numpy out (host path); CUDA tensor in -> CUDA tensors out (device path, asynchronous)."""
-        if isinstance(queries, torch.Tensor) and queries.is_cuda:
+    def search(self, queries, k, mode=0, out=None):
+        """numpy / CPU tensor in -> host arrays out (host path, H2D + D2H inside the call); CUDA tensor in -> CUDA
+        tensors out (device path).  ``out`` = preallocated (scores, ids) of the matching kind."""
+        if isinstance(queries, torch.Tensor) and not queries.is_cuda:
+            q = queries.to(torch.float32).contiguous()          # e.g. pinned host memory
+            nq = q.shape[0]
+            if out is None:
+                out = (torch.empty((nq, k), dtype=torch.float32), torch.empty((nq, k), dtype=torch.int64))
+            where = MSR_HOST
+        elif isinstance(queries, torch.Tensor) and queries.is_cuda:
             q = queries.to(torch.float32).contiguous()
             nq = q.shape[0]
-            out = (torch.empty((nq, k), dtype=torch.float32, device=q.device),
-                   torch.empty((nq, k), dtype=torch.int64, device=q.device))
+            if out is None:
+                out = (torch.empty((nq, k), dtype=torch.float32, device=q.device),
+                       torch.empty((nq, k), dtype=torch.int64, device=q.device))
             where = MSR_DEVICE
         else:
             q = np.ascontiguousarray(np.asarray(queries), dtype=np.float32)
             nq = q.shape[0]
-            out = (np.empty((nq, k), dtype=np.float32), np.empty((nq, k), dtype=np.int64))
+            if out is None:
+                out = (np.empty((nq, k), dtype=np.float32), np.empty((nq, k), dtype=np.int64))
             where = MSR_HOST
         assert q.shape[1] == self.dim
         with torch.cuda.device(self.device):
