@@ -164,6 +164,22 @@ int msr_dense_tc_scores(msr_dense_index* h, uint32_t nq, const float* queries, f
                         void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
+ * On-device query / document vector construction.
+ * Replaces get_img_valid_tokens_values (/root/reference/src/encode.py:56-93; the full-vocabulary branch of
+ * get_text_valid_tokens_values :114-124), the query-string builder (src/search.py:419-422) / doc-vector builder
+ * (src/encode.py:351-352) and pyserini's TokFreqQueryEncoder for a batch of activation rows that are already on the GPU.
+ * logits [n_rows, row_stride] of dtype 0 = f32, 1 = f16, 2 = bf16 (first `vocab` columns used).  Per row: top-`top`
+ * by (value desc, token id asc); token ids >= vocab_len are skipped with the reference's value shift; weight =
+ * rint(float32(value)*100) half-even; token id -> term id via token_to_term[vocab_len] (-1 = not in the index; NULL =
+ * identity); duplicates merged (doc_mode 0: sum = query string semantics, 1: last wins = doc vector semantics).
+ * Output = a query CSR at fixed pitch: out_indptr[r] = r*top, unused slots have weight 0 (ignored by msr_sparse_search).
+ * Device pointers only, asynchronous on `stream`.  top <= 1024, vocab >= top.
+ */
+int msr_quantise_topk(int device, uint32_t n_rows, uint32_t vocab, const void* logits, int dtype, size_t row_stride,
+                      uint32_t top, uint32_t vocab_len, const int32_t* token_to_term, int doc_mode,
+                      uint64_t* out_indptr, uint32_t* out_terms, uint32_t* out_weights, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
  * Hybrid fusion (kernel (d)) = hybrid.fuse([dense_run, sparse_run], [alpha, 1-alpha]) for a query batch.
  * Inputs per modality: scores f32 [nq,k_*], docs i32 [nq,k_*] (global internal ids), counts u32 [nq] and
  * self ids i32 [nq] (the query's own id in the doc id space, or -1): with remove_query != 0 a doc equal to

@@ -155,6 +155,25 @@ class ImpactCollection:
         np.cumsum(np.bincount(term_of[m], minlength=self.n_terms), out=indptr[1:])
         return indptr, (self.post_docs[m] - lo).astype(np.uint32), self.post_impacts[m]
 
+    def token_to_term_map(self, vocab_dict, is_filtered=False):
+        """int32 [len(vocab_dict)]: tokenizer id -> term id of this index, -1 when the token is not in the dictionary.
+
+        The string is built as the reference builds it (src/encode.py:78-83): ``vocab_dict[i].lower()``, through
+        ``filter_token`` when ``is_filtered`` -- then split on whitespace as the query encoder would (S4).  Used by
+        ops.quantise_topk to go from activation rows to a query CSR without leaving the GPU."""
+        n = len(vocab_dict)
+        out = np.full(n, -1, dtype=np.int32)
+        for i in range(n):
+            tok = vocab_dict[i].lower()
+            if is_filtered and tok and (ord(tok[0]) < ord('a') or ord(tok[0]) > ord('z')):
+                tok = tok[1:]
+            pieces = tok.split()
+            if len(pieces) > 1:
+                raise ValueError(f"vocabulary entry {i} ({tok!r}) contains whitespace: it is several index terms")
+            if pieces:
+                out[i] = self.term_to_id.get(pieces[0], -1)
+        return out
+
     def encode_queries(self, queries):
         """S4 + dictionary lookup: list of query strings (or {token: weight} maps) -> query CSR (u64, u32, u32).
 

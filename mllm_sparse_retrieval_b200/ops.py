@@ -253,3 +253,28 @@ def fuse_lists(d_scores, d_docs, d_counts, s_scores, s_docs, s_counts, self_ids,
                                    float(w_sparse), ptr(out[0]), ptr(out[1]), ptr(out[2]), ptr(out[3]),
                                    current_stream_ptr(di)))
     return out
+
+
+_DTYPES = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
+
+
+def quantise_topk(logits, top, token_to_term=None, vocab_len=None, doc_mode=False):
+    """Activation rows on the GPU -> query CSR on the GPU (msr_quantise_topk): (indptr i64 [n+1], terms i32, weights i32).
+
+    logits: CUDA tensor [n_rows, V] (f32 / f16 / bf16, last dim contiguous); token_to_term: CUDA int32 [vocab_len] or None."""
+    assert logits.is_cuda and logits.dim() == 2 and logits.stride(1) == 1 and logits.dtype in _DTYPES
+    n, V = logits.shape
+    dev = logits.device
+    vocab_len = V if vocab_len is None else int(vocab_len)
+    if token_to_term is not None:
+        token_to_term = token_to_term.to(device=dev, dtype=torch.int32).contiguous()
+        assert token_to_term.numel() >= min(vocab_len, V)
+    indptr = torch.empty((n + 1,), dtype=torch.int64, device=dev)
+    terms = torch.empty((n * top,), dtype=torch.int32, device=dev)
+    weights = torch.empty((n * top,), dtype=torch.int32, device=dev)
+    di = _dev_index(dev)
+    with torch.cuda.device(di):
+        check(_lib.load().msr_quantise_topk(di, n, V, ptr(logits), _DTYPES[logits.dtype], logits.stride(0), int(top),
+                                            vocab_len, ptr(token_to_term), int(bool(doc_mode)), ptr(indptr), ptr(terms),
+                                            ptr(weights), current_stream_ptr(di)))
+    return indptr, terms, weights

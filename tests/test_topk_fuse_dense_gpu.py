@@ -173,3 +173,75 @@ def test_tensor_core_scores_match_bf16_matmul(lib_built):
         got = idx.tc_scores(q)
         ref = q.bfloat16().float() @ x.bfloat16().float().T
         torch.testing.assert_close(got, ref, rtol=0, atol=2e-6)
+
+
+def _csr_row_to_dict(coll, ip, t, w, r):
+    lo, hi = int(ip[r]), int(ip[r + 1])
+    return {coll.terms[int(a)]: int(b) for a, b in zip(t[lo:hi], w[lo:hi]) if int(b) > 0}
+
+
+def test_quantise_topk_matches_reference_fixtures(oracle, lib_built):
+    """msr_quantise_topk against the fixtures generated from the reference's own get_img_valid_tokens_values and
+    query-string / doc-vector builders (tests/golden/reference_glue.json), and against the oracle restatement."""
+    import json, os
+    from collections import Counter
+    from mllm_sparse_retrieval_b200.index import ImpactCollection
+    from mllm_sparse_retrieval_b200.ops import quantise_topk
+    with open(os.path.join(os.path.dirname(__file__), "golden", "reference_glue.json")) as f:
+        golden = json.load(f)
+    for c in golden["quantiser"]:
+        vocab = c["vocab"]
+        logits = np.asarray(c["logits"], dtype=np.float32)
+        uniq, cnt = np.unique(logits, return_counts=True)
+        top = c["sparse_length"] if c["sparse_manual"] else 128
+        top = min(top, len(logits))
+        if (cnt > 1).any() and logits[np.argsort(-logits)[top - 1]] in uniq[cnt > 1]:
+            continue                                         # torch.topk tie order at the cut is unspecified
+        # an index whose dictionary holds every lower-cased token, so nothing is dropped by the dictionary
+        names = sorted({t for v in vocab for t in v.lower().split()} | {t[1:] for v in vocab for t in [v.lower()] if len(t) > 1})
+        coll = ImpactCollection.from_vectors(["d"], [{n: 1 for n in names if n.split() == [n]}])
+        vocab_len = len(vocab)
+        tmap = torch.from_numpy(coll.token_to_term_map(vocab, is_filtered=c["is_filtered"])).cuda()
+        x = torch.from_numpy(logits)[None, :].cuda()
+        for dt in (torch.float32,):
+            ip, t, w = quantise_topk(x.to(dt), top, tmap, vocab_len=vocab_len, doc_mode=False)
+            got = _csr_row_to_dict(coll, ip.cpu().numpy(), t.cpu().numpy(), w.cpu().numpy(), 0)
+            assert got == dict(Counter(c["query_string"].split())), c["sparse_length"]
+            ip, t, w = quantise_topk(x.to(dt), top, tmap, vocab_len=vocab_len, doc_mode=True)
+            got = _csr_row_to_dict(coll, ip.cpu().numpy(), t.cpu().numpy(), w.cpu().numpy(), 0)
+            assert got == {k: v for k, v in c["doc_vector"].items() if v > 0}
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16, torch.bfloat16])
+def test_quantise_topk_feeds_sparse_search(oracle, lib_built, dtype):
+    """logits -> query CSR on the device -> msr_sparse_search, equal to the host path (oracle quantiser -> query
+    strings -> ImpactCollection.encode_queries -> search)."""
+    from mllm_sparse_retrieval_b200.index import ImpactCollection
+    from mllm_sparse_retrieval_b200.ops import SparseIndex, quantise_topk
+    rng = np.random.default_rng(4)
+    V, n_docs, nq, top = 3000, 400, 50, 64
+    vocab = [f"Tok{i}" if i % 7 else f"tok{i - 1}" for i in range(V)]        # case-folding collisions: Tok8 / tok8 ...
+    vocab_len = V - 5                                                        # ids beyond the dictionary (value-shift quirk)
+    vecs = []
+    for _ in range(n_docs):
+        ids = rng.choice(V - 200, size=30, replace=False)                    # 200 tokens never indexed
+        vecs.append({vocab[i].lower(): int(rng.integers(1, 300)) for i in ids})
+    coll = ImpactCollection.from_vectors([str(i) for i in range(n_docs)], vecs)
+    logits = torch.from_numpy(np.log1p(np.maximum(rng.standard_normal((nq, V)) * 2, 0)).astype(np.float32)).cuda().to(dtype)
+    tmap = torch.from_numpy(coll.token_to_term_map(vocab)).cuda()
+    ip, t, w = quantise_topk(logits, top, tmap, vocab_len=vocab_len)
+    idx = SparseIndex(coll.indptr, coll.post_docs, coll.post_impacts, coll.n_docs)
+    s, d, c = idx.search(ip, t, w, 20)
+    idx.status()
+    # host path through the oracle's restatement of the reference quantiser
+    lf = logits.float().cpu().numpy()
+    strings = []
+    for r in range(nq):
+        counts = oracle.quantise_row(lf[r], top, vocab, vocab_len=vocab_len)
+        strings.append(" ".join(tok for tok, n in counts.items() for _ in range(n)))
+        got = _csr_row_to_dict(coll, ip.cpu().numpy(), t.cpu().numpy(), w.cpu().numpy(), r)
+        assert got == {k: v for k, v in counts.items() if k in coll.term_to_id}, r
+    qi, qt, qw = coll.encode_queries(strings)
+    es, ed, ec = oracle.impact_search_c(coll.indptr, coll.post_docs, coll.post_impacts, coll.n_docs, qi, qt, qw, 20)
+    np.testing.assert_array_equal(d.cpu().numpy(), ed)
+    np.testing.assert_array_equal(s.cpu().numpy(), es)
