@@ -158,3 +158,67 @@ def test_end_to_end_hybrid_like_search_py(oracle, lib_built, tmp_path):
         for doc in exp[qid]:
             assert fused[qid][doc] == exp[qid][doc] and type(fused[qid][doc]) is type(exp[qid][doc])
         assert qid not in fused[qid]
+
+
+def test_search_cli_writes_reference_format_runs(oracle, lib_built, tmp_path):
+    """python -m mllm_sparse_retrieval_b200.search on the files src/encode.py writes (corpus_0.jsonl / corpus_0.pkl /
+    query.tsv / query.pkl): hybrid run file equals oracle searchers -> get_run_dict -> fuse -> stable sort."""
+    import json, pickle
+    from mllm_sparse_retrieval_b200 import search as cli
+    from mllm_sparse_retrieval_b200.index import ImpactCollection
+    rng = np.random.default_rng(8)
+    n_docs, nq, dim, V, depth = 300, 40, 64, 200, 50
+    doc_ids = [str(x) for x in rng.permutation(1000)[:n_docs]]
+    vecs = [{f"w{j}": int(rng.integers(1, 200)) for j in rng.choice(V, 12, replace=False)} for _ in range(n_docs)]
+    sp = tmp_path / "sparse"; sp.mkdir()
+    with open(sp / "corpus_0.jsonl", "w") as f:
+        for i, v in zip(doc_ids, vecs):
+            f.write(json.dumps({"id": i, "content": "", "vector": v}) + "\n")
+    reps = rng.standard_normal((n_docs, dim)).astype(np.float32); reps /= np.linalg.norm(reps, axis=1, keepdims=True)
+    dn = tmp_path / "dense"; dn.mkdir()
+    with open(dn / "corpus_0.pkl", "wb") as f:
+        pickle.dump((reps, doc_ids), f)
+    qids = [doc_ids[i] if i % 3 == 0 else f"q{i}" for i in range(nq)]            # some query ids equal doc ids
+    q_reps = rng.standard_normal((nq, dim)).astype(np.float32); q_reps /= np.linalg.norm(q_reps, axis=1, keepdims=True)
+    with open(dn / "query.pkl", "wb") as f:
+        pickle.dump((q_reps, qids), f)
+    topics = [" ".join(f"w{j}" for j in rng.choice(V, 8) for _ in range(int(rng.integers(1, 5)))) for _ in range(nq)]
+    with open(sp / "query.tsv", "w") as f:
+        for q, t in zip(qids, topics):
+            f.write(f"{q}\t{t}\n")
+    out = tmp_path / "runs"
+    cli.main(["--passage_reps", str(dn), "--sparse_index", str(sp), "--query_reps", str(dn), "--query_sparse", str(sp),
+              "--depth", str(depth), "--alpha", "0.3", "--remove_query", "--save_dir", str(out), "--batch_size", "16",
+              "--model_name_or_path", "ignored", "--threads", "16"])
+    # expectation through the oracle and the reference-shaped glue
+    coll = ImpactCollection.from_vectors(doc_ids, vecs)
+    qi, qt, qw = coll.encode_queries(topics)
+    ss, sd, sc = oracle.impact_search_c(coll.indptr, coll.post_docs, coll.post_impacts, coll.n_docs, qi, qt, qw, depth)
+    ds, di = oracle.flat_ip_search_numpy(reps, q_reps, depth)
+    dense_run = oracle.get_run_dict(qids, [[np.float32(x) for x in r] for r in ds], [[doc_ids[j] for j in r] for r in di], True)
+    sparse_run = oracle.get_run_dict(qids, [[float(x) for x in ss[r, :sc[r]]] for r in range(nq)],
+                                     [[coll.docids[j] for j in sd[r, :sc[r]]] for r in range(nq)], True)
+    fused = oracle.fuse([dense_run, sparse_run], [0.3, 0.7])
+    lines = (out / "run.fusion.trec").read_text().splitlines()
+    got = {}
+    for ln in lines:
+        q, q0, d, rank, score, name = ln.split()
+        assert q0 == "Q0" and name == "fusion"
+        got.setdefault(q, []).append((d, int(rank), float(score)))
+    for q in qids:
+        exp = sorted(fused[q].items(), key=lambda kv: kv[1], reverse=True)
+        g = got[q]
+        assert [r for _, r, _ in g] == list(range(1, len(g) + 1))
+        assert len(g) == len(exp)
+        np.testing.assert_allclose([s for _, _, s in g], [float(v) for _, v in exp], rtol=1e-5, atol=1e-7)
+        # identical docs wherever neighbouring fused scores are not within float32 noise of each other
+        ev = np.array([float(v) for _, v in exp])
+        for j, ((gd, _, _), (ed, _)) in enumerate(zip(g, exp)):
+            if gd != ed:
+                assert np.sum(np.abs(ev - ev[j]) < 1e-6) > 1, (q, j, gd, ed)
+        assert q not in [d for d, _, _ in g]                                   # remove_query
+    assert (out / "run.dense.trec").exists() and (out / "run.sparse.trec").exists()
+    srun = (out / "run.sparse.trec").read_text().splitlines()
+    first_q = qids[0]
+    exp_docs = [d for d in sparse_run[first_q]["docs"]]
+    assert [ln.split()[2] for ln in srun if ln.split()[0] == first_q] == exp_docs
