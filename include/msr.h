@@ -131,7 +131,8 @@ int msr_topk_rows(int device, uint32_t nq, uint32_t n, const float* scores, size
 /* ---------------------------------------------------------------------------------------------------------
  * Dense flat inner-product index (kernel (c)).
  * vecs = [n_docs, dim] row-major fp32 (the (reps, lookup) pickle of src/encode.py:386-457 after pickle_load,
- * search.py:49-52).  The index stores bf16 for the tensor-core pass AND fp32 for the exact re-score.
+ * search.py:49-52).  The index stores fp16 for the tensor-core pass (the reference's own
+ * GPU storage type, GpuClonerOptions.useFloat16) AND fp32 for the exact re-score.
  * msr_dense_index_add appends rows (FaissFlatSearcher.add).  Row ids are doc_base + row.
  */
 int msr_dense_index_create(int device, uint32_t dim, int32_t doc_base, msr_dense_index** out);
@@ -143,23 +144,32 @@ int msr_dense_index_info(const msr_dense_index* h, uint32_t info[5]);
  * Exact top-k by inner product: queries [nq, dim] fp32; out_scores fp32 [nq,k] are fp32 dot products
  * accumulated in a fixed order (|err| <= 1e-6 abs on unit vectors), out_ids int64 [nq,k] (FAISS convention:
  * -1 / -3.4028235e38 padding when k > n_docs).  Order = score desc, id asc.
- * mode: 0 = auto, 1 = exact fp32 CUDA-core pass only, 2 = tcgen05 bf16 pass + certified fp32 re-score.
- * Mode 2: approximate scores of all docs on the tensor cores, the 4k best (at least 256) re-scored in fp32 with the
- * accumulation order of mode 1, and a per-query certificate that no other doc can reach the exact k-th score
- * (bf16 rounding of both sides bounded by Cauchy-Schwarz from stored norms); uncertified queries are re-run by
- * mode 1.  Both modes therefore return identical ids and bit-identical scores.  Mode 2 (and auto with nq >= 16)
- * synchronises `stream` inside the call even with MSR_DEVICE.  Needs dim % 8 == 0 (auto falls back to mode 1).
+ * mode: 0 = auto, 1 = exact fp32 CUDA-core pass only, 2 = tcgen05 fp16 pass + certified fp32 re-score.
+ * Mode 2: approximate scores a(d) of all docs on the tensor cores with the selection FUSED into the GEMM epilogue (docs
+ * with a(d) >= a per-query threshold, estimated from a strided sample of the index, are appended to a candidate buffer; no
+ * score matrix is written).  With E = a Cauchy-Schwarz bound on |exact - a| from stored norms (fp16 rounding of both
+ * sides + fp32 accumulation), the docs with a(d) >= a_k - 2E (a_k = k-th best a) provably contain the exact top-k; they
+ * are re-scored in fp32 with the accumulation order of mode 1.  A query is certified when its buffer did not overflow,
+ * holds >= k docs and the threshold was <= a_k - 2E; uncertified queries are re-run by mode 1.  Both modes therefore
+ * return identical ids and bit-identical scores.  Mode 2 (and auto with nq >= 16, n_docs >= 4096) synchronises
+ * `stream` inside the call even with MSR_DEVICE.  Needs dim % 8 == 0 (auto falls back to mode 1).
  */
 int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* queries, uint32_t k,
                      float* out_scores, int64_t* out_ids, int mode, int where, void* stream);
 
 /*
- * The tensor-core pass of mode 2 on its own (tests, benchmarks, profiling): out_scores[q*ld + d] =
- * sum_h bf16(queries[q,h]) * bf16(vecs[d,h]) accumulated in fp32 by tcgen05.mma.  Device pointers only; ld >= n_docs,
- * ld % 4 == 0, dim % 8 == 0.  Asynchronous on `stream`.
+ * Per-kernel timing of mode 2 for bench.py's roofline: returns the summed CUDA-event durations (ms) of the fused
+ * tcgen05 pass (GEMM + selection epilogue) and of the exact re-score over all query blocks since the previous call
+ * plus their count, then switches event recording on (enable != 0) or off.  Searches synchronise internally.
  */
+int msr_dense_profile(msr_dense_index* h, int enable, double* tc_ms, double* rescore_ms, uint64_t* launches);
 /* Queries of the last mode-2 (or auto) search on this handle whose certificate failed and that were re-run exactly. */
 int msr_dense_last_fallback(const msr_dense_index* h, uint32_t* n);
+/*
+ * The tensor-core pass of mode 2 on its own (tests, benchmarks, profiling): out_scores[q*ld + d] =
+ * sum_h fp16(queries[q,h]) * fp16(vecs[d,h]) accumulated in fp32 by tcgen05.mma.  Device pointers only; ld >= n_docs,
+ * ld % 4 == 0, dim % 8 == 0.  Asynchronous on `stream`.
+ */
 int msr_dense_tc_scores(msr_dense_index* h, uint32_t nq, const float* queries, float* out_scores, size_t ld,
                         void* stream);
 

@@ -41,6 +41,7 @@ def _declare(lib):
         "msr_dense_index_destroy": (I, [P]),
         "msr_dense_index_info": (I, [P, P]),
         "msr_dense_search": (I, [P, U32, P, U32, P, P, I, I, P]),
+        "msr_dense_profile": (I, [P, I, ctypes.POINTER(D), ctypes.POINTER(D), ctypes.POINTER(U64)]),
         "msr_dense_last_fallback": (I, [P, ctypes.POINTER(U32)]),
         "msr_dense_tc_scores": (I, [P, U32, P, P, ctypes.c_size_t, P]),
         "msr_quantise_topk": (I, [I, U32, U32, P, I, ctypes.c_size_t, U32, U32, P, I, P, P, P, P]),

@@ -3,14 +3,16 @@
 // Replaces tevatron FaissFlatSearcher / faiss.IndexFlatIP (reference call sites src/search.py:232,237,57,59 and the
 // fp16 GPU clone :254-270) under rules D1-D6 of SURVEY.md 8(a).
 //
-// The index keeps two copies of the vectors in HBM: fp32 [n, dim] (exact scores) and bf16 [n, dim] (tensor-core
-// pass).  Search modes:
+// The index keeps two copies of the vectors in HBM: fp32 [n, dim] (exact scores) and fp16 [n, dim] (tensor-core
+// pass; fp16 is what the reference's own GPU path stores, GpuClonerOptions.useFloat16).  Search modes:
 //   1  exact: fp32 CUDA-core inner products in a fixed accumulation order -> score rows -> radix-select top-k;
-//   2  tcgen05: bf16 x bf16 -> fp32 tensor-core pass (dense_tc.cuh) producing approximate score rows, top-k' of
-//      those, exact fp32 re-score of the k' candidates, and a CERTIFICATE per query that no doc outside the
-//      candidates can reach the exact k-th score; queries that fail it are re-run in mode 1.
+//   2  tcgen05: fp16 x fp16 -> fp32 tensor-core pass (dense_tc.cuh) whose epilogue keeps only the docs above a
+//      per-query threshold (selection fused into the GEMM, no score matrix in HBM), exact fp32 re-score of a
+//      candidate set that is CERTIFIED to hold the exact top-k; queries that fail the certificate are re-run in mode 1.
 //   0  auto: mode 2 when the batch is large enough to be tensor-bound, else mode 1 (HBM-bound GEMV regime).
-#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
+#include <cmath>
 
 #include <vector>
 
@@ -27,11 +29,16 @@ struct msr_dense_index {
     uint32_t dim = 0, n_docs = 0, capacity = 0;
     int32_t doc_base = 0;
     float* v32 = nullptr;
-    __nv_bfloat16* v16 = nullptr;
+    __half* v16 = nullptr;          // fp16 copy for the tensor-core pass
     float* err16 = nullptr;          // [capacity] || v32 - float(v16) ||_2 per row (certificate of mode 2)
-    float* stats = nullptr;          // [2] max row norm, max row bf16 error over the whole index (certificate of mode 2)
+    float* stats = nullptr;          // [2] max row norm, max row fp16 error over the whole index (certificate of mode 2)
     msr::Workspace ws;
     uint32_t last_fallback = 0;      // queries of the last mode-2 search that needed the exact pass
+    // optional per-kernel timing (msr_dense_profile): events bracket the fused GEMM pass and the re-score of every block
+    bool profiling = false;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+    double prof_tc_ms = 0, prof_rescore_ms = 0;
+    uint64_t prof_launches = 0;
 };
 
 namespace msr {
@@ -40,19 +47,19 @@ constexpr int kIpThreads = 256;
 constexpr int kIpWarps = kIpThreads / 32;
 constexpr int kIpQ = 4;              // queries held in shared memory per pass
 
-// fp32 -> bf16 copy + per-row quantisation error norm
-__global__ void dense_convert_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+// fp32 -> fp16 copy + per-row quantisation error norm (overflow to inf makes the error inf: mode 2 then certifies nothing)
+__global__ void dense_convert_kernel(const float* __restrict__ src, __half* __restrict__ dst,
                                      float* __restrict__ err, float* __restrict__ stats, uint32_t n_rows, uint32_t dim) {
     const uint32_t warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (warp >= n_rows) return;
     const float* s = src + (size_t)warp * dim;
-    __nv_bfloat16* d = dst + (size_t)warp * dim;
+    __half* d = dst + (size_t)warp * dim;
     float e2 = 0.f, n2 = 0.f;
     for (uint32_t i = lane; i < dim; i += 32) {
         float x = s[i];
-        __nv_bfloat16 b = __float2bfloat16_rn(x);
+        __half b = __float2half_rn(x);
         d[i] = b;
-        float r = x - __bfloat162float(b);
+        float r = x - __half2float(b);
         e2 = fmaf(r, r, e2);
         n2 = fmaf(x, x, n2);
     }
@@ -159,6 +166,7 @@ extern "C" int msr_dense_index_destroy(msr_dense_index* h) {
     if (!h) return MSR_OK;
     cudaSetDevice(h->device);
     cudaFree(h->v32); cudaFree(h->v16); cudaFree(h->err16); cudaFree(h->stats);
+    for (cudaEvent_t e : h->ev) if (e) cudaEventDestroy(e);
     h->ws.release();
     delete h;
     return MSR_OK;
@@ -185,7 +193,7 @@ extern "C" int msr_dense_index_add(msr_dense_index* h, uint32_t n_rows, const fl
     if (need > h->capacity) {
         uint32_t cap = h->capacity ? (uint32_t)std::min<uint64_t>((uint64_t)h->capacity * 3 / 2, 0x7FFFFFFFull) : need;
         cap = std::max(cap, need);
-        float* n32 = nullptr; __nv_bfloat16* n16 = nullptr; float* nerr = nullptr;
+        float* n32 = nullptr; __half* n16 = nullptr; float* nerr = nullptr;
         MSR_CUDA_CHECK(cudaMalloc(&n32, (size_t)cap * h->dim * 4));
         MSR_CUDA_CHECK(cudaMalloc(&n16, (size_t)cap * h->dim * 2));
         MSR_CUDA_CHECK(cudaMalloc(&nerr, (size_t)cap * 4));
@@ -251,9 +259,28 @@ static int dense_search_exact(msr_dense_index* h, uint32_t nq, const float* d_q,
     return MSR_OK;
 }
 
-// ---- mode 2 helpers: tensor-core candidates -> exact fp32 re-score -> certificate ----
+// ---- mode 2: tensor-core pass with fused selection -> exact fp32 re-score of a certified candidate set ----
+//
+// Notation: a(d) = fp16(q).fp16(x_d) accumulated in fp32 by tcgen05 (approximate), e(d) = the fp32 score of mode 1 (exact,
+// fixed order).  |e(d) - a(d)| <= E_q for every doc, with
+//     E_q = ||q - q^||*max||x|| + ||q^||*max||x - x^|| + (fp32 accumulation slack of both passes)        (Cauchy-Schwarz).
+// Let a_k be the k-th largest a(d).  Every doc outside C = {d : a(d) >= a_k - 2 E_q} has e(d) < a_k - E_q, while the k docs
+// with a(d) >= a_k have e(d) >= a_k - E_q: the exact top-k is a subset of C.  So:
+//   P1  theta_q: an ESTIMATE of a_k - 2 E_q from a strided sample of m docs (rank r of the sample, r chosen so that the
+//       sample holds r of the true top-k with probability < 1e-4) -- full-score GEMM on m docs + radix select;
+//   P2  GEMM over all docs with the fused filter epilogue: survivors S = {a(d) >= theta_q} land in per-query buffers;
+//   P3  per query: sort S, read a_k, keep C, and CERTIFY: |S| >= k, no buffer overflow and theta_q <= a_k - 2 E_q
+//       (then S held every member of C).  The certificate is unconditional; only its success rate is statistical.
+//   P4  exact re-score of C (same accumulation order as mode 1), final order (score desc, id asc), FAISS-convention rows.
+// Uncertified queries are re-run by mode 1, so both modes return identical ids and bit-identical scores.
 
-// per query: ||q||_2 and ||q - bf16(q)||_2 (both rounded up a little)
+__device__ __forceinline__ float cert_E(float qn, float qe, const float* __restrict__ stats, uint32_t dim) {
+    const float xn = stats[0], ex = stats[1], qh = qn + qe;
+    const float slack = ((float)dim * 1.1920929e-7f + 9.5367432e-7f) * qh * (xn + ex);
+    return (qe * xn + qh * ex + slack) * 1.0001f;
+}
+
+// per query: ||q||_2 and ||q - fp16(q)||_2 (both rounded up a little)
 __global__ void dense_query_norms_kernel(const float* __restrict__ q, uint32_t nq, uint32_t dim, float* __restrict__ qn,
                                          float* __restrict__ qe) {
     const uint32_t w = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
@@ -261,7 +288,7 @@ __global__ void dense_query_norms_kernel(const float* __restrict__ q, uint32_t n
     const float* s = q + (size_t)w * dim;
     float n2 = 0.f, e2 = 0.f;
     for (uint32_t i = lane; i < dim; i += 32) {
-        const float x = s[i], r = x - __bfloat162float(__float2bfloat16_rn(x));
+        const float x = s[i], r = x - __half2float(__float2half_rn(x));
         n2 = fmaf(x, x, n2);
         e2 = fmaf(r, r, e2);
     }
@@ -273,55 +300,133 @@ __global__ void dense_query_norms_kernel(const float* __restrict__ q, uint32_t n
     if (lane == 0) { qn[w] = sqrtf(n2) * 1.0001f; qe[w] = sqrtf(e2) * 1.0001f; }
 }
 
-// Exact score of candidate r of query q: one warp per (q, r), the SAME accumulation order as dense_ip_exact_kernel
-// (lane-strided fmaf chain, xor-shuffle tree), so both modes return bit-identical scores.
-__global__ void __launch_bounds__(256)
-dense_rescore_kernel(const float* __restrict__ docs, uint32_t dim, int32_t doc_base, const float* __restrict__ queries,
-                     const int32_t* __restrict__ cand, const uint32_t* __restrict__ cnt, uint32_t nq, uint32_t kp,
-                     float* __restrict__ out) {
-    const size_t w = (blockIdx.x * (size_t)blockDim.x + threadIdx.x) >> 5;
-    const uint32_t lane = threadIdx.x & 31;
-    if (w >= (size_t)nq * kp) return;
-    const uint32_t q = (uint32_t)(w / kp), r = (uint32_t)(w - (size_t)q * kp);
-    if (r >= cnt[q]) return;
-    const float* d = docs + (size_t)(cand[w] - doc_base) * dim;
-    const float* y = queries + (size_t)q * dim;
-    float acc = 0.f;
-    if ((dim & 3) == 0) {
-        const float4* d4 = reinterpret_cast<const float4*>(d);
-        const float4* y4 = reinterpret_cast<const float4*>(y);
-        for (uint32_t i = lane; i < dim / 4; i += 32) {
-            const float4 a = __ldg(d4 + i), b = __ldg(y4 + i);
-            acc = fmaf(a.x, b.x, acc); acc = fmaf(a.y, b.y, acc); acc = fmaf(a.z, b.z, acc); acc = fmaf(a.w, b.w, acc);
-        }
-    } else {
-        for (uint32_t i = lane; i < dim; i += 32) acc = fmaf(__ldg(d + i), __ldg(y + i), acc);
-    }
-#pragma unroll
-    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-    if (lane == 0) out[w] = acc;
-}
-
-// flags[q] = 1 when no doc outside the candidate list can reach the exact k-th score:
-//   exact(d) <= approx(d) + E_q  for every doc, with
-//   E_q = ||q - q^||*max||x|| + ||q^||*max||x - x^|| + (fp32 accumulation slack of both passes),
-// and approx(d) <= a_min (the smallest approximate score among the candidates) for every d outside the list.
-__global__ void dense_certify_kernel(const float* __restrict__ ts, const uint32_t* __restrict__ tcnt, const float* __restrict__ fs,
-                                     const float* __restrict__ qn, const float* __restrict__ qe, const float* __restrict__ stats,
-                                     uint32_t nq, uint32_t kp, uint32_t kk, uint32_t n_docs, uint32_t dim,
-                                     uint32_t* __restrict__ flags) {
+// P1 tail: theta_q = (r-th best sampled score) - 2 E_q, or -inf when the sample has fewer than r finite scores
+__global__ void dense_thr_kernel(const float* __restrict__ top, const uint32_t* __restrict__ top_cnt, uint32_t r,
+                                 const float* __restrict__ qn, const float* __restrict__ qe, const float* __restrict__ stats,
+                                 uint32_t nq, uint32_t dim, float* __restrict__ thr) {
     const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
     if (q >= nq) return;
-    const uint32_t c = tcnt[q];
-    bool ok = c >= n_docs;                                       // every doc was re-scored
-    if (!ok && c == kp && kp >= kk) {
-        const float a_min = ts[(size_t)q * kp + kp - 1], e_k = fs[(size_t)q * kk + kk - 1];
-        const float xn = stats[0], ex = stats[1], qh = qn[q] + qe[q];
-        const float slack = ((float)dim * 1.1920929e-7f + 9.5367432e-7f) * qh * (xn + ex);
-        const float E = qe[q] * xn + qh * ex + slack;
-        ok = a_min + E * 1.0001f < e_k;                          // NaN anywhere -> not certified
+    float t = -INFINITY;
+    if (r > 0 && top_cnt[q] >= r) t = top[(size_t)q * r + r - 1] - 2.f * cert_E(qn[q], qe[q], stats, dim);
+    thr[q] = (t == t) ? t : -INFINITY;
+}
+__global__ void fill_f32_kernel(float* __restrict__ p, float v, uint32_t n) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+constexpr int kSelThreads = 256;
+
+// P3: one CTA per query.  Sorts the survivors by (a desc, doc asc), cuts the candidate set C and certifies it.
+__global__ void __launch_bounds__(kSelThreads)
+dense_select_kernel(const uint2* __restrict__ cand, const uint32_t* __restrict__ cnt, uint32_t cap, const float* __restrict__ thr,
+                    const float* __restrict__ qn, const float* __restrict__ qe, const float* __restrict__ stats, uint32_t kk,
+                    uint32_t n_docs, uint32_t dim, int32_t doc_base, int32_t* __restrict__ out_docs,
+                    uint32_t* __restrict__ out_cnt, uint32_t* __restrict__ flags) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
+    __shared__ uint32_t s_nc;
+    const uint32_t q = blockIdx.x, tid = threadIdx.x;
+    const uint32_t n_raw = cnt[q], n = min(n_raw, cap);
+    uint32_t n2 = 2;
+    while (n2 < n) n2 <<= 1;
+    const uint2* mine = cand + (size_t)q * cap;
+    for (uint32_t i = tid; i < n2; i += kSelThreads) {
+        uint64_t key = 0;
+        if (i < n) { const uint2 c = mine[i]; key = make_key(__uint_as_float(c.x), c.y); }
+        buf[i] = key;
     }
-    flags[q] = ok ? 1u : 0u;
+    if (tid == 0) s_nc = 0;
+    bitonic_sort_desc(buf, n2);
+    bool ok = false;
+    uint32_t nc = 0;
+    if (n_raw <= cap) {
+        if (n_raw >= n_docs) {                                  // every doc survived: C = all docs
+            ok = true; nc = n;
+        } else if (n >= kk) {
+            const float a_k = key_score(buf[kk - 1]);
+            const float lim = a_k - 2.f * cert_E(qn[q], qe[q], stats, dim);
+            ok = thr[q] <= lim;                                 // NaN anywhere -> not certified
+            if (ok) {
+                uint32_t c = 0;
+                for (uint32_t i = tid; i < n; i += kSelThreads) c += key_score(buf[i]) >= lim ? 1u : 0u;
+                c = warp_reduce_add(c);
+                if ((tid & 31) == 0 && c) atomicAdd(&s_nc, c);
+                __syncthreads();
+                nc = s_nc;                                      // the list is sorted: C is its first nc entries
+            }
+        }
+    }
+    for (uint32_t i = tid; i < nc; i += kSelThreads) out_docs[(size_t)q * cap + i] = doc_base + (int32_t)key_doc(buf[i]);
+    if (tid == 0) { out_cnt[q] = nc; flags[q] = ok ? 1u : 0u; }
+}
+
+constexpr int kRsThreads = 256;
+constexpr int kRsWarps = kRsThreads / 32;
+constexpr int kRsPer = 4;            // candidates a warp scores together (independent fmaf chains)
+
+// P4a: exact scores of the candidates of one query (CTA = query, query row in shared memory).  Each candidate is scored
+// by one warp in the SAME accumulation order as dense_ip_exact_kernel (lane-strided fmaf chain over float4 elements,
+// xor-shuffle tree), so both modes return bit-identical scores.  dim % 4 == 0.
+__global__ void __launch_bounds__(kRsThreads)
+dense_rescore_kernel(const float* __restrict__ docs, uint32_t dim, int32_t doc_base, const float* __restrict__ queries,
+                     const int32_t* __restrict__ cand, const uint32_t* __restrict__ cnt, uint32_t cap, float* __restrict__ out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float4* qs = reinterpret_cast<float4*>(smem_raw);
+    const uint32_t q = blockIdx.x, n = min(cnt[q], cap), d4n = dim / 4;
+    if (n == 0) return;
+    const float4* y4 = reinterpret_cast<const float4*>(queries + (size_t)q * dim);
+    for (uint32_t i = threadIdx.x; i < d4n; i += kRsThreads) qs[i] = __ldg(y4 + i);
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int32_t* mine = cand + (size_t)q * cap;
+    for (uint32_t r0 = warp * kRsPer; r0 < n; r0 += kRsWarps * kRsPer) {
+        const float4* d4[kRsPer];
+        float acc[kRsPer];
+#pragma unroll
+        for (int j = 0; j < kRsPer; ++j) {
+            const uint32_t r = min(r0 + j, n - 1);              // tail: recompute the last candidate, never stored
+            d4[j] = reinterpret_cast<const float4*>(docs + (size_t)(mine[r] - doc_base) * dim);
+            acc[j] = 0.f;
+        }
+#pragma unroll 2
+        for (uint32_t i = lane; i < d4n; i += 32) {
+            const float4 b = qs[i];
+            float4 a[kRsPer];
+#pragma unroll
+            for (int j = 0; j < kRsPer; ++j) a[j] = __ldg(d4[j] + i);
+#pragma unroll
+            for (int j = 0; j < kRsPer; ++j) {
+                acc[j] = fmaf(a[j].x, b.x, acc[j]); acc[j] = fmaf(a[j].y, b.y, acc[j]);
+                acc[j] = fmaf(a[j].z, b.z, acc[j]); acc[j] = fmaf(a[j].w, b.w, acc[j]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < kRsPer; ++j) {
+#pragma unroll
+            for (int o = 16; o > 0; o >>= 1) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], o);
+            if (lane == 0 && r0 + j < n) out[(size_t)q * cap + r0 + j] = acc[j];
+        }
+    }
+}
+
+// P4b: final order by (exact score desc, id asc) and FAISS-convention output rows (int64 ids, -1 / -FLT_MAX padding, D5)
+__global__ void __launch_bounds__(kSelThreads)
+dense_final_kernel(const float* __restrict__ es, const int32_t* __restrict__ cand, const uint32_t* __restrict__ cnt, uint32_t cap,
+                   uint32_t k, float* __restrict__ s_out, int64_t* __restrict__ id_out) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
+    const uint32_t q = blockIdx.x, tid = threadIdx.x, n = min(cnt[q], cap);
+    uint32_t n2 = 2;
+    while (n2 < n) n2 <<= 1;
+    for (uint32_t i = tid; i < n2; i += kSelThreads)
+        buf[i] = i < n ? make_key(es[(size_t)q * cap + i], (uint32_t)cand[(size_t)q * cap + i]) : 0ull;
+    bitonic_sort_desc(buf, n2);
+    for (uint32_t r = tid; r < k; r += kSelThreads) {
+        const bool ok = r < n;
+        s_out[(size_t)q * k + r] = ok ? key_score(buf[r]) : -3.4028234663852886e38f;
+        id_out[(size_t)q * k + r] = ok ? (int64_t)(int32_t)key_doc(buf[r]) : -1;
+    }
 }
 
 __global__ void gather_rows_kernel(const float* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t n, uint32_t dim,
@@ -351,32 +456,45 @@ static size_t dense_scratch_bytes(const msr_dense_index* h, uint32_t nq, uint32_
 
 // workspace of the tensor-core path for a block of nqb queries
 struct TcLayout {
-    uint32_t nqb, kp, kk;
-    size_t ld, scores_bytes;
-    size_t o_scores, o_q16, o_ts, o_td, o_tc, o_es, o_fs, o_fd, o_fc, o_qn, o_qe, o_flags, o_gq, o_gos, o_goi, o_gidx, total;
+    uint32_t nqb, kk, cap, m, stride, r;
+    size_t ld_m, exact_bytes;
+    size_t o_q16, o_samp, o_ts, o_td, o_tc, o_thr, o_cnt, o_cand, o_cd, o_es, o_ccnt, o_flags, o_qn, o_qe, o_gq, o_gos, o_goi,
+        o_gidx, o_exact, total;
 };
 
 static TcLayout make_tc_layout(const msr_dense_index* h, uint32_t nq, uint32_t k) {
     TcLayout L{};
-    L.kk = std::min(k, h->n_docs);
-    L.kp = std::min<uint32_t>(h->n_docs, std::min<uint32_t>(MSR_MAX_K, std::max<uint32_t>(4 * k, 256u)));
-    L.kp = std::max(L.kp, L.kk);
-    L.ld = align_up(h->n_docs, 4);
-    const size_t row = L.ld * 4;
-    uint32_t nqb = (uint32_t)std::min<size_t>(nq, std::max<size_t>(128, ((size_t)2 << 30) / row / 128 * 128));
+    const uint32_t N = h->n_docs;
+    L.kk = std::min(k, N);
+    uint32_t cap = 2048;
+    while (cap < 3 * L.kk && cap < 8192) cap <<= 1;
+    L.cap = cap;
+    if (N <= cap) {                                              // every doc fits the candidate buffer: no threshold needed
+        L.m = 0; L.stride = 1; L.r = 0;
+    } else {
+        L.m = std::min<uint32_t>(N, std::min<uint32_t>(16384, std::max<uint32_t>(2048, N / 16)));
+        L.stride = N / L.m;
+        const double lam = (double)L.kk * L.m / N;
+        L.r = (uint32_t)std::min<double>(std::ceil(lam + 4.0 * std::sqrt(lam) + 2.0), (double)std::min<uint32_t>(L.m, MSR_MAX_K));
+    }
+    L.ld_m = align_up(std::max<uint32_t>(L.m, 4), 4);
+    const size_t per_q = (size_t)h->dim * 2 + L.ld_m * 4 + (size_t)L.r * 8 + (size_t)cap * 16 + (size_t)h->dim * 4 + (size_t)k * 12 + 64;
+    uint32_t nqb = (uint32_t)std::min<size_t>(nq, std::max<size_t>(128, ((size_t)3 << 30) / per_q / 128 * 128));
     L.nqb = nqb;
-    // the score block doubles as the scratch of the exact pass that re-runs uncertified queries
-    L.scores_bytes = std::max((size_t)nqb * row, dense_scratch_bytes(h, std::min<uint32_t>(nqb, 64), k));
+    L.exact_bytes = dense_scratch_bytes(h, std::min<uint32_t>(nqb, 64), k);
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 256); return at; };
-    L.o_scores = take(L.scores_bytes);
     L.o_q16 = take((size_t)nqb * h->dim * 2);
-    L.o_ts = take((size_t)nqb * L.kp * 4); L.o_td = take((size_t)nqb * L.kp * 4); L.o_tc = take((size_t)nqb * 4);
-    L.o_es = take((size_t)nqb * L.kp * 4);
-    L.o_fs = take((size_t)nqb * L.kk * 4); L.o_fd = take((size_t)nqb * L.kk * 4); L.o_fc = take((size_t)nqb * 4);
-    L.o_qn = take((size_t)nqb * 4); L.o_qe = take((size_t)nqb * 4); L.o_flags = take((size_t)nqb * 4);
+    L.o_samp = take((size_t)nqb * L.ld_m * 4);
+    L.o_ts = take((size_t)nqb * std::max<uint32_t>(L.r, 1) * 4); L.o_td = take((size_t)nqb * std::max<uint32_t>(L.r, 1) * 4);
+    L.o_tc = take((size_t)nqb * 4);
+    L.o_thr = take((size_t)nqb * 4); L.o_cnt = take((size_t)nqb * 4);
+    L.o_cand = take((size_t)nqb * cap * 8); L.o_cd = take((size_t)nqb * cap * 4); L.o_es = take((size_t)nqb * cap * 4);
+    L.o_ccnt = take((size_t)nqb * 4); L.o_flags = take((size_t)nqb * 4);
+    L.o_qn = take((size_t)nqb * 4); L.o_qe = take((size_t)nqb * 4);
     L.o_gq = take((size_t)nqb * h->dim * 4); L.o_gos = take((size_t)nqb * k * 4); L.o_goi = take((size_t)nqb * k * 8);
     L.o_gidx = take((size_t)nqb * 4);
+    L.o_exact = take(L.exact_bytes);
     L.total = o;
     return L;
 }
@@ -386,44 +504,67 @@ static TcLayout make_tc_layout(const msr_dense_index* h, uint32_t nq, uint32_t k
 static int dense_search_tc(msr_dense_index* h, uint32_t nq, const float* d_q, uint32_t k, float* d_os, int64_t* d_oi,
                            unsigned char* base, const TcLayout& L, cudaStream_t s, uint32_t* n_fallback) {
     std::vector<uint32_t> flags, fail;
+    static bool attr_set = false;
+    if (!attr_set) {
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8));
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_final_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8));
+        attr_set = true;
+    }
     for (uint32_t q0 = 0; q0 < nq; q0 += L.nqb) {
         const uint32_t n = std::min(L.nqb, nq - q0);
         const float* q = d_q + (size_t)q0 * h->dim;
-        float* scores = (float*)(base + L.o_scores);
-        __nv_bfloat16* q16 = (__nv_bfloat16*)(base + L.o_q16);
+        __half* q16 = (__half*)(base + L.o_q16);
+        float* samp = (float*)(base + L.o_samp);
         float* ts = (float*)(base + L.o_ts); int32_t* td = (int32_t*)(base + L.o_td); uint32_t* tcn = (uint32_t*)(base + L.o_tc);
-        float* es = (float*)(base + L.o_es);
-        float* fs = (float*)(base + L.o_fs); int32_t* fd = (int32_t*)(base + L.o_fd); uint32_t* fc = (uint32_t*)(base + L.o_fc);
-        float* qn = (float*)(base + L.o_qn); float* qe = (float*)(base + L.o_qe); uint32_t* d_flags = (uint32_t*)(base + L.o_flags);
-        // 1. approximate scores on the tensor cores
+        float* thr = (float*)(base + L.o_thr); uint32_t* cnt = (uint32_t*)(base + L.o_cnt);
+        uint2* cand = (uint2*)(base + L.o_cand); int32_t* cd = (int32_t*)(base + L.o_cd); float* es = (float*)(base + L.o_es);
+        uint32_t* ccnt = (uint32_t*)(base + L.o_ccnt); uint32_t* d_flags = (uint32_t*)(base + L.o_flags);
+        float* qn = (float*)(base + L.o_qn); float* qe = (float*)(base + L.o_qe);
         const size_t ne = (size_t)n * h->dim;
-        tc::to_bf16_kernel<<<(unsigned)std::min<size_t>((ne + 255) / 256, 148 * 16), 256, 0, s>>>(q, q16, ne);
+        tc::to_f16_kernel<<<(unsigned)std::min<size_t>((ne + 255) / 256, 148 * 16), 256, 0, s>>>(q, q16, ne);
         dense_query_norms_kernel<<<(n + 7) / 8, 256, 0, s>>>(q, n, h->dim, qn, qe);
         count_launch(2);
-        int rc = tc::dense_tc_scores_launch(q16, n, h->v16, h->n_docs, h->dim, scores, L.ld, s);
-        if (rc) return rc;
-        // 2. k' best by approximate score, 3. exact fp32 re-score, 4. final order (score desc, id asc)
-        rc = topk_rows_launch(n, h->n_docs, scores, L.ld, L.kp, h->doc_base, ts, td, tcn, s);
-        if (rc) return rc;
-        const size_t warps = (size_t)n * L.kp;
-        dense_rescore_kernel<<<(unsigned)((warps + 7) / 8), 256, 0, s>>>(h->v32, h->dim, h->doc_base, q, td, tcn, n, L.kp, es);
+        MSR_CUDA_CHECK(cudaMemsetAsync(cnt, 0, (size_t)n * 4, s));
+        int rc;
+        // P1: threshold from the strided sample
+        if (L.m) {
+            rc = tc::dense_tc_scores_launch(q16, n, h->v16, L.m, h->dim, (uint64_t)L.stride * h->dim, samp, L.ld_m, s);
+            if (rc) return rc;
+            rc = topk_rows_launch(n, L.m, samp, L.ld_m, L.r, 0, ts, td, tcn, s);
+            if (rc) return rc;
+            dense_thr_kernel<<<(n + 255) / 256, 256, 0, s>>>(ts, tcn, L.r, qn, qe, h->stats, n, h->dim, thr);
+        } else {
+            fill_f32_kernel<<<(n + 255) / 256, 256, 0, s>>>(thr, -INFINITY, n);
+        }
         count_launch();
-        MSR_CUDA_CHECK(cudaGetLastError());
-        rc = msr_topk_merge(h->device, 1, n, L.kp, es, td, tcn, L.kk, fs, fd, fc, (void*)s);
+        // P2: all docs, fused filter epilogue
+        if (h->profiling) MSR_CUDA_CHECK(cudaEventRecord(h->ev[0], s));
+        rc = tc::dense_tc_filter_launch(q16, n, h->v16, h->n_docs, h->dim, thr, cnt, cand, L.cap, s);
         if (rc) return rc;
-        // 5. certificate, FAISS-convention output
-        dense_certify_kernel<<<(n + 255) / 256, 256, 0, s>>>(ts, tcn, fs, qn, qe, h->stats, n, L.kp, L.kk, h->n_docs, h->dim, d_flags);
-        dense_finish_kernel<<<(unsigned)(((size_t)n * k + 255) / 256), 256, 0, s>>>(fs, fd, fc, n, L.kk, k, d_os + (size_t)q0 * k,
-                                                                                   d_oi + (size_t)q0 * k);
-        count_launch(2);
+        if (h->profiling) MSR_CUDA_CHECK(cudaEventRecord(h->ev[1], s));
+        // P3: candidate set + certificate, P4: exact re-score + final order
+        dense_select_kernel<<<n, kSelThreads, (size_t)L.cap * 8, s>>>(cand, cnt, L.cap, thr, qn, qe, h->stats, L.kk, h->n_docs,
+                                                                      h->dim, h->doc_base, cd, ccnt, d_flags);
+        if (h->profiling) MSR_CUDA_CHECK(cudaEventRecord(h->ev[2], s));
+        dense_rescore_kernel<<<n, kRsThreads, (size_t)h->dim * 4, s>>>(h->v32, h->dim, h->doc_base, q, cd, ccnt, L.cap, es);
+        if (h->profiling) MSR_CUDA_CHECK(cudaEventRecord(h->ev[3], s));
+        dense_final_kernel<<<n, kSelThreads, (size_t)L.cap * 8, s>>>(es, cd, ccnt, L.cap, k, d_os + (size_t)q0 * k,
+                                                                     d_oi + (size_t)q0 * k);
+        count_launch(3);
         MSR_CUDA_CHECK(cudaGetLastError());
         flags.resize(n);
         MSR_CUDA_CHECK(cudaMemcpyAsync(flags.data(), d_flags, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
         MSR_CUDA_CHECK(cudaStreamSynchronize(s));
+        if (h->profiling) {
+            float a = 0, b = 0;
+            MSR_CUDA_CHECK(cudaEventElapsedTime(&a, h->ev[0], h->ev[1]));
+            MSR_CUDA_CHECK(cudaEventElapsedTime(&b, h->ev[2], h->ev[3]));
+            h->prof_tc_ms += a; h->prof_rescore_ms += b; h->prof_launches += 1;
+        }
         fail.clear();
         for (uint32_t i = 0; i < n; ++i) if (!flags[i]) fail.push_back(i);
         if (fail.empty()) continue;
-        // 6. uncertified queries: exact pass (still on the GPU), results scattered over the tensor-core ones
+        // uncertified queries: exact pass (still on the GPU), results scattered over the tensor-core ones
         *n_fallback += (uint32_t)fail.size();
         uint32_t* gidx = (uint32_t*)(base + L.o_gidx);
         float* gq = (float*)(base + L.o_gq); float* gos = (float*)(base + L.o_gos); int64_t* goi = (int64_t*)(base + L.o_goi);
@@ -431,7 +572,7 @@ static int dense_search_tc(msr_dense_index* h, uint32_t nq, const float* d_q, ui
         const uint32_t nf = (uint32_t)fail.size();
         gather_rows_kernel<<<nf, 256, 0, s>>>(q, gidx, nf, h->dim, gq);
         count_launch();
-        rc = dense_search_exact(h, nf, gq, k, gos, goi, base + L.o_scores, L.scores_bytes, s);
+        rc = dense_search_exact(h, nf, gq, k, gos, goi, base + L.o_exact, L.exact_bytes, s);
         if (rc) return rc;
         scatter_results_kernel<<<nf, 128, 0, s>>>(gos, goi, gidx, nf, k, d_os + (size_t)q0 * k, d_oi + (size_t)q0 * k);
         count_launch();
@@ -455,7 +596,7 @@ extern "C" int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* qu
     int rc = use_device(h->device);
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
-    bool use_tc = mode == 2 || (mode == 0 && nq >= 16 && h->n_docs >= 256);
+    bool use_tc = mode == 2 || (mode == 0 && nq >= 16 && h->n_docs >= 4096);
     if (use_tc && h->dim % 8 != 0) {
         MSR_REQUIRE(mode != 2, "msr_dense_search: mode 2 needs dim %% 8 == 0 (TMA row pitch), dim is %u", h->dim);
         use_tc = false;
@@ -495,7 +636,7 @@ extern "C" int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* qu
 
 
 // ---------------------------------------------------------------------------------------------------------
-// tensor-core pass on its own (tests, bench.py --dense, ncu): scores[nq, n_docs] = bf16(Q) . bf16(X)^T, fp32 out
+// tensor-core pass on its own (tests, bench.py --dense, ncu): scores[nq, n_docs] = fp16(Q) . fp16(X)^T, fp32 out
 // ---------------------------------------------------------------------------------------------------------
 extern "C" int msr_dense_tc_scores(msr_dense_index* h, uint32_t nq, const float* queries, float* out_scores, size_t ld,
                                    void* stream) {
@@ -507,12 +648,26 @@ extern "C" int msr_dense_tc_scores(msr_dense_index* h, uint32_t nq, const float*
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
     MSR_CUDA_CHECK(h->ws.reserve(align_up((size_t)nq * h->dim * 2, 256), s));
-    __nv_bfloat16* q16 = (__nv_bfloat16*)h->ws.p;
+    __half* q16 = (__half*)h->ws.p;
     const size_t n = (size_t)nq * h->dim;
-    tc::to_bf16_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 148 * 16), 256, 0, s>>>(queries, q16, n);
+    tc::to_f16_kernel<<<(unsigned)std::min<size_t>((n + 255) / 256, 148 * 16), 256, 0, s>>>(queries, q16, n);
     count_launch();
     MSR_CUDA_CHECK(cudaGetLastError());
-    return tc::dense_tc_scores_launch(q16, nq, h->v16, h->n_docs, h->dim, out_scores, ld, s);
+    return tc::dense_tc_scores_launch(q16, nq, h->v16, h->n_docs, h->dim, h->dim, out_scores, ld, s);
+}
+
+extern "C" int msr_dense_profile(msr_dense_index* h, int enable, double* tc_ms, double* rescore_ms, uint64_t* launches) {
+    MSR_REQUIRE(h, "msr_dense_profile: NULL handle");
+    int rc = use_device(h->device);
+    if (rc) return rc;
+    if (tc_ms) *tc_ms = h->prof_tc_ms;
+    if (rescore_ms) *rescore_ms = h->prof_rescore_ms;
+    if (launches) *launches = h->prof_launches;
+    h->prof_tc_ms = h->prof_rescore_ms = 0; h->prof_launches = 0;
+    if (enable && !h->ev[0])
+        for (cudaEvent_t& e : h->ev) MSR_CUDA_CHECK(cudaEventCreate(&e));
+    h->profiling = enable != 0;
+    return MSR_OK;
 }
 
 extern "C" int msr_dense_last_fallback(const msr_dense_index* h, uint32_t* n) {

@@ -1,10 +1,17 @@
 // dense_tc.cuh -- kernel (c), tensor-core pass: approximate inner products of a query block against the whole
-// flat index with tcgen05.mma (bf16 x bf16 -> fp32 in TMEM), operands staged by TMA.  sm_100a only.
+// flat index with tcgen05.mma (fp16 x fp16 -> fp32 in TMEM), operands staged by TMA.  sm_100a only.
 //
 // Replaces the cuBLAS HGEMM that faiss-gpu runs behind `--use_gpu` (reference src/search.py:254-270,
-// GpuClonerOptions.useFloat16) -- here as one persistent, warp-specialised kernel:
+// GpuClonerOptions.useFloat16 -- fp16 storage is the reference's own choice) -- here as one persistent,
+// warp-specialised kernel:
 //
-//   scores[q, d] = sum_h bf16(Q[q,h]) * bf16(X[d,h])            (fp32 accumulate)
+//   scores[q, d] = sum_h fp16(Q[q,h]) * fp16(X[d,h])            (fp32 accumulate)
+//
+// Two epilogues (template FILTER):
+//   false  the 128 x 256 accumulator is written out as score rows (sample pass, tests, msr_dense_tc_scores);
+//   true   FUSED SELECTION: each epilogue thread owns one query row of the tile, compares its 256 scores with the
+//          query's threshold thr[q] and appends the few survivors (score bits, doc) to the query's candidate buffer
+//          (one atomicAdd per 32-column chunk that has any).  The nq x N score matrix never exists in HBM.
 //
 //   tile      = 128 queries (UMMA M, TMEM lanes) x 256 docs (UMMA N, TMEM columns), K walked in 64-element slabs
 //   warp 0    = TMA producer: one elected lane issues cp.async.bulk.tensor loads of the Q slab [128 x 64] and the
@@ -18,7 +25,7 @@
 //               the CTAs running together share one X slab through L2 and X leaves HBM once per pass.
 #pragma once
 #include <cuda.h>
-#include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include "common.cuh"
 
@@ -27,7 +34,7 @@ namespace tc {
 
 constexpr int BM = 128;            // queries per tile
 constexpr int BN = 256;            // docs per tile
-constexpr int BK = 64;             // bf16 elements per K slab = one 128-byte swizzle row
+constexpr int BK = 64;             // fp16 elements per K slab = one 128-byte swizzle row
 constexpr int UMMA_K = 16;
 constexpr int STAGES = 4;
 constexpr int THREADS = 192;
@@ -37,8 +44,9 @@ constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr uint32_t TMEM_COLS = 512;            // 2 accumulators x 256 columns
 constexpr size_t SMEM_BYTES = 1024 + (size_t)STAGES * STAGE_BYTES + 256;
 
-// instruction descriptor (cute::UMMA::InstrDescriptor layout): fp32 accumulate, A/B = bf16, both K-major, M=128, N=256
-constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+// instruction descriptor (cute::UMMA::InstrDescriptor layout): fp32 accumulate (bit 4), A/B format 0 = fp16 (bits 7-9,
+// 10-12), both K-major, N >> 3 at bit 17, M >> 4 at bit 24
+constexpr uint32_t IDESC = (1u << 4) | ((uint32_t)(BN >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -77,7 +85,7 @@ __device__ __forceinline__ void tcgen05_fence_after() { asm volatile("tcgen05.fe
 __device__ __forceinline__ uint64_t umma_desc_k_sw128(uint32_t saddr) {
     return (uint64_t)((saddr & 0x3FFFFu) >> 4) | (1ull << 16) | ((uint64_t)(1024 >> 4) << 32) | (1ull << 46) | (2ull << 61);
 }
-__device__ __forceinline__ void umma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t accumulate) {
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t accumulate) {
     asm volatile(
         "{\n\t"
         ".reg .pred p;\n\t"
@@ -103,10 +111,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
 
 struct TcParams {
     uint32_t nq, n_docs, n_qblk, n_dblk, n_kslab;
-    float* scores;                 // [nq][ld] approximate inner products
-    size_t ld;                     // row pitch in floats (multiple of 4)
+    float* scores;                 // FILTER = false: [nq][ld] approximate inner products
+    size_t ld;                     //                 row pitch in floats (multiple of 4)
+    const float* thr;              // FILTER = true:  [nq] keep docs with score >= thr[q]
+    uint32_t* cnt;                 //                 [nq] survivors appended so far (may exceed cap = overflow)
+    uint2* cand;                   //                 [nq][cap] (score bits, local doc row)
+    uint32_t cap;
 };
 
+template <bool FILTER>
 __global__ void __launch_bounds__(THREADS, 1)
 dense_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant__ CUtensorMap map_x, const TcParams P) {
     extern __shared__ unsigned char smem_raw[];
@@ -168,7 +181,7 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
                     const uint64_t b_desc = umma_desc_k_sw128(base + stage * STAGE_BYTES + A_BYTES);
 #pragma unroll
                     for (uint32_t k = 0; k < BK / UMMA_K; ++k)  // +32 bytes along K inside the swizzle atom
-                        umma_bf16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, (ks | k) != 0 ? 1u : 0u);
+                        umma_f16(d_tmem, a_desc + 2 * k, b_desc + 2 * k, (ks | k) != 0 ? 1u : 0u);
                     umma_commit(empty(stage));                  // slot free once these MMAs retire
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
@@ -185,6 +198,31 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
             const uint32_t q = (t % P.n_qblk) * BM + row, d0 = (t / P.n_qblk) * BN;
             mbar_wait(tfull(acc), acc_phase);
             tcgen05_fence_after();
+            if constexpr (FILTER) {
+                // NaN never passes (>= is false); rows past nq and zero-filled doc rows past n_docs are masked out
+                const float th = q < P.nq ? __ldg(P.thr + q) : INFINITY;
+                uint2* mine = P.cand + (size_t)q * P.cap;
+#pragma unroll 1
+                for (uint32_t c = 0; c < BN / 32; ++c) {
+                    uint32_t v[32];
+                    tmem_ld32(tmem_base + ((quarter * 32u) << 16) + acc * BN + c * 32, v);
+                    const uint32_t dc = d0 + c * 32;
+                    uint32_t mask = 0;
+#pragma unroll
+                    for (uint32_t j = 0; j < 32; ++j) mask |= (__uint_as_float(v[j]) >= th ? 1u : 0u) << j;
+                    if (dc + 32 > P.n_docs) mask &= dc < P.n_docs ? ((1u << (P.n_docs - dc)) - 1u) : 0u;
+                    if (mask && q < P.nq) {
+                        const uint32_t at = atomicAdd(P.cnt + q, (uint32_t)__popc(mask));
+#pragma unroll
+                        for (uint32_t j = 0; j < 32; ++j) {
+                            if ((mask >> j) & 1u) {
+                                const uint32_t pos = at + __popc(mask & ((1u << j) - 1u));
+                                if (pos < P.cap) mine[pos] = make_uint2(v[j], dc + j);
+                            }
+                        }
+                    }
+                }
+            } else {
             float* dst = P.scores + (size_t)q * P.ld + d0;
 #pragma unroll 1
             for (uint32_t c = 0; c < BN / 32; ++c) {
@@ -206,6 +244,7 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
                     }
                 }
             }
+            }
             tcgen05_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(tempty(acc));
@@ -219,18 +258,19 @@ dense_tc_kernel(const __grid_constant__ CUtensorMap map_q, const __grid_constant
     }
 }
 
-// fp32 -> bf16 copy of the query block (row-major, same pitch)
-__global__ void to_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, size_t n) {
+// fp32 -> fp16 copy of the query block (row-major, same pitch)
+__global__ void to_f16_kernel(const float* __restrict__ src, __half* __restrict__ dst, size_t n) {
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
-        dst[i] = __float2bfloat16_rn(src[i]);
+        dst[i] = __float2half_rn(src[i]);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-// bf16 [rows, dim] row-major -> tensor map with a [box_rows x 64] box, 128-byte swizzle, zero fill out of bounds
-static int make_map_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t dim, uint32_t box_rows) {
+// fp16 [rows, dim] with a row pitch of `pitch` elements -> tensor map with a [box_rows x 64] box, 128-byte swizzle, zero
+// fill out of bounds.  pitch = dim is the plain matrix; pitch = s * dim addresses every s-th row (the strided sample).
+static int make_map_f16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64_t dim, uint64_t pitch, uint32_t box_rows) {
     static EncodeTiledFn fn = nullptr;
     if (!fn) {
         void* p = nullptr;
@@ -243,10 +283,10 @@ static int make_map_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint6
         fn = (EncodeTiledFn)p;
     }
     const cuuint64_t gdim[2] = {dim, rows};
-    const cuuint64_t gstride[1] = {dim * 2};
+    const cuuint64_t gstride[1] = {pitch * 2};
     const cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
     const cuuint32_t estr[2] = {1, 1};
-    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
+    CUresult r = fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(ptr), gdim, gstride, box, estr,
                     CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                     CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) {
@@ -257,29 +297,55 @@ static int make_map_bf16(CUtensorMap* map, const void* ptr, uint64_t rows, uint6
     return MSR_OK;
 }
 
-// scores[nq][ld] = bf16(Q) . bf16(X)^T on the tensor cores.  q16 [nq,dim] and x16 [n_docs,dim] are bf16, dim % 8 == 0.
-static int dense_tc_scores_launch(const __nv_bfloat16* q16, uint32_t nq, const __nv_bfloat16* x16, uint32_t n_docs, uint32_t dim,
-                                  float* scores, size_t ld, cudaStream_t s) {
-    CUtensorMap mq, mx;
-    int rc = make_map_bf16(&mq, q16, nq, dim, BM);
-    if (rc) return rc;
-    rc = make_map_bf16(&mx, x16, n_docs, dim, BN);
-    if (rc) return rc;
+static int tc_launch_common(const CUtensorMap& mq, const CUtensorMap& mx, TcParams& P, uint32_t nq, uint32_t n_docs,
+                            uint32_t dim, bool filter, cudaStream_t s) {
     static bool attr_set = false;
     if (!attr_set) {
-        MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
         attr_set = true;
     }
-    TcParams P;
     P.nq = nq; P.n_docs = n_docs; P.n_qblk = (nq + BM - 1) / BM; P.n_dblk = (n_docs + BN - 1) / BN;
-    P.n_kslab = (dim + BK - 1) / BK; P.scores = scores; P.ld = ld;
-    int sms = 148;
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0);
-    const uint32_t total = P.n_qblk * P.n_dblk;
-    dense_tc_kernel<<<std::min<uint32_t>(total, (uint32_t)sms), THREADS, SMEM_BYTES, s>>>(mq, mx, P);
+    P.n_kslab = (dim + BK - 1) / BK;
+    int sms = 148, dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    const uint64_t total = (uint64_t)P.n_qblk * P.n_dblk;
+    if (total >= (1ull << 32)) { set_error("dense tensor-core pass: %llu tiles", (unsigned long long)total); return MSR_ERR_INVALID; }
+    const uint32_t grid = (uint32_t)std::min<uint64_t>(total, (uint64_t)sms);
+    if (filter) dense_tc_kernel<true><<<grid, THREADS, SMEM_BYTES, s>>>(mq, mx, P);
+    else dense_tc_kernel<false><<<grid, THREADS, SMEM_BYTES, s>>>(mq, mx, P);
     count_launch();
     MSR_CUDA_CHECK(cudaGetLastError());
     return MSR_OK;
+}
+
+// scores[nq][ld] = fp16(Q) . fp16(X)^T on the tensor cores.  q16 [nq,dim] fp16; x16 = n_docs rows of fp16 at a pitch of
+// x_pitch elements (dim = every row, s * dim = every s-th row); dim % 8 == 0.
+static int dense_tc_scores_launch(const __half* q16, uint32_t nq, const __half* x16, uint32_t n_docs, uint32_t dim,
+                                  uint64_t x_pitch, float* scores, size_t ld, cudaStream_t s) {
+    CUtensorMap mq, mx;
+    int rc = make_map_f16(&mq, q16, nq, dim, dim, BM);
+    if (rc) return rc;
+    rc = make_map_f16(&mx, x16, n_docs, dim, x_pitch, BN);
+    if (rc) return rc;
+    TcParams P{};
+    P.scores = scores; P.ld = ld;
+    return tc_launch_common(mq, mx, P, nq, n_docs, dim, false, s);
+}
+
+// Fused selection: survivors {d : fp16(Q[q]) . fp16(X[d]) >= thr[q]} appended to cand[q][0..cap), cnt[q] += survivors.
+// cnt must be zeroed by the caller.
+static int dense_tc_filter_launch(const __half* q16, uint32_t nq, const __half* x16, uint32_t n_docs, uint32_t dim,
+                                  const float* thr, uint32_t* cnt, uint2* cand, uint32_t cap, cudaStream_t s) {
+    CUtensorMap mq, mx;
+    int rc = make_map_f16(&mq, q16, nq, dim, dim, BM);
+    if (rc) return rc;
+    rc = make_map_f16(&mx, x16, n_docs, dim, dim, BN);
+    if (rc) return rc;
+    TcParams P{};
+    P.thr = thr; P.cnt = cnt; P.cand = cand; P.cap = cap;
+    return tc_launch_common(mq, mx, P, nq, n_docs, dim, true, s);
 }
 
 }  // namespace tc

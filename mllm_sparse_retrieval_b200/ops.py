@@ -195,8 +195,15 @@ class DenseIndex:
         check(_lib.load().msr_dense_last_fallback(self._h, ctypes.byref(n)))
         return int(n.value)
 
+    def profile(self, enable=True):
+        """(fused tcgen05 pass ms, re-score ms, query blocks) accumulated since the last call; then switch timing on/off."""
+        a, b, n = ctypes.c_double(), ctypes.c_double(), ctypes.c_uint64()
+        with torch.cuda.device(self.device):
+            check(_lib.load().msr_dense_profile(self._h, int(bool(enable)), ctypes.byref(a), ctypes.byref(b), ctypes.byref(n)))
+        return a.value, b.value, int(n.value)
+
     def tc_scores(self, queries):
-        """Tensor-core pass alone: CUDA fp32 queries [nq,dim] -> approximate scores fp32 [nq, n_docs] (bf16 inputs)."""
+        """Tensor-core pass alone: CUDA fp32 queries [nq,dim] -> approximate scores fp32 [nq, n_docs] (fp16 inputs)."""
         q = queries.to(torch.float32).contiguous()
         n = self.ntotal
         ld = (n + 3) // 4 * 4

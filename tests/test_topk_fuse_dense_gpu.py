@@ -115,9 +115,10 @@ def test_dense_exact_matches_oracle(oracle, lib_built, n_docs, dim, nq, k):
 
 
 @pytest.mark.parametrize("n_docs,dim,nq,k", [(5000, 4096, 200, 100), (25000, 1024, 300, 100), (777, 256, 130, 1000),
-                                              (3000, 3584, 64, 10), (2048, 64, 129, 5)])
+                                              (3000, 3584, 64, 10), (2048, 64, 129, 5), (30000, 512, 256, 1000),
+                                              (70000, 256, 140, 10), (9000, 128, 33, 4096)])
 def test_dense_tensor_core_mode_equals_exact_mode(oracle, lib_built, n_docs, dim, nq, k):
-    """Mode 2 (tcgen05 bf16 pass + fp32 re-score + certificate) returns the ids AND the bit pattern of the scores of
+    """Mode 2 (tcgen05 fp16 pass with fused threshold selection + certified fp32 re-score) returns the ids AND the bit pattern of the scores of
     mode 1; both match the float64 oracle (ids identical up to fp32-resolution ties, scores within 1e-3 relative)."""
     from mllm_sparse_retrieval_b200 import synth
     from mllm_sparse_retrieval_b200.ops import DenseIndex
@@ -143,7 +144,7 @@ def test_dense_tensor_core_mode_equals_exact_mode(oracle, lib_built, n_docs, dim
 
 
 def test_dense_certificate_falls_back_on_near_ties(oracle, lib_built):
-    """Thousands of near-duplicate docs: bf16 cannot separate them, the certificate must fail and the exact pass
+    """Thousands of near-duplicate docs: fp16 cannot separate them, the certificate must fail and the exact pass
     must take over -- results still equal mode 1."""
     from mllm_sparse_retrieval_b200.ops import DenseIndex
     g = torch.Generator(device="cuda"); g.manual_seed(5)
@@ -162,8 +163,45 @@ def test_dense_certificate_falls_back_on_near_ties(oracle, lib_built):
     torch.testing.assert_close(s2, s1, rtol=0, atol=0)
 
 
-def test_tensor_core_scores_match_bf16_matmul(lib_built):
-    """The tcgen05 pass alone against a torch fp32 matmul of the bf16-rounded operands (tolerance: fp32 accumulation)."""
+def test_dense_clustered_docs_partial_fallback(oracle, lib_built):
+    """Caption-group structure (5 near-identical docs per group, groups contiguous, so the strided sample is biased)
+    plus a few queries that sit on a dense cluster: whatever mix of certified / fallback queries results, mode 2 must
+    equal mode 1 bit for bit, and the bulk of the batch must stay on the tensor-core path."""
+    from mllm_sparse_retrieval_b200.ops import DenseIndex
+    g = torch.Generator(device="cuda"); g.manual_seed(11)
+    dim, groups, nq, k = 1024, 6000, 300, 100
+    cent = torch.randn(groups, dim, generator=g, device="cuda")
+    docs = cent.repeat_interleave(5, dim=0) + 0.3 * torch.randn(groups * 5, dim, generator=g, device="cuda")
+    docs[:2000] = cent[0][None, :] + 1e-5 * torch.randn(2000, dim, generator=g, device="cuda")      # one dense cluster
+    docs = docs / docs.norm(dim=1, keepdim=True)
+    q = cent[torch.randint(0, groups, (nq,), generator=g, device="cuda")] + 0.5 * torch.randn(nq, dim, generator=g, device="cuda")
+    q[:7] = cent[0][None, :] + 0.2 * torch.randn(7, dim, generator=g, device="cuda")               # land on the cluster
+    q = q / q.norm(dim=1, keepdim=True)
+    idx = DenseIndex(dim); idx.add(docs)
+    s1, i1 = idx.search(q, k, mode=1)
+    s2, i2 = idx.search(q, k, mode=2)
+    assert 1 <= idx.last_fallback <= nq // 4, idx.last_fallback
+    torch.testing.assert_close(i2, i1, rtol=0, atol=0)
+    torch.testing.assert_close(s2, s1, rtol=0, atol=0)
+
+
+def test_dense_fp16_overflow_is_never_certified(lib_built):
+    """Vectors outside the fp16 range become inf in the tensor-core copy: the error bound is inf, nothing is certified
+    and the exact pass answers every query."""
+    from mllm_sparse_retrieval_b200.ops import DenseIndex
+    g = torch.Generator(device="cuda"); g.manual_seed(12)
+    docs = torch.randn(5000, 256, generator=g, device="cuda") * 1e5
+    q = torch.randn(40, 256, generator=g, device="cuda")
+    idx = DenseIndex(256); idx.add(docs)
+    s1, i1 = idx.search(q, 10, mode=1)
+    s2, i2 = idx.search(q, 10, mode=2)
+    assert idx.last_fallback == 40
+    torch.testing.assert_close(i2, i1, rtol=0, atol=0)
+    torch.testing.assert_close(s2, s1, rtol=0, atol=0)
+
+
+def test_tensor_core_scores_match_fp16_matmul(lib_built):
+    """The tcgen05 pass alone against a torch fp32 matmul of the fp16-rounded operands (tolerance: fp32 accumulation)."""
     from mllm_sparse_retrieval_b200.ops import DenseIndex
     g = torch.Generator(device="cuda"); g.manual_seed(3)
     for n, nq, dim in [(256, 128, 64), (1000, 37, 128), (4099, 257, 4096)]:
@@ -171,7 +209,7 @@ def test_tensor_core_scores_match_bf16_matmul(lib_built):
         q = torch.randn(nq, dim, generator=g, device="cuda"); q = q / q.norm(dim=1, keepdim=True)
         idx = DenseIndex(dim); idx.add(x)
         got = idx.tc_scores(q)
-        ref = q.bfloat16().float() @ x.bfloat16().float().T
+        ref = q.half().float() @ x.half().float().T
         torch.testing.assert_close(got, ref, rtol=0, atol=2e-6)
 
 
