@@ -48,13 +48,17 @@ def parse_args():
     ap.add_argument("--tile-docs", type=int, default=0)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--chunks", type=int, default=4, help="query chunks of the pipelined multi-GPU exchange")
     ap.add_argument("--check", type=int, default=32, help="queries verified against the oracle after the run")
-    ap.add_argument("--workload", default="sparse", choices=["sparse", "dense", "hybrid"],
+    ap.add_argument("--workload", default="sparse", choices=["sparse", "dense", "hybrid", "config5"],
                     help="sparse = the headline metric (default); dense / hybrid = the other kernels of the path (bench_extra.py)")
     ap.add_argument("--dense-docs", type=int, default=25000)
     ap.add_argument("--dense-nq", type=int, default=5000)
     ap.add_argument("--dense-dim", type=int, default=4096)
     ap.add_argument("--hybrid-nq", type=int, default=25000)
+    ap.add_argument("--c5-docs-per-gpu", type=int, default=1_250_000, help="config5: docs of each index per GPU (x8 = 10 M)")
+    ap.add_argument("--c5-dense-nq", type=int, default=4096)
+    ap.add_argument("--c5-dense-batch", type=int, default=1024)
     ap.add_argument("--depth", type=int, default=1000)
     ap.add_argument("--alpha", type=float, default=0.5)
     return ap.parse_args()
@@ -64,7 +68,7 @@ def workload_config(a, world):
     return {"workload": f"synthetic {a.n_docs}-doc vocab-sparse index (Zipf s=1, V={a.vocab}, {a.nnz_per_doc} nnz/doc), "
                         f"{a.nq} queries x {a.q_len} terms, top-{a.k} (BASELINE.json configs[3])",
             "n_docs": a.n_docs, "nq": a.nq, "q_len": a.q_len, "k": a.k, "vocab": a.vocab, "seed": a.seed,
-            "sharding": f"doc-range x{world} + NCCL all-gather merge" if world > 1 else "single GPU",
+            "sharding": f"doc-range x{world} + NCCL all-gather merge, {a.chunks}-chunk pipelined exchange" if world > 1 else "single GPU",
             "l2": "index (4 B/posting physical, >= 512 MB) is larger than the 126 MB L2; no explicit flush"}
 
 
@@ -212,7 +216,7 @@ def run_ours(a, rank, world, local_rank):
     import torch
     import torch.distributed as dist
     from mllm_sparse_retrieval_b200 import synth
-    from mllm_sparse_retrieval_b200.ops import SparseIndex, kernel_launches, topk_merge
+    from mllm_sparse_retrieval_b200.ops import SparseIndex, kernel_launches
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback (use --impl reference for the CPU arm)")
@@ -236,38 +240,39 @@ def run_ours(a, rank, world, local_rank):
     postings, kept = idx.query_work(qs.indptr, qs.terms, qs.weights)
     nq, k = qs.nq, a.k
 
-    out = (torch.empty((nq, k), dtype=torch.float32, device=dev), torch.empty((nq, k), dtype=torch.int32, device=dev),
-           torch.empty((nq,), dtype=torch.int32, device=dev))
-    if world > 1:
-        g_s = torch.empty((world, nq, k), dtype=torch.float32, device=dev)
-        g_d = torch.empty((world, nq, k), dtype=torch.int32, device=dev)
-        g_c = torch.empty((world, nq), dtype=torch.int32, device=dev)
+    # doc-sharded exchange: chunk i's all-gather + merge run on a side stream while chunk i+1 is scored
+    from mllm_sparse_retrieval_b200.sharded import PipelinedExchange
+    ex = PipelinedExchange(nq, k, dev, world, chunks=a.chunks if world > 1 else 1)
+    q_chunks = [qs.slice(lo, hi) for lo, hi in ex.chunks()]
 
     def step_device():
-        idx.search(qs.indptr, qs.terms, qs.weights, k, out=out)
-        if world == 1:
-            return out
-        dist.all_gather_into_tensor(g_s, out[0])
-        dist.all_gather_into_tensor(g_d, out[1])
-        dist.all_gather_into_tensor(g_c, out[2])
-        return topk_merge(g_s, g_d, g_c, k)
+        return ex.run(lambda i, lo, hi, o: idx.search(q_chunks[i].indptr, q_chunks[i].terms, q_chunks[i].weights, k, out=o))
 
-    # e2e: pinned host buffers through the MSR_HOST path of the C ABI
+    # e2e: pinned host buffers.  1 GPU: the MSR_HOST path of the C ABI.  N GPUs: every rank copies the pinned query CSR
+    # to its GPU, scores its shard, exchanges on the device, and rank 0 reads the merged lists back to pinned memory.
     h_qi = qs.indptr.cpu().pin_memory(); h_qt = qs.terms.cpu().pin_memory(); h_qw = qs.weights.cpu().pin_memory()
     h_out = (torch.empty((nq, k), dtype=torch.float32).pin_memory(), torch.empty((nq, k), dtype=torch.int32).pin_memory(),
              torch.empty((nq,), dtype=torch.int32).pin_memory())
     h2d = h_qi.numel() * 8 + h_qt.numel() * 4 + h_qw.numel() * 4
     d2h = nq * k * 8 + nq * 4
+    d_q = (torch.empty_like(qs.indptr), torch.empty_like(qs.terms), torch.empty_like(qs.weights))
+    cuts = [(int(qs.indptr[lo]), int(qs.indptr[hi])) for lo, hi in ex.chunks()]
 
     def step_host():
-        idx.search_host(h_qi, h_qt, h_qw, k, out=h_out)
         if world == 1:
+            idx.search_host(h_qi, h_qt, h_qw, k, out=h_out)
             return h_out
-        # multi-GPU: the per-GPU host results would be merged on the host; the exchange stays on the device path
-        o = tuple(t.to(dev, non_blocking=True) for t in h_out)
-        dist.all_gather_into_tensor(g_s, o[0]); dist.all_gather_into_tensor(g_d, o[1]); dist.all_gather_into_tensor(g_c, o[2])
-        m = topk_merge(g_s, g_d, g_c, k)
-        return tuple(t.cpu() for t in m)
+        d_q[0].copy_(h_qi, non_blocking=True); d_q[1].copy_(h_qt, non_blocking=True); d_q[2].copy_(h_qw, non_blocking=True)
+
+        def chunk(i, lo, hi, o):
+            a0, a1 = cuts[i]
+            idx.search(d_q[0][lo:hi + 1] - a0, d_q[1][a0:a1], d_q[2][a0:a1], k, out=o)
+        m = ex.run(chunk)
+        if rank == 0:
+            for dst, src in zip(h_out, m):
+                dst.copy_(src, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        return h_out
 
     def barrier():
         if world > 1:
@@ -319,8 +324,7 @@ def run_ours(a, rank, world, local_rank):
         sub = slice_queries(*qs.numpy(), 0, n)
         es, ed, ec = oracle.impact_search_c(*coll_np, a.n_docs, *sub, k, threads=os.cpu_count() or 1)
         ok = np.array_equal(final[1][:n].cpu().numpy(), ed) and np.array_equal(final[0][:n].cpu().numpy(), es)
-        if world == 1:
-            ok = ok and np.array_equal(h_out[1][:n].numpy(), ed) and np.array_equal(h_out[0][:n].numpy(), es)
+        ok = ok and np.array_equal(h_out[1][:n].numpy(), ed) and np.array_equal(h_out[0][:n].numpy(), es)
         check = f"bit-exact on {n} queries" if ok else "MISMATCH"
         if not ok:
             print(json.dumps({"error": "GPU result differs from the oracle", "metric": METRIC}), flush=True)
@@ -358,7 +362,7 @@ def main():
     if a.impl == "reference":
         run_reference(a, rank, world)
         return
-    if a.workload != "sparse":
+    if a.workload in ("dense", "hybrid"):
         if rank == 0:
             import bench_extra
             (bench_extra.run_dense if a.workload == "dense" else bench_extra.run_hybrid)(a, ROOT, ClockSampler)
@@ -370,7 +374,11 @@ def main():
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     try:
-        run_ours(a, rank, world, local_rank)
+        if a.workload == "config5":
+            import bench_extra
+            bench_extra.run_config5(a, rank, world, local_rank, ROOT, ClockSampler)
+        else:
+            run_ours(a, rank, world, local_rank)
     finally:
         if world > 1:
             import torch.distributed as dist

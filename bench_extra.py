@@ -200,3 +200,240 @@ def run_hybrid(a, root, ClockSampler):
                             "sample": f"{n_s} of {nq} queries, {dt:.2f} s; oracle.fuse = restatement of the reference's pure-Python "
                                       f"hybrid.fuse (src/hybrid.py:32-53), single core as in the reference"}}
     print(json.dumps(res), flush=True)
+
+
+# -------------------------------------------------------------------------------------------------------------
+# config 5 (BASELINE.json configs[4]): 10 M-doc sparse index + 4096-d dense flat-IP, doc-sharded over the GPUs of one
+# box with an NCCL all-gather merge.  Per-GPU work is FIXED (1.25 M docs of each kind per GPU): at 8 GPUs the collection
+# is the named 10 M docs; at fewer GPUs it is the same shards, fewer of them ("scaling": "weak").
+# -------------------------------------------------------------------------------------------------------------
+def _dense_chunks(n_rows, dim, seed, dev, torch, chunk=65536, groups=4096):
+    """Seeded generator of unit-norm fp32 doc blocks (same law as synth.make_dense), never materialised as a whole."""
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(seed)
+    cent = torch.randn((groups, dim), generator=gen, device=dev)
+    cent = cent / cent.norm(dim=1, keepdim=True)
+    scale = 0.3 * dim ** 0.5
+    for lo in range(0, n_rows, chunk):
+        n = min(chunk, n_rows - lo)
+        g = torch.randint(0, groups, (n,), generator=gen, device=dev)
+        x = torch.randn((n, dim), generator=gen, device=dev) + scale * cent[g]
+        yield lo, x / x.norm(dim=1, keepdim=True)
+
+
+def run_config5(a, rank, world, local_rank, root, ClockSampler):
+    import torch
+    import torch.distributed as dist
+    from mllm_sparse_retrieval_b200 import synth
+    from mllm_sparse_retrieval_b200.ops import DenseIndex, SparseIndex, fuse_lists, kernel_launches
+    from mllm_sparse_retrieval_b200.sharded import PipelinedExchange
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    per_gpu, V, k, H = a.c5_docs_per_gpu, a.vocab, a.k, a.dense_dim
+    n_total = per_gpu * world
+    base = rank * per_gpu
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item())
+
+    # ---- sparse shard: drawn independently per rank from the shared term law; df is summed over the ranks ----
+    t_build = time.time()
+    coll = synth.make_collection(per_gpu, a.nnz_per_doc, V=V, seed=1005 + 101 * (rank + 1), perm_seed=1005, device=dev)
+    df = torch.diff(coll.indptr)
+    if world > 1:
+        dist.all_reduce(df, op=dist.ReduceOp.SUM)
+    sidx = SparseIndex(coll.indptr, coll.docids, coll.impacts, per_gpu, device=dev, n_docs_global=n_total,
+                       df_global=df.to(torch.int32), doc_base=base, tile_docs=a.tile_docs)
+    coll_np = coll.numpy() if rank == 0 else None
+    del coll
+    torch.cuda.empty_cache()
+    qs = synth.make_queries(a.nq, a.q_len, V=V, seed=1005, device=dev)
+    postings, kept = sidx.query_work(qs.indptr, qs.terms, qs.weights)
+    ex_s = PipelinedExchange(qs.nq, k, dev, world, chunks=a.chunks if world > 1 else 1)
+    q_chunks = [qs.slice(lo, hi) for lo, hi in ex_s.chunks()]
+
+    def sparse_step():
+        return ex_s.run(lambda i, lo, hi, o: sidx.search(q_chunks[i].indptr, q_chunks[i].terms, q_chunks[i].weights, k, out=o))
+
+    # ---- dense shard: generated on the device block by block ----
+    didx = DenseIndex(H, device=dev, doc_base=base)
+    for lo, x in _dense_chunks(per_gpu, H, 2005 + 101 * (rank + 1), dev, torch):
+        didx.add(x)
+    del x
+    torch.cuda.empty_cache()
+    gq = torch.Generator(device=dev)
+    gq.manual_seed(3005)
+    dq = torch.randn((a.c5_dense_nq, H), generator=gq, device=dev)
+    # queries near docs of rank 0's first block so that true neighbours exist
+    dq = dq / dq.norm(dim=1, keepdim=True)
+    dbatch = a.c5_dense_batch
+    ex_d = PipelinedExchange(a.c5_dense_nq, k, dev, world, chunks=max(1, a.c5_dense_nq // dbatch), min_chunk=dbatch,
+                             id_dtype=torch.int64)
+    ex_d.local[2].fill_(k)
+    fallback = [0]
+
+    def dense_chunk(i, lo, hi, o):
+        didx.search(dq[lo:hi], k, mode=0, out=(o[0], o[1]))
+        fallback[0] += didx.last_fallback
+
+    def dense_step():
+        return ex_d.run(dense_chunk)
+    build_s = time.time() - t_build
+
+    # ---- timed regions (device-resident inputs; max over ranks) ----
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    for _ in range(a.warmup):
+        sparse_step()
+    barrier()
+    sidx.profile(True)
+    l0 = kernel_launches()
+    t0 = time.time()
+    ms_sparse = timed(sparse_step, a.steps, 0)
+    t1 = time.time()
+    launches = kernel_launches() - l0
+    score_ms, merge_ms, n_launch = sidx.profile(False)
+    clocks = sampler.stop(t0, t1) if rank == 0 else None
+    dense_step()
+    dense_step()
+    fallback[0] = 0
+    didx.profile(True)
+    ms_dense = timed(dense_step, a.steps, 0)
+    tc_ms, rs_ms, n_blk = didx.profile(False)
+    n_fb = fallback[0] // a.steps
+
+    # ---- e2e: pinned host query buffers in, merged lists back to pinned host memory on rank 0 ----
+    h_q = tuple(t.cpu().pin_memory() for t in (qs.indptr, qs.terms, qs.weights))
+    d_q = tuple(torch.empty_like(t) for t in (qs.indptr, qs.terms, qs.weights))
+    h_out = (torch.empty((qs.nq, k), dtype=torch.float32).pin_memory(), torch.empty((qs.nq, k), dtype=torch.int32).pin_memory(),
+             torch.empty((qs.nq,), dtype=torch.int32).pin_memory())
+    cuts = [(int(qs.indptr[lo]), int(qs.indptr[hi])) for lo, hi in ex_s.chunks()]
+
+    def sparse_host_step():
+        for d, h in zip(d_q, h_q):
+            d.copy_(h, non_blocking=True)
+
+        def chunk(i, lo, hi, o):
+            a0, a1 = cuts[i]
+            sidx.search(d_q[0][lo:hi + 1] - a0, d_q[1][a0:a1], d_q[2][a0:a1], k, out=o)
+        m = ex_s.run(chunk)
+        if rank == 0:
+            for dst, src in zip(h_out, m):
+                dst.copy_(src, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+    ms_e2e = timed(sparse_host_step, a.steps, 1)
+
+    s_fin = tuple(t.clone() for t in sparse_step())
+    d_fin = tuple(t.clone() for t in dense_step())
+    torch.cuda.synchronize()
+    sidx.status()
+
+    # ---- hybrid fusion of the merged lists (first c5_dense_nq sparse queries x the dense queries) on every rank ----
+    nf = min(a.c5_dense_nq, qs.nq)
+    self_ids = torch.full((nf,), -1, dtype=torch.int32, device=dev)
+    f_args = (d_fin[0][:nf].contiguous(), d_fin[1][:nf].to(torch.int32).contiguous(), d_fin[2][:nf].contiguous(),
+              s_fin[0][:nf].contiguous(), s_fin[1][:nf].contiguous(), s_fin[2][:nf].contiguous(), self_ids, False, a.alpha, 1 - a.alpha)
+    ms_fuse = timed(lambda: fuse_lists(*f_args), a.steps, 1)
+
+    # ---- parity at full size: size-independent properties + bounded oracle checks on rank 0's shard ----
+    problems = []
+    sc, dc = s_fin[2].long(), d_fin[2].long()
+    for name, (S, D, C) in (("sparse", s_fin), ("dense", d_fin)):
+        valid = torch.arange(k, device=dev)[None, :] < C.long()[:, None]
+        pair_ok = (S[:, :-1] > S[:, 1:]) | ((S[:, :-1] == S[:, 1:]) & (D[:, :-1] < D[:, 1:]))
+        if not bool((pair_ok | ~valid[:, 1:]).all()):
+            problems.append(f"{name}: merged lists not ordered by (score desc, id asc)")
+        if not bool(((D >= 0) & (D < n_total) | ~valid).all()):
+            problems.append(f"{name}: doc id outside [0, {n_total})")
+    if world > 1:                                               # every rank must hold the same merged lists
+        for name, D in (("sparse", s_fin[1]), ("dense", d_fin[1])):
+            h = (D.long() * torch.arange(1, D.numel() + 1, device=dev).view_as(D) % 1000003).sum().view(1)
+            lo_, hi_ = h.clone(), h.clone()
+            dist.all_reduce(lo_, op=dist.ReduceOp.MIN); dist.all_reduce(hi_, op=dist.ReduceOp.MAX)
+            if int(lo_) != int(hi_):
+                problems.append(f"{name}: ranks disagree on the merged lists")
+    if rank == 0 and a.check > 0:
+        from oracle import oracle
+        oracle.build()
+        n = min(8, a.check)
+        sub = qs.slice(0, n)
+        ls, ld, lc = sidx.search(sub.indptr, sub.terms, sub.weights, k)
+        es, ed, ec = oracle.impact_search_c(*coll_np, per_gpu, *sub.numpy(), k, threads=os.cpu_count() or 1,
+                                            n_docs_global=n_total, df_global=df.cpu().numpy().astype(np.uint32), doc_base=base)
+        if not (np.array_equal(ld.cpu().numpy(), ed) and np.array_equal(ls.cpu().numpy(), es)):
+            problems.append("sparse: rank 0 shard differs from the oracle")
+        # dense: float64 scores of 16 queries against the regenerated shard
+        nd = 16
+        best_s = torch.full((nd, 0), 0.0, dtype=torch.float64, device=dev)
+        best_i = torch.zeros((nd, 0), dtype=torch.int64, device=dev)
+        for lo, x in _dense_chunks(per_gpu, H, 2005 + 101 * (rank + 1), dev, torch):
+            sc64 = dq[:nd].double() @ x.double().T
+            best_s = torch.cat([best_s, sc64], 1); best_i = torch.cat([best_i, (base + lo + torch.arange(x.shape[0], device=dev))[None, :].expand(nd, -1)], 1)
+            top = torch.topk(best_s, k, dim=1)
+            best_s, best_i = top.values, torch.gather(best_i, 1, top.indices)
+        gs, gi = didx.search(dq[:nd], k, mode=0)
+        same = float((gi == best_i).float().mean())
+        if same < 0.999 or not torch.allclose(gs.double(), best_s, rtol=1e-3, atol=2e-6):
+            problems.append(f"dense: rank 0 shard differs from the float64 scores (id agreement {same:.4f})")
+    if rank != 0:
+        return
+    if problems:
+        print(json.dumps({"error": "; ".join(problems), "metric": "sparse top-%d queries/sec" % k}), flush=True)
+        raise SystemExit(3)
+
+    hbm, hbm_src = 6650.0, "fallback (B200_PROFILING.md)"
+    p = os.path.join(root, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        with open(p) as f:
+            hbm, hbm_src = float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    burst, sustained, tsrc = _peaks(root)
+    alg = 6 * postings + 8 * kept + 8 * k * qs.nq
+    per_launch = score_ms / max(1, n_launch)
+    lps = max(1, n_launch // a.steps)
+    achieved = alg / lps / (per_launch * 1e-3) / 1e9 if per_launch > 0 else 0.0
+    d_flops = 2.0 * a.c5_dense_nq * per_gpu * H
+    d_ach = d_flops / (tc_ms / a.steps * 1e-3) / 1e12 if tc_ms > 0 else 0.0
+    res = {"metric": "sparse top-%d queries/sec" % k, "value": qs.nq * a.steps / (ms_sparse * 1e-3), "unit": "queries/s",
+           "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms_sparse / a.steps, "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
+           "config": {"workload": f"synthetic {n_total}-doc sparse index ({per_gpu} docs/GPU, Zipf s=1, V={V}, {a.nnz_per_doc} nnz/doc, "
+                                  f"{qs.nq} queries x {a.q_len} terms) + {H}-d dense flat-IP over the same {n_total} docs "
+                                  f"({a.c5_dense_nq} queries in batches of {dbatch}), top-{k}, doc-sharded x{world} with NCCL "
+                                  f"all-gather merge (BASELINE.json configs[4]; the named 10 M docs at 8 GPUs)",
+                      "docs_per_gpu": per_gpu, "n_docs": n_total, "nq": qs.nq, "k": k, "dense_nq": a.c5_dense_nq, "dim": H,
+                      "l2": "per-GPU sparse index %d MB and dense index %d GB are larger than the 126 MB L2" %
+                            (sidx.resident_bytes >> 20, per_gpu * H * 6 >> 30)},
+           "e2e": {"value": qs.nq * a.steps / (ms_e2e * 1e-3), "unit": "queries/s", "h2d_bytes_per_step": sum(t.numel() * t.element_size() for t in h_q),
+                   "d2h_bytes_per_step": qs.nq * k * 8 + qs.nq * 4,
+                   "api": "pinned query CSR -> msr_sparse_search(MSR_DEVICE) per shard -> NCCL all-gather -> msr_topk_merge -> pinned host lists on rank 0"},
+           "gpu_launches": int(launches),
+           "roofline": {"bound": "hbm", "kernel": "sparse_score_topk_kernel", "achieved": achieved, "peak": hbm, "unit": "GB/s",
+                        "frac": achieved / hbm, "traffic": None, "peak_source": hbm_src, "algorithmic_bytes_per_launch": alg / lps,
+                        "kernel_ms_per_launch": per_launch, "kernel_share_of_step": score_ms / ms_sparse, "rank": 0},
+           "dense": {"value": a.c5_dense_nq * a.steps / (ms_dense * 1e-3), "unit": "queries/s", "ms_per_step": ms_dense / a.steps,
+                     "fused_tc_ms_per_step": tc_ms / a.steps, "rescore_ms_per_step": rs_ms / a.steps, "achieved_tflops_rank0": d_ach,
+                     "frac_of_peak": d_ach / burst, "frac_of_sustained": d_ach / sustained, "peak_source": tsrc,
+                     "certificate_fallback_queries_per_step": n_fb, "query_blocks_per_step": n_blk / a.steps},
+           "hybrid": {"value": nf * a.steps / (ms_fuse * 1e-3), "unit": "queries/s", "nq": nf},
+           "clocks": clocks, "index_build_s": build_s,
+           "parity_check": "merged lists ordered and identical on all ranks; rank-0 shard: sparse bit-exact vs the C oracle on 8 "
+                           "queries, dense ids identical to float64 scores on 16 queries"}
+    print(json.dumps(res), flush=True)

@@ -126,12 +126,14 @@ class SparseIndex:
         return int(p.value), int(c.value)
 
 
-def topk_merge(scores, docs, counts, k):
-    """[n_lists,nq,k_in] lists (e.g. an all-gather of per-GPU results) -> merged [nq,k]."""
+def topk_merge(scores, docs, counts, k, out=None):
+    """[n_lists,nq,k_in] lists (e.g. an all-gather of per-GPU results) -> merged [nq,k] (into ``out`` when given)."""
     n_lists, nq, k_in = scores.shape
     dev = scores.device
-    out = (torch.empty((nq, k), dtype=torch.float32, device=dev), torch.empty((nq, k), dtype=torch.int32, device=dev),
-           torch.empty((nq,), dtype=torch.int32, device=dev))
+    if out is None:
+        out = (torch.empty((nq, k), dtype=torch.float32, device=dev), torch.empty((nq, k), dtype=torch.int32, device=dev),
+               torch.empty((nq,), dtype=torch.int32, device=dev))
+    assert all(t.is_contiguous() for t in out)
     di = _dev_index(dev)
     with torch.cuda.device(di):
         check(_lib.load().msr_topk_merge(di, n_lists, nq, k_in, ptr(scores.contiguous()), ptr(docs.contiguous()),

@@ -21,6 +21,7 @@ import torch
 
 from . import ops
 from .index import ImpactCollection
+from .sharded import PipelinedExchange
 
 
 class Hit:
@@ -87,16 +88,14 @@ class LuceneImpactSearcher:
             return self.index.search_host(qi, qt, qw, k)
         dev = self.device
         t = lambda a, dt: torch.from_numpy(a.astype(dt)).to(dev)
-        s, d, c = self.index.search(t(qi, np.int64), t(qt, np.int32), t(qw, np.int32), k)
+        d_qi, d_qt, d_qw = t(qi, np.int64), t(qt, np.int32), t(qw, np.int32)
+        ex = PipelinedExchange(len(queries), k, dev, self.world)
+
+        def chunk(i, lo, hi, o):
+            a0, a1 = int(qi[lo]), int(qi[hi])
+            self.index.search(d_qi[lo:hi + 1] - a0, d_qt[a0:a1], d_qw[a0:a1], k, out=o)
+        ms, md, mc = ex.run(chunk)
         self.index.status()
-        nq = len(queries)
-        g_s = torch.empty((self.world, nq, k), dtype=torch.float32, device=dev)
-        g_d = torch.empty((self.world, nq, k), dtype=torch.int32, device=dev)
-        g_c = torch.empty((self.world, nq), dtype=torch.int32, device=dev)
-        torch.distributed.all_gather_into_tensor(g_s, s)
-        torch.distributed.all_gather_into_tensor(g_d, d)
-        torch.distributed.all_gather_into_tensor(g_c, c)
-        ms, md, mc = ops.topk_merge(g_s, g_d, g_c, k)
         return ms.cpu().numpy(), md.cpu().numpy(), mc.cpu().numpy().astype(np.uint32)
 
     # -- pyserini surface ---------------------------------------------------------------------------------------

@@ -1,0 +1,71 @@
+"""Doc-sharded exchange step: per-GPU top-k lists -> one all-gather -> merge, pipelined.
+
+The document collection is split into contiguous internal-id ranges, one per GPU (the precedent in the reference is
+FAISS ``IndexShards`` behind ``GpuMultipleClonerOptions.shard=True``, src/search.py:265-270).  Every rank scores the
+whole query batch against its shard; the only exchange is an all-gather of ``[nq, k]`` (score, id) lists plus counts,
+followed by ``msr_topk_merge`` with the same (score desc, id asc) key, so the result does not depend on the number
+of shards.
+
+``PipelinedExchange`` cuts the query batch into chunks: while the scorer works on chunk i+1 on the compute stream, the
+all-gather and merge of chunk i run on a side stream (NCCL over NVLink needs a handful of SMs; the scorer keeps the
+rest).  With one chunk it degenerates to score -> gather -> merge; with one rank it only runs the chunks.
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+from . import ops
+
+
+class PipelinedExchange:
+    def __init__(self, nq, k, device, world, *, chunks=4, min_chunk=1024, id_dtype=torch.int32, group=None):
+        self.nq, self.k, self.device, self.world, self.group = nq, k, torch.device(device), world, group
+        n_chunks = max(1, min(chunks, nq // max(1, min_chunk)))
+        self.bounds = [nq * i // n_chunks for i in range(n_chunks + 1)]
+        dev = self.device
+        # local results of the whole batch (chunk views are contiguous row ranges)
+        self.local = (torch.empty((nq, k), dtype=torch.float32, device=dev), torch.empty((nq, k), dtype=id_dtype, device=dev),
+                      torch.empty((nq,), dtype=torch.int32, device=dev))
+        self.final = self.local
+        self.gathered = []
+        if world > 1:
+            self.final = (torch.empty((nq, k), dtype=torch.float32, device=dev), torch.empty((nq, k), dtype=torch.int32, device=dev),
+                          torch.empty((nq,), dtype=torch.int32, device=dev))
+            for lo, hi in self.chunks():
+                n = hi - lo
+                self.gathered.append((torch.empty((world, n, k), dtype=torch.float32, device=dev),
+                                      torch.empty((world, n, k), dtype=torch.int32, device=dev),
+                                      torch.empty((world, n), dtype=torch.int32, device=dev)))
+            self.side = torch.cuda.Stream(device=dev)
+            self.events = [torch.cuda.Event() for _ in self.gathered]
+
+    def chunks(self):
+        return list(zip(self.bounds[:-1], self.bounds[1:]))
+
+    def local_views(self, lo, hi):
+        return tuple(t[lo:hi] for t in self.local)
+
+    def run(self, search_chunk):
+        """search_chunk(i, lo, hi, out_views) scores queries [lo,hi) of the batch against the local shard on the
+        current stream, writing (scores, ids, counts) into out_views.  Returns the merged (scores, ids, counts) of the
+        whole batch, ready on the current stream."""
+        if self.world == 1:
+            for i, (lo, hi) in enumerate(self.chunks()):
+                search_chunk(i, lo, hi, self.local_views(lo, hi))
+            return self.local
+        main = torch.cuda.current_stream(self.device)
+        self.side.wait_stream(main)                              # buffers of the previous run are free again
+        for i, (lo, hi) in enumerate(self.chunks()):
+            ls, ld, lc = self.local_views(lo, hi)
+            search_chunk(i, lo, hi, (ls, ld, lc))
+            self.events[i].record(main)
+            g_s, g_d, g_c = self.gathered[i]
+            with torch.cuda.stream(self.side):
+                self.side.wait_event(self.events[i])
+                dist.all_gather_into_tensor(g_s, ls, group=self.group)
+                dist.all_gather_into_tensor(g_d, ld if ld.dtype == torch.int32 else ld.to(torch.int32), group=self.group)
+                dist.all_gather_into_tensor(g_c, lc, group=self.group)
+                ops.topk_merge(g_s, g_d, g_c, self.k, out=tuple(t[lo:hi] for t in self.final))
+        main.wait_stream(self.side)
+        return self.final

@@ -86,12 +86,16 @@ def _draw_weights(shape, gen, device):
     return torch.clamp(torch.round(100.0 * torch.log1p(e)), 1, 400).to(torch.int32)
 
 
-def make_collection(n_docs, nnz_per_doc=128, V=V_DEFAULT, seed=1004, device="cpu", chunk_docs=65536) -> SparseCSR:
+def make_collection(n_docs, nnz_per_doc=128, V=V_DEFAULT, seed=1004, device="cpu", chunk_docs=65536, perm_seed=None) -> SparseCSR:
+    """perm_seed: seed of the rank -> term-id permutation when it must be shared between independently drawn shards of
+    one collection (make_queries(seed=perm_seed) then uses the same permutation); default = ``seed``."""
     device = torch.device(device)
     gen = torch.Generator(device=device)
-    gen.manual_seed(seed)
+    gen.manual_seed(seed if perm_seed is None else perm_seed)
     cdf = _zipf_cdf(V, device)
     perm = torch.randperm(V, generator=gen, device=device)
+    if perm_seed is not None:
+        gen.manual_seed(seed)
     keys, imps = [], []
     for lo in range(0, n_docs, chunk_docs):
         n = min(chunk_docs, n_docs - lo)
