@@ -48,7 +48,7 @@ def parse_args():
     ap.add_argument("--tile-docs", type=int, default=0)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--chunks", type=int, default=4, help="query chunks of the pipelined multi-GPU exchange")
+    ap.add_argument("--chunks", type=int, default=1, help="query chunks of the pipelined multi-GPU exchange (1 = score -> gather -> merge; more was not faster)")
     ap.add_argument("--check", type=int, default=32, help="queries verified against the oracle after the run")
     ap.add_argument("--workload", default="sparse", choices=["sparse", "dense", "hybrid", "config5"],
                     help="sparse = the headline metric (default); dense / hybrid = the other kernels of the path (bench_extra.py)")
@@ -345,7 +345,9 @@ def run_ours(a, rank, world, local_rank):
            "warmup": a.warmup, "ms_per_step": ms_dev / a.steps, "higher_is_better": True, "scaling": "strong",
            "vs_baseline": None, "dtype": "u32", "data": "synthetic", "config": workload_config(a, world),
            "e2e": {"value": nq * a.steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                   "api": "msr_sparse_search(MSR_HOST) with pinned host buffers"},
+                   "api": "msr_sparse_search(MSR_HOST) with pinned host buffers" if world == 1 else
+                          "pinned query CSR -> msr_sparse_search(MSR_DEVICE) per shard -> NCCL all-gather -> msr_topk_merge -> "
+                          "pinned host lists on rank 0"},
            "gpu_launches": int(launches), "roofline": roof, "clocks": clocks, "parity_check": check,
            "index": {"n_tiles": idx.n_tiles, "tile_docs": idx.tile_docs, "nnz_shard": idx.nnz, "resident_bytes": idx.resident_bytes}}
     if world == 1 and not a.no_cpu_baseline:

@@ -466,13 +466,15 @@ static TcLayout make_tc_layout(const msr_dense_index* h, uint32_t nq, uint32_t k
     TcLayout L{};
     const uint32_t N = h->n_docs;
     L.kk = std::min(k, N);
-    uint32_t cap = 2048;
+    // candidate buffer per query: the survivor count is ~ Gamma(r) * N / m, so its tail must stay below cap (a query that
+    // overflows is re-run by the exact pass, which reads the whole fp32 index again)
+    uint32_t cap = 4096;
     while (cap < 3 * L.kk && cap < 8192) cap <<= 1;
     L.cap = cap;
     if (N <= cap) {                                              // every doc fits the candidate buffer: no threshold needed
         L.m = 0; L.stride = 1; L.r = 0;
     } else {
-        L.m = std::min<uint32_t>(N, std::min<uint32_t>(16384, std::max<uint32_t>(2048, N / 16)));
+        L.m = std::min<uint32_t>(N, std::min<uint32_t>(65536, std::max<uint32_t>(2048, N / 16)));
         L.stride = N / L.m;
         const double lam = (double)L.kk * L.m / N;
         L.r = (uint32_t)std::min<double>(std::ceil(lam + 4.0 * std::sqrt(lam) + 2.0), (double)std::min<uint32_t>(L.m, MSR_MAX_K));

@@ -9,6 +9,9 @@ of shards.
 ``PipelinedExchange`` cuts the query batch into chunks: while the scorer works on chunk i+1 on the compute stream, the
 all-gather and merge of chunk i run on a side stream (NCCL over NVLink needs a handful of SMs; the scorer keeps the
 rest).  With one chunk it degenerates to score -> gather -> merge; with one rank it only runs the chunks.
+Measured on config 4 (1 M docs, 10 K queries, k = 100): the exchange is ~4 % of the step at 2 GPUs and ~12 % at 8, and
+smaller scorer launches lose about as much as the overlap wins (2 GPUs: 668 K QPS with 1 chunk, 640 K with 4; 8 GPUs:
+1.85 M with 1, 1.84 M with 2), so the default is ONE chunk; dense search uses its natural query batches as chunks.
 """
 from __future__ import annotations
 
@@ -19,7 +22,7 @@ from . import ops
 
 
 class PipelinedExchange:
-    def __init__(self, nq, k, device, world, *, chunks=4, min_chunk=1024, id_dtype=torch.int32, group=None):
+    def __init__(self, nq, k, device, world, *, chunks=1, min_chunk=1024, id_dtype=torch.int32, group=None):
         self.nq, self.k, self.device, self.world, self.group = nq, k, torch.device(device), world, group
         n_chunks = max(1, min(chunks, nq // max(1, min_chunk)))
         self.bounds = [nq * i // n_chunks for i in range(n_chunks + 1)]
