@@ -208,6 +208,18 @@ int msr_fuse(int device, uint32_t nq,
              const int32_t* self_ids, int remove_query, int dense_f32, double w_dense, double w_sparse,
              double* out_scores, int32_t* out_docs, uint8_t* out_src, uint32_t* out_counts, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------------
+ * Recall@k hit counts on the device.
+ * Replaces RecallMetrics._sort/_count, /root/reference/src/metrices.py:29-35 and :76-84: for every query whose ranked
+ * list is not empty (counts[q] > 0), hits[c] += 1 when ANY of the query's targets t_docs[t_indptr[q]..t_indptr[q+1])
+ * appears among the first cutoffs[c] entries of docs[q*row_stride ...] (rows already in rank order: score desc, the
+ * reference's stable sort).  *n_eval = number of non-empty lists.  The reference's recall is hits / (number of queries),
+ * metrices.py:86-100.  Device pointers only, asynchronous on `stream`; n_cut <= 32.
+ */
+int msr_recall_hits(int device, uint32_t nq, const int32_t* docs, size_t row_stride, const uint32_t* counts,
+                    const uint64_t* t_indptr, const int32_t* t_docs, uint32_t n_cut, const uint32_t* cutoffs,
+                    uint64_t* hits, uint64_t* n_eval, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -45,6 +45,7 @@ def _declare(lib):
         "msr_dense_last_fallback": (I, [P, ctypes.POINTER(U32)]),
         "msr_dense_tc_scores": (I, [P, U32, P, P, ctypes.c_size_t, P]),
         "msr_quantise_topk": (I, [I, U32, U32, P, I, ctypes.c_size_t, U32, U32, P, I, P, P, P, P]),
+        "msr_recall_hits": (I, [I, U32, P, ctypes.c_size_t, P, P, P, U32, P, P, P, P]),
         "msr_fuse": (I, [I, U32, U32, P, P, P, U32, P, P, P, P, I, I, D, D, P, P, P, P, P]),
     }
     for name, (res, args) in sigs.items():

@@ -264,6 +264,28 @@ def fuse_lists(d_scores, d_docs, d_counts, s_scores, s_docs, s_counts, self_ids,
     return out
 
 
+RECALL_CUTOFFS = (1, 5, 10, 100, 200)           # metrices.py:9
+
+
+def recall_hits(docs, counts, t_indptr, t_docs, cutoffs=RECALL_CUTOFFS):
+    """Kernel of SURVEY 8(f) row 3.  docs i32 [nq, w] ranked lists (CUDA), counts i32 [nq], targets as a CSR of internal
+    ids (t_indptr i64 [nq+1], t_docs i32).  Returns (hits per cutoff as a CUDA int64 tensor, n_eval CUDA int64 [1])."""
+    assert docs.is_cuda and docs.dtype == torch.int32 and docs.stride(1) == 1
+    nq = docs.shape[0]
+    dev = docs.device
+    di = _dev_index(dev)
+    cuts = torch.tensor(list(cutoffs), dtype=torch.int32, device=dev)
+    hits = torch.empty((len(cutoffs),), dtype=torch.int64, device=dev)
+    n_eval = torch.empty((1,), dtype=torch.int64, device=dev)
+    t_indptr = t_indptr.to(device=dev, dtype=torch.int64).contiguous()
+    t_docs = t_docs.to(device=dev, dtype=torch.int32).contiguous()
+    counts = counts.to(torch.int32).contiguous()
+    with torch.cuda.device(di):
+        check(_lib.load().msr_recall_hits(di, nq, ptr(docs), docs.stride(0) if nq else 0, ptr(counts), ptr(t_indptr), ptr(t_docs),
+                                          len(cutoffs), ptr(cuts), ptr(hits), ptr(n_eval), current_stream_ptr(di)))
+    return hits, n_eval
+
+
 _DTYPES = {torch.float32: 0, torch.float16: 1, torch.bfloat16: 2}
 
 

@@ -122,19 +122,23 @@ def write_trec_arrays(path, qids, names, scores, docs, counts, run_name):
             f.writelines(f"{qid} Q0 {names[docs[r, j]]} {j + 1} {scores[r, j]} {run_name}\n" for j in range(n))
 
 
-def recall_at(qids, names, docs, counts, qrels, ks=(1, 5, 10, 100, 200)):
-    """Recall@k as metrices.py:37-84 defines it: |top-k ∩ targets| / |targets|, averaged over the queries."""
-    out = {k: 0.0 for k in ks}
-    n_eval = 0
-    for r, qid in enumerate(qids):
-        tg = qrels.get(qid)
-        if not tg:
-            continue
-        n_eval += 1
-        ranked = [names[docs[r, j]] for j in range(int(counts[r]))]
-        for k in ks:
-            out[k] += len(tg.intersection(ranked[:k])) / len(tg)
-    return {k: (v / n_eval if n_eval else 0.0) for k, v in out.items()}, n_eval
+def recall_at(qids, name_id, docs, counts, qrels, ks=ops.RECALL_CUTOFFS):
+    """Recall@k as the reference computes it (metrices.py:29-100): a query scores a hit at k when ANY of its targets is
+    among its first k ranked docs; queries with an empty list never hit; recall = hits / number of queries.
+    docs i32 [nq, w] CUDA ranked lists of internal ids, counts [nq]; qrels = {qid: set of external docids}.
+    The hit test runs on the device (msr_recall_hits); only the 5 counters come back."""
+    indptr, flat = [0], []
+    for qid in qids:
+        for t in sorted(qrels.get(qid, ())):
+            i = name_id.get(t)
+            if i is not None:
+                flat.append(i)
+        indptr.append(len(flat))
+    hits, n_eval = ops.recall_hits(docs.contiguous(), counts, torch.tensor(indptr, dtype=torch.int64),
+                                   torch.tensor(flat, dtype=torch.int32), ks)
+    hits = hits.cpu().tolist()
+    n = max(1, len(qids))
+    return {k: h / n for k, h in zip(ks, hits)}, int(n_eval.item())
 
 
 def main(argv=None):
@@ -241,8 +245,8 @@ def main(argv=None):
                 if parts:
                     qrels.setdefault(parts[0], set()).update(parts[1:])
         qids, s, d, c = outputs[main_tag]
-        rec, n_eval = recall_at(qids, names, d.cpu().numpy(), c.cpu().numpy(), qrels)
-        print(f"[{main_tag}] queries evaluated: {n_eval}")
+        rec, n_eval = recall_at(qids, lookup, d, c, qrels)
+        print(f"[{main_tag}] queries: {len(qids)} (non-empty lists: {n_eval})")
         for k, v in rec.items():
             print(f"Recall@{k}: {v:.4f}")
     return outputs, names

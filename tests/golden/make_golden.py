@@ -5,7 +5,8 @@
 
 Pinned functions: hybrid.fuse / hybrid.fuse_statistic / hybrid.write_trec_run / hybrid.read_trec_run (hybrid.py),
 search.get_run_dict / search.sparse_search / search.search_queries (search.py:55-99) and
-encode.get_img_valid_tokens_values (encode.py:56-93).  Third-party modules that are absent here (faiss, tevatron,
+encode.get_img_valid_tokens_values (encode.py:56-93); with ``--metrics`` RecallMetrics.sort_and_count
+(metrices.py:29-84) -> reference_metrics.json.  Third-party modules that are absent here (faiss, tevatron,
 pyserini, nltk, peft) are stubbed in sys.modules exactly as SURVEY.md Appendix B describes; none of the pinned
 functions executes stub code except through the fake searcher objects handed to them below.
 """
@@ -185,8 +186,50 @@ def make_quantiser_cases(encode, rng):
     return out
 
 
+def make_metrics_cases():
+    """RecallMetrics.sort_and_count (src/metrices.py:29-84) on random runs.  The class calls ``.cuda()`` on tiny tensors
+    and ``dist.get_world_size()`` in its constructor; both are patched to CPU / 1 here, nothing else is touched."""
+    import torch
+    import torch.distributed as dist
+    import metrices
+    torch.Tensor.cuda = lambda self, *a, **k: self
+    dist.get_world_size = lambda *a, **k: 1
+    rng = np.random.default_rng(20261105)
+    cases = []
+    for nq, n_docs, depth, multi in [(40, 300, 250, False), (25, 60, 40, True), (30, 1000, 12, True), (8, 50, 0, False)]:
+        targets, runs = {}, {}
+        for name in ("dense", "sparse", "fusion"):
+            run = {}
+            for q in range(nq):
+                n = 0 if depth == 0 or (q % 11 == 7) else int(rng.integers(1, depth + 1))
+                docs = rng.choice(n_docs, size=min(n, n_docs), replace=False)
+                # scores with ties: the stable sort keeps insertion order among equals
+                sc = np.round(rng.random(len(docs)) * 8) / 8
+                d = {str(int(x)): float(v) for x, v in zip(docs, sc)}
+                run[str(q)] = d if name == "fusion" else {"docs": d, "min_score": 0.0, "max_score": 1.0}
+            runs[name] = run
+        for q in range(nq):
+            tg = [str(int(x)) for x in rng.choice(n_docs, size=5 if multi else 1, replace=False)]
+            targets[str(q)] = tg if multi else tg[0]
+
+        class _DS:
+            def get_target(self, qid, query_type):
+                return targets[qid]
+        rm = metrices.RecallMetrics(_DS(), runs["dense"], runs["sparse"], runs["fusion"], [], list(range(nq)),
+                                    types.SimpleNamespace(query_type="text"))
+        rm.sort_and_count()
+        cases.append({"nq": nq, "n_docs": n_docs, "targets": targets, "runs": runs,
+                      "counts": {"dense": rm.dense_counts, "sparse": rm.sparse_counts, "fusion": rm.fusion_counts}})
+    return cases
+
+
 def main():
     hybrid, search, encode = import_reference()
+    if "--metrics" in sys.argv:
+        with open(os.path.join(HERE, "reference_metrics.json"), "w") as f:
+            json.dump({"metrics": make_metrics_cases()}, f)
+        print("wrote reference_metrics.json", os.path.getsize(os.path.join(HERE, "reference_metrics.json")), "bytes")
+        return
     rng = np.random.default_rng(20261104)
     golden = {
         "numpy": np.__version__,

@@ -130,3 +130,24 @@ def test_collection_doc_order_and_cache(tmp_path):
     assert (d / "msr_index" / "meta.json").exists()
     assert again.docids == coll.docids and again.terms == coll.terms
     np.testing.assert_array_equal(again.post_docs, coll.post_docs)
+
+
+# ---- Recall@k (metrices.py) ----------------------------------------------------------------------------------
+METRICS = os.path.join(os.path.dirname(__file__), "golden", "reference_metrics.json")
+
+
+def metrics_cases():
+    with open(METRICS) as f:
+        return json.load(f)["metrics"]
+
+
+def test_oracle_recall_counts_match_reference():
+    """oracle.recall_counts against RecallMetrics.sort_and_count of the reference (hit metric, stable order, empty
+    lists skipped) on the committed fixtures."""
+    from oracle import oracle
+    for case in metrics_cases():
+        for name in ("dense", "sparse", "fusion"):
+            run = case["runs"][name]
+            docs = {q: (v if name == "fusion" else v["docs"]) for q, v in run.items()}
+            got = oracle.recall_counts(docs, case["targets"])
+            assert {str(k): v for k, v in got.items()} == case["counts"][name], (case["nq"], name)

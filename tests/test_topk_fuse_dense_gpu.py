@@ -283,3 +283,35 @@ def test_quantise_topk_feeds_sparse_search(oracle, lib_built, dtype):
     es, ed, ec = oracle.impact_search_c(coll.indptr, coll.post_docs, coll.post_impacts, coll.n_docs, qi, qt, qw, 20)
     np.testing.assert_array_equal(d.cpu().numpy(), ed)
     np.testing.assert_array_equal(s.cpu().numpy(), es)
+
+
+@pytest.mark.gpu
+def test_recall_hits_kernel_matches_reference_fixtures(lib_built):
+    """msr_recall_hits against the counts RecallMetrics.sort_and_count of the reference produced
+    (tests/golden/reference_metrics.json): rows are put in the reference's stable score-descending order first."""
+    import json, os
+    from mllm_sparse_retrieval_b200.ops import recall_hits, RECALL_CUTOFFS
+    with open(os.path.join(os.path.dirname(__file__), "golden", "reference_metrics.json")) as f:
+        cases = json.load(f)["metrics"]
+    for case in cases:
+        nq = case["nq"]
+        for name in ("dense", "sparse", "fusion"):
+            run = case["runs"][name]
+            lists = []
+            for q in range(nq):
+                v = run[str(q)]
+                d = v if name == "fusion" else v["docs"]
+                lists.append([int(x) for x, _ in sorted(d.items(), key=lambda kv: kv[1], reverse=True)])
+            w = max(1, max(len(x) for x in lists))
+            docs = torch.full((nq, w + 3), -1, dtype=torch.int32)           # pitch > width: padding must be ignored
+            for q, x in enumerate(lists):
+                docs[q, :len(x)] = torch.tensor(x, dtype=torch.int32)
+            counts = torch.tensor([len(x) for x in lists], dtype=torch.int32)
+            indptr, flat = [0], []
+            for q in range(nq):
+                t = case["targets"][str(q)]
+                flat += [int(x) for x in (t if isinstance(t, list) else [t])]
+                indptr.append(len(flat))
+            hits, n_eval = recall_hits(docs.cuda(), counts.cuda(), torch.tensor(indptr), torch.tensor(flat, dtype=torch.int32))
+            assert {str(k): int(h) for k, h in zip(RECALL_CUTOFFS, hits.cpu())} == case["counts"][name], (nq, name)
+            assert int(n_eval) == sum(1 for x in lists if x)
