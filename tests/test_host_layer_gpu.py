@@ -187,7 +187,7 @@ def test_search_cli_writes_reference_format_runs(oracle, lib_built, tmp_path):
         for q, t in zip(qids, topics):
             f.write(f"{q}\t{t}\n")
     out = tmp_path / "runs"
-    cli.main(["--passage_reps", str(dn), "--sparse_index", str(sp), "--query_reps", str(dn), "--query_sparse", str(sp),
+    outputs, names = cli.main(["--passage_reps", str(dn), "--sparse_index", str(sp), "--query_reps", str(dn), "--query_sparse", str(sp),
               "--depth", str(depth), "--alpha", "0.3", "--remove_query", "--save_dir", str(out), "--batch_size", "16",
               "--model_name_or_path", "ignored", "--threads", "16"])
     # expectation through the oracle and the reference-shaped glue
@@ -222,3 +222,11 @@ def test_search_cli_writes_reference_format_runs(oracle, lib_built, tmp_path):
     first_q = qids[0]
     exp_docs = [d for d in sparse_run[first_q]["docs"]]
     assert [ln.split()[2] for ln in srun if ln.split()[0] == first_q] == exp_docs
+    # Recall@k of the fused run, counted on the device, against the restatement of RecallMetrics (hit metric)
+    qrels = {q: {doc_ids[int(j)] for j in rng.choice(n_docs, 3, replace=False)} for q in qids}
+    f_qids, _, f_docs, f_cnt = outputs["fusion"]
+    rec, n_eval = cli.recall_at(f_qids, {n: i for i, n in enumerate(names)}, f_docs, f_cnt, qrels)
+    ranked = {q: {d: -r for d, r, _ in got[q]} for q in qids}                    # run-file order as scores
+    exp_counts = oracle.recall_counts(ranked, {q: sorted(qrels[q]) for q in qids})
+    assert {k: round(v * len(qids)) for k, v in rec.items()} == exp_counts
+    assert n_eval == len(qids)
