@@ -209,6 +209,36 @@ int msr_fuse(int device, uint32_t nq,
              double* out_scores, int32_t* out_docs, uint8_t* out_src, uint32_t* out_counts, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
+ * Index builder: replaces the offline Lucene indexing step of the reference,
+ * `python -m pyserini.index.lucene --collection JsonVectorCollection --impact --pretokenized` (scripts/sparse_index.sh:12-18),
+ * for the JSONL files /root/reference/src/encode.py:353-359,426 writes ({"id", "content", "vector": {term: int}} per line).
+ *
+ * msr_jsonl_parse (host C++, no GPU needed): reads the files in the given order and builds the term dictionary, the
+ * docid table and DOC-MAJOR postings under rules S1 (tf = vector[t], non-positive weights dropped, keys split on
+ * whitespace, pieces add up; impacts above 65535 -> MSR_ERR_RANGE), S2 (terms verbatim) and S8 (doc_rank = rank of the
+ * docid string in UTF-8 byte order; duplicate ids -> MSR_ERR_INVALID).  Term ids follow first appearance.
+ * msr_collection_info: n_docs, n_terms, nnz, total bytes of docid strings, total bytes of term strings.
+ * msr_collection_export copies into caller buffers (any may be NULL): doc_indptr u64[n_docs+1], terms u32[nnz],
+ * impacts u16[nnz], doc_rank u32[n_docs] (file order -> internal id), and the two string tables as a byte blob plus
+ * offsets u64[n+1] each (docids in FILE order).
+ *
+ * msr_invert_docs (device): doc-major postings -> the canonical term-major CSR msr_sparse_index_build takes (postings
+ * grouped by term, internal doc ids strictly ascending): 64-bit keys (term, internal doc) from one warp per document,
+ * a radix sort over the used key bits, a histogram scan for indptr.  doc_rank NULL = documents are already in internal
+ * order.  Outputs: out_indptr u64[n_terms+1], out_docids u32[nnz], out_impacts u16[nnz]; host or device pointers per
+ * `where` (the call synchronises `stream`).  A term occurring twice in one document is reported as MSR_ERR_INVALID.
+ */
+typedef struct msr_collection msr_collection;
+int msr_jsonl_parse(const char* const* paths, uint32_t n_paths, msr_collection** out);
+int msr_collection_info(const msr_collection* c, uint64_t info[5]);
+int msr_collection_export(const msr_collection* c, uint64_t* doc_indptr, uint32_t* terms, uint16_t* impacts,
+                          uint32_t* doc_rank, char* docid_blob, uint64_t* docid_off, char* term_blob, uint64_t* term_off);
+int msr_collection_destroy(msr_collection* c);
+int msr_invert_docs(int device, uint32_t n_docs, uint32_t n_terms, const uint64_t* doc_indptr, const uint32_t* terms,
+                    const uint16_t* impacts, const uint32_t* doc_rank, uint64_t* out_indptr, uint32_t* out_docids,
+                    uint16_t* out_impacts, int where, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
  * Recall@k hit counts on the device.
  * Replaces RecallMetrics._sort/_count, /root/reference/src/metrices.py:29-35 and :76-84: for every query whose ranked
  * list is not empty (counts[q] > 0), hits[c] += 1 when ANY of the query's targets t_docs[t_indptr[q]..t_indptr[q+1])

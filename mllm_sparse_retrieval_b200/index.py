@@ -88,8 +88,66 @@ class ImpactCollection:
         return cls(terms, [doc_ids[i] for i in order], indptr, d, w)
 
     @classmethod
-    def from_jsonl_dir(cls, path, use_cache=True):
-        """path = the reference's ``--sparse_index`` directory (holds corpus_*.jsonl; Lucene's own ``index/`` is ignored)."""
+    def from_jsonl_files(cls, files, device=None):
+        """Native builder: libmsr's C++ JSONL reader (msr_jsonl_parse: dictionary, docid table,
+        doc-major postings under rules S1/S2/S8) followed by the inversion to the canonical term-major CSR -- on the GPU
+        (msr_invert_docs: key build + radix sort + histogram scan) when one is present, else a NumPy lexsort on the host
+        (index building is not the search path; the scorer itself has no CPU fallback).  Same numbering as
+        ``from_vectors`` on the parsed lines."""
+        import ctypes
+        from . import _lib
+        lib = _lib.load()
+        files = [os.fspath(f) for f in files]
+        arr = (ctypes.c_char_p * len(files))(*[f.encode() for f in files])
+        h = ctypes.c_void_p()
+        _lib.check(lib.msr_jsonl_parse(arr, len(files), ctypes.byref(h)))
+        try:
+            info = (ctypes.c_uint64 * 5)()
+            _lib.check(lib.msr_collection_info(h, info))
+            n_docs, n_terms, nnz, db, tb = (int(x) for x in info)
+            doc_indptr = np.empty(n_docs + 1, dtype=np.uint64)
+            p_terms = np.empty(nnz, dtype=np.uint32); p_imps = np.empty(nnz, dtype=np.uint16)
+            rank = np.empty(n_docs, dtype=np.uint32)
+            d_blob = np.empty(max(db, 1), dtype=np.uint8); d_off = np.empty(n_docs + 1, dtype=np.uint64)
+            t_blob = np.empty(max(tb, 1), dtype=np.uint8); t_off = np.empty(n_terms + 1, dtype=np.uint64)
+            _lib.check(lib.msr_collection_export(h, _lib.ptr(doc_indptr), _lib.ptr(p_terms), _lib.ptr(p_imps), _lib.ptr(rank),
+                                                 _lib.ptr(d_blob), _lib.ptr(d_off), _lib.ptr(t_blob), _lib.ptr(t_off)))
+        finally:
+            lib.msr_collection_destroy(h)
+        db_, tb_ = d_blob.tobytes(), t_blob.tobytes()
+        docids = [None] * n_docs
+        for i in range(n_docs):
+            docids[int(rank[i])] = db_[int(d_off[i]):int(d_off[i + 1])].decode("utf-8")
+        terms = [tb_[int(t_off[i]):int(t_off[i + 1])].decode("utf-8") for i in range(n_terms)]
+        if n_terms == 0 or n_docs == 0:
+            return cls(terms or [""], docids, np.zeros(max(n_terms, 1) + 1, dtype=np.uint64), np.zeros(0, np.uint32), np.zeros(0, np.uint16))
+        use_gpu = False
+        try:
+            import torch
+            use_gpu = torch.cuda.is_available()
+        except ImportError:
+            pass
+        if use_gpu:
+            import torch
+            dev = torch.cuda.current_device() if device is None else torch.device(device).index or 0
+            indptr = np.empty(n_terms + 1, dtype=np.uint64)
+            o_docs = np.empty(nnz, dtype=np.uint32); o_imps = np.empty(nnz, dtype=np.uint16)
+            with torch.cuda.device(dev):
+                _lib.check(lib.msr_invert_docs(dev, n_docs, n_terms, _lib.ptr(doc_indptr), _lib.ptr(p_terms), _lib.ptr(p_imps),
+                                               _lib.ptr(rank), _lib.ptr(indptr), _lib.ptr(o_docs), _lib.ptr(o_imps), 0,
+                                               _lib.current_stream_ptr(dev)))
+            return cls(terms, docids, indptr, o_docs, o_imps)
+        d = np.repeat(rank.astype(np.int64), np.diff(doc_indptr.astype(np.int64)))
+        t = p_terms.astype(np.int64)
+        o = np.lexsort((d, t))
+        indptr = np.zeros(n_terms + 1, dtype=np.uint64)
+        np.cumsum(np.bincount(t, minlength=n_terms), out=indptr[1:])
+        return cls(terms, docids, indptr, d[o], p_imps[o])
+
+    @classmethod
+    def from_jsonl_dir(cls, path, use_cache=True, native=True):
+        """path = the reference's ``--sparse_index`` directory (holds corpus_*.jsonl; Lucene's own ``index/`` is ignored).
+        native=True builds through libmsr (C++ reader + GPU inversion); False keeps the pure-Python reader."""
         files = sorted(glob.glob(os.path.join(path, "corpus*.jsonl")))
         if not files:
             raise FileNotFoundError(f"no corpus*.jsonl under {path}")
@@ -99,6 +157,14 @@ class ImpactCollection:
             got = cls._load_cache(cdir, stamp)
             if got is not None:
                 return got
+        if native:
+            coll = cls.from_jsonl_files(files)
+            if use_cache:
+                try:
+                    coll._save_cache(cdir, stamp)
+                except OSError:
+                    pass
+            return coll
         ids, vecs = [], []
         for fn in files:
             with open(fn, "r", encoding="utf-8") as f:
