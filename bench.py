@@ -123,6 +123,20 @@ def load_peaks():
     return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
 
 
+def ncu_traffic(kernel, **cfg):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch from the committed ncu --set full capture of this exact
+    configuration (profiles/traffic.json), else None."""
+    p = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(p) as f:
+            e = json.load(f).get(kernel)
+        if e and all(cfg.get(k) == v for k, v in e["match"].items()):
+            return e["dram_bytes_per_launch"]
+    except (OSError, ValueError, KeyError):
+        pass
+    return None
+
+
 def shard_collection(coll, lo, hi):
     """Doc-range shard [lo,hi) of a term-major CSR held as torch tensors (docs rebased to 0)."""
     import torch
@@ -336,7 +350,10 @@ def run_ours(a, rank, world, local_rank):
     launches_per_step = max(1, n_launch // a.steps)
     achieved = alg_bytes_step / launches_per_step / (per_launch_ms * 1e-3) / 1e9 if per_launch_ms > 0 else 0.0
     roof = {"bound": "hbm", "kernel": "sparse_score_topk_kernel", "achieved": achieved, "peak": peak, "unit": "GB/s",
-            "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+            "frac": achieved / peak,
+            "traffic": ncu_traffic("sparse_score_topk_kernel", n_docs=a.n_docs, nq=a.nq, q_len=a.q_len, k=a.k, n_gpus=world,
+                                   tile_docs=a.tile_docs) if launches_per_step == 1 else None,
+            "peak_source": peak_src,
             "algorithmic_bytes_per_launch": alg_bytes_step / launches_per_step,
             "physical_posting_bytes_per_launch": 4 * postings / launches_per_step,
             "kernel_ms_per_launch": per_launch_ms, "kernel_share_of_step": score_ms / ms_dev,

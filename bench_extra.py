@@ -24,6 +24,17 @@ def _peaks(root):
     return 1590.0, 1400.0, "fallback (B200_PROFILING.md)"
 
 
+def _traffic(root, kernel, **cfg):
+    try:
+        with open(os.path.join(root, "profiles", "traffic.json")) as f:
+            e = json.load(f).get(kernel)
+        if e and all(cfg.get(k) == v for k, v in e["match"].items()):
+            return e["dram_bytes_per_launch"]
+    except (OSError, ValueError, KeyError):
+        pass
+    return None
+
+
 def _timed(fn, steps, warmup, torch):
     for _ in range(warmup):
         fn()
@@ -107,7 +118,8 @@ def run_dense(a, root, ClockSampler):
                    "d2h_bytes_per_step": nq * k * 12, "api": "msr_dense_search(MSR_HOST), pinned host buffers"},
            "gpu_launches": int(launches),
            "roofline": {"bound": "tensor", "kernel": "dense_tc_kernel<FILTER> (tcgen05.mma fp16, fused threshold selection)", "achieved": achieved, "peak": burst,
-                        "unit": "TFLOP/s", "frac": achieved / burst, "frac_of_sustained": achieved / sustained, "traffic": None,
+                        "unit": "TFLOP/s", "frac": achieved / burst, "frac_of_sustained": achieved / sustained,
+                        "traffic": _traffic(root, "dense_tc_kernel<1>", n_docs=N, nq=nq, dim=H, k=k),
                         "peak_source": src + " dense bf16 figure (fp16 and bf16 share the kind::f16 tensor rate); burst: the kernel is "
                                       "bracketed by its own events", "flops_per_launch": flops,
                         "kernel_ms_per_launch": ms_tc, "kernel_share_of_step": ms_tc / (ms_dev / a.steps),

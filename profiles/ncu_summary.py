@@ -48,6 +48,7 @@ def main():
     ia, isamp, isrc = hdr.index("Instructions Executed"), hdr.index("# Samples"), hdr.index("Source")
     iw = hdr.index("L1 Wavefronts Shared") if "L1 Wavefronts Shared" in hdr else None
     st = [i for i, h in enumerate(hdr) if h.startswith("stall_") and "Not Issued" not in h]
+    data = [r for r in data if len(r) == len(hdr) and r[ia].strip().isdigit()]     # multi-kernel reports repeat the header
     tot = sum(int(r[ia]) for r in data) or 1
     ts = sum(int(r[isamp]) for r in data) or 1
     print(f"-- source page: {len(data)} SASS instructions, {tot} warp-instructions executed, {ts} samples")
