@@ -189,6 +189,24 @@ int msr_quantise_topk(int device, uint32_t n_rows, uint32_t vocab, const void* l
                       uint32_t top, uint32_t vocab_len, const int32_t* token_to_term, int doc_mode,
                       uint64_t* out_indptr, uint32_t* out_terms, uint32_t* out_weights, void* stream);
 
+/*
+ * Candidate branch of the text quantiser: get_text_valid_tokens_values without --sparse_manual
+ * (/root/reference/src/encode.py:96-112,125-135), the default of scripts/search_sparse.sh.  The caller tokenises the
+ * caption on the host as the reference does (nltk words minus stop-words/punctuation -> tokenizer.encode -> set of token
+ * ids, encode.py:97-100) and passes the per-row candidate lists as a HOST CSR (cand_indptr u64[n_rows+1], cand_tokens
+ * i32[], in the order of the reference's list(token_ids)).  Per row: top-min(n_candidates, cap) of logits[candidates]
+ * by (value desc, candidate position asc) -- the reference uses cap = 128; a row WITHOUT candidates falls back to the
+ * top-`fallback_top` of the whole vocabulary (the reference uses 10).  Quantisation, the `id < vocab_len` skip with
+ * its value shift, the token -> term map and the duplicate rule are those of msr_quantise_topk.  Output pitch =
+ * max(cap, fallback_top) entries per row.  logits / token_to_term / out_* are device pointers; at most 4096 candidates
+ * per row; candidate ids must be < vocab.  The call synchronises `stream` before returning (it reads pageable host
+ * arrays).  Expansion terms (num_expended_tokens > 0; every script of the reference passes 0) are not provided.
+ */
+int msr_quantise_candidates(int device, uint32_t n_rows, uint32_t vocab, const void* logits, int dtype, size_t row_stride,
+                            const uint64_t* cand_indptr_host, const int32_t* cand_tokens_host, uint32_t cap,
+                            uint32_t fallback_top, uint32_t vocab_len, const int32_t* token_to_term, int doc_mode,
+                            uint64_t* out_indptr, uint32_t* out_terms, uint32_t* out_weights, void* stream);
+
 /* ---------------------------------------------------------------------------------------------------------
  * Hybrid fusion (kernel (d)) = hybrid.fuse([dense_run, sparse_run], [alpha, 1-alpha]) for a query batch.
  * Inputs per modality: scores f32 [nq,k_*], docs i32 [nq,k_*] (global internal ids), counts u32 [nq] and
@@ -249,6 +267,16 @@ int msr_invert_docs(int device, uint32_t n_docs, uint32_t n_terms, const uint64_
 int msr_recall_hits(int device, uint32_t nq, const int32_t* docs, size_t row_stride, const uint32_t* counts,
                     const uint64_t* t_indptr, const int32_t* t_docs, uint32_t n_cut, const uint32_t* cutoffs,
                     uint64_t* hits, uint64_t* n_eval, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Provenance histogram: the loop of /root/reference/src/score_statistic.py:406-417 over the
+ * output of fuse_statistic (hybrid.py:56-90) = msr_fuse's (out_scores, out_src, out_counts).  Per query the fused list
+ * is ordered by score descending with equal scores in insertion order (Python's stable sort), cut at `depth` (the
+ * reference uses 200), and hist[(tag-1)*depth + rank-1] += 1 for the entry at 1-based `rank` with tag 1 = dense only,
+ * 2 = sparse only, 3 = both ("fuse").  hist u64[3*depth] is zeroed by the call.  Device pointers, asynchronous on `stream`.
+ */
+int msr_provenance_hist(int device, uint32_t nq, const double* scores, const uint8_t* src, size_t row_stride,
+                        const uint32_t* counts, uint32_t depth, uint64_t* hist, void* stream);
 
 #ifdef __cplusplus
 }

@@ -37,6 +37,31 @@ recall_hits_kernel(const int32_t* __restrict__ docs, size_t row_stride, const ui
     if (lane < n_cut && best < cutoffs[lane]) atomicAdd(hits + lane, 1ull);
 }
 
+
+// Provenance histogram of score_statistic.py (/root/reference/src/score_statistic.py:406-417): per query the fused
+// list is ordered by score descending (Python's stable sort: equal scores keep insertion order), cut at `depth`, and
+// the 1-based rank of every entry is appended to the list of its tag (dense / sparse / fuse, hybrid.py:76-85).  The
+// three rank lists are only ever binned, so the device result is hist[tag-1][rank-1] summed over the batch.
+// One CTA per query; rank by counting over the row (<= 2*MSR_MAX_K entries, read through L1).
+__global__ void __launch_bounds__(256)
+provenance_hist_kernel(const double* __restrict__ scores, const uint8_t* __restrict__ src, size_t row_stride,
+                       const uint32_t* __restrict__ counts, uint32_t depth, unsigned long long* __restrict__ hist) {
+    const uint32_t q = blockIdx.x;
+    const uint32_t n = counts[q];
+    const double* s = scores + (size_t)q * row_stride;
+    const uint8_t* t = src + (size_t)q * row_stride;
+    for (uint32_t j = threadIdx.x; j < n; j += blockDim.x) {
+        const double a = s[j];
+        uint32_t r = 0;
+        for (uint32_t i = 0; i < n; ++i) {
+            const double b = __ldg(s + i);
+            r += (b > a) || (b == a && i < j);
+        }
+        const uint32_t tag = t[j];
+        if (r < depth && tag >= 1 && tag <= 3) atomicAdd(hist + (size_t)(tag - 1) * depth + r, 1ull);
+    }
+}
+
 }  // namespace msr
 
 using namespace msr;
@@ -55,6 +80,22 @@ extern "C" int msr_recall_hits(int device, uint32_t nq, const int32_t* docs, siz
     MSR_REQUIRE(docs && counts && t_indptr, "msr_recall_hits: NULL input");
     recall_hits_kernel<<<(nq + 7) / 8, 256, 0, s>>>(docs, row_stride, counts, nq, t_indptr, t_docs, cutoffs, n_cut,
                                                     (unsigned long long*)hits, (unsigned long long*)n_eval);
+    count_launch();
+    MSR_CUDA_CHECK(cudaGetLastError());
+    return MSR_OK;
+}
+
+extern "C" int msr_provenance_hist(int device, uint32_t nq, const double* scores, const uint8_t* src, size_t row_stride,
+                                   const uint32_t* counts, uint32_t depth, uint64_t* hist, void* stream) {
+    MSR_REQUIRE(depth >= 1 && depth <= 2 * MSR_MAX_K, "msr_provenance_hist: depth=%u outside [1,%u]", depth, 2 * MSR_MAX_K);
+    MSR_REQUIRE(hist, "msr_provenance_hist: NULL hist");
+    int rc = use_device(device);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    MSR_CUDA_CHECK(cudaMemsetAsync(hist, 0, (size_t)3 * depth * 8, s));
+    if (nq == 0) return MSR_OK;
+    MSR_REQUIRE(scores && src && counts, "msr_provenance_hist: NULL input");
+    provenance_hist_kernel<<<nq, 256, 0, s>>>(scores, src, row_stride, counts, depth, (unsigned long long*)hist);
     count_launch();
     MSR_CUDA_CHECK(cudaGetLastError());
     return MSR_OK;

@@ -19,6 +19,9 @@
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
+#include <algorithm>
+#include <vector>
+
 #include "common.cuh"
 
 namespace msr {
@@ -107,6 +110,38 @@ quantise_map_kernel(const float* __restrict__ ts, const int32_t* __restrict__ td
     if (lane == 0) out_indptr[row] = (unsigned long long)row * top;
 }
 
+
+// Candidate branch of get_text_valid_tokens_values (/root/reference/src/encode.py:96-135): the row's candidates are
+// the token ids of the caption's content words (host tokenisation); keep the top-min(n_c, cap) of logits[cands] by
+// (value desc, candidate position asc).  One CTA per row; ranks by counting in shared memory (n_c is ~10 for a caption).
+// Writes the same (ts, td, cnt) triple the full-vocabulary selection produces, so quantise_map_kernel finishes the job.
+constexpr int kCandMax = 4096;
+template <class T>
+__global__ void __launch_bounds__(128)
+cand_select_kernel(const T* __restrict__ logits, size_t row_stride, const unsigned long long* __restrict__ c_indptr,
+                   const int32_t* __restrict__ c_tok, uint32_t cap, uint32_t pitch, float* __restrict__ ts,
+                   int32_t* __restrict__ td, uint32_t* __restrict__ cnt) {
+    __shared__ float v[kCandMax];
+    const uint32_t row = blockIdx.x;
+    const unsigned long long lo = c_indptr[row];
+    const uint32_t n = (uint32_t)(c_indptr[row + 1] - lo);
+    if (n == 0) return;                                   // empty rows take the top-`fallback` path (host-driven)
+    const T* x = logits + (size_t)row * row_stride;
+    for (uint32_t j = threadIdx.x; j < n; j += blockDim.x) v[j] = to_f32<T>(x[c_tok[lo + j]]);
+    __syncthreads();
+    const uint32_t keep = min(n, cap);
+    for (uint32_t j = threadIdx.x; j < n; j += blockDim.x) {
+        const float a = v[j];
+        uint32_t r = 0;
+        for (uint32_t i = 0; i < n; ++i) {
+            const float b = v[i];
+            r += (b > a) || (b == a && i < j);
+        }
+        if (r < keep) { ts[(size_t)row * pitch + r] = a; td[(size_t)row * pitch + r] = c_tok[lo + j]; }
+    }
+    if (threadIdx.x == 0) cnt[row] = keep;
+}
+
 }  // namespace msr
 
 using namespace msr;
@@ -153,5 +188,73 @@ extern "C" int msr_quantise_topk(int device, uint32_t n_rows, uint32_t vocab, co
     }
     if (f32) cudaFreeAsync(f32, s);
     cudaFreeAsync(ts, s); cudaFreeAsync(td, s); cudaFreeAsync(tc, s);
+    return rc;
+}
+
+extern "C" int msr_quantise_candidates(int device, uint32_t n_rows, uint32_t vocab, const void* logits, int dtype,
+                                       size_t row_stride, const uint64_t* cand_indptr_host, const int32_t* cand_tokens_host,
+                                       uint32_t cap, uint32_t fallback_top, uint32_t vocab_len, const int32_t* token_to_term,
+                                       int doc_mode, uint64_t* out_indptr, uint32_t* out_terms, uint32_t* out_weights,
+                                       void* stream) {
+    MSR_REQUIRE(dtype >= 0 && dtype <= 2, "msr_quantise_candidates: dtype %d outside {0 f32, 1 f16, 2 bf16}", dtype);
+    MSR_REQUIRE(cap >= 1 && cap <= (uint32_t)kQuantMaxTop && fallback_top >= 1 && fallback_top <= (uint32_t)kQuantMaxTop,
+                "msr_quantise_candidates: cap=%u / fallback_top=%u outside [1,%d]", cap, fallback_top, kQuantMaxTop);
+    MSR_REQUIRE(vocab >= fallback_top && row_stride >= vocab, "msr_quantise_candidates: vocab (%u) must be >= fallback_top and row_stride >= vocab", vocab);
+    MSR_REQUIRE(out_indptr, "msr_quantise_candidates: NULL out_indptr");
+    int rc = use_device(device);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (n_rows == 0) {
+        MSR_CUDA_CHECK(cudaMemsetAsync(out_indptr, 0, 8, s));
+        return MSR_OK;
+    }
+    MSR_REQUIRE(logits && out_terms && out_weights && cand_indptr_host, "msr_quantise_candidates: NULL buffer");
+    MSR_REQUIRE(cand_indptr_host[0] == 0, "msr_quantise_candidates: cand_indptr[0] != 0");
+    const uint64_t n_c = cand_indptr_host[n_rows];
+    MSR_REQUIRE(n_c == 0 || cand_tokens_host, "msr_quantise_candidates: NULL cand_tokens");
+    std::vector<uint32_t> empty_rows;
+    for (uint32_t r = 0; r < n_rows; ++r) {
+        MSR_REQUIRE(cand_indptr_host[r + 1] >= cand_indptr_host[r], "msr_quantise_candidates: cand_indptr not monotone at row %u", r);
+        const uint64_t m = cand_indptr_host[r + 1] - cand_indptr_host[r];
+        MSR_REQUIRE(m <= (uint64_t)kCandMax, "msr_quantise_candidates: row %u has %llu candidates (max %d)", r, (unsigned long long)m, kCandMax);
+        if (m == 0) empty_rows.push_back(r);
+    }
+    for (uint64_t i = 0; i < n_c; ++i)
+        MSR_REQUIRE(cand_tokens_host[i] >= 0 && (uint32_t)cand_tokens_host[i] < vocab,
+                    "msr_quantise_candidates: candidate token id %d outside [0,%u)", cand_tokens_host[i], vocab);
+    const uint32_t pitch = std::max(cap, fallback_top);
+    float* ts = nullptr; int32_t* td = nullptr; uint32_t* tc = nullptr; unsigned long long* ci = nullptr; int32_t* ct = nullptr;
+    float* f32 = nullptr;
+    MSR_CUDA_CHECK(cudaMallocAsync(&ts, (size_t)n_rows * pitch * 4, s));
+    MSR_CUDA_CHECK(cudaMallocAsync(&td, (size_t)n_rows * pitch * 4, s));
+    MSR_CUDA_CHECK(cudaMallocAsync(&tc, (size_t)n_rows * 4, s));
+    MSR_CUDA_CHECK(cudaMallocAsync(&ci, (size_t)(n_rows + 1) * 8, s));
+    MSR_CUDA_CHECK(cudaMallocAsync(&ct, (size_t)std::max<uint64_t>(n_c, 1) * 4, s));
+    MSR_CUDA_CHECK(cudaMemcpyAsync(ci, cand_indptr_host, (size_t)(n_rows + 1) * 8, cudaMemcpyHostToDevice, s));
+    if (n_c) MSR_CUDA_CHECK(cudaMemcpyAsync(ct, cand_tokens_host, (size_t)n_c * 4, cudaMemcpyHostToDevice, s));
+    if (dtype == 0) cand_select_kernel<float><<<n_rows, 128, 0, s>>>((const float*)logits, row_stride, ci, ct, cap, pitch, ts, td, tc);
+    else if (dtype == 1) cand_select_kernel<__half><<<n_rows, 128, 0, s>>>((const __half*)logits, row_stride, ci, ct, cap, pitch, ts, td, tc);
+    else cand_select_kernel<__nv_bfloat16><<<n_rows, 128, 0, s>>>((const __nv_bfloat16*)logits, row_stride, ci, ct, cap, pitch, ts, td, tc);
+    count_launch();
+    // rows without a candidate (encode.py:103-112): top-`fallback_top` of the whole vocabulary
+    if (!empty_rows.empty() && dtype != 0) MSR_CUDA_CHECK(cudaMallocAsync(&f32, (size_t)vocab * 4, s));
+    for (uint32_t r : empty_rows) {
+        const float* row = (const float*)logits + (size_t)r * row_stride;
+        if (dtype == 1) { rows_to_f32_kernel<__half><<<148, 256, 0, s>>>((const __half*)logits + (size_t)r * row_stride, row_stride, 1, vocab, f32); row = f32; count_launch(); }
+        if (dtype == 2) { rows_to_f32_kernel<__nv_bfloat16><<<148, 256, 0, s>>>((const __nv_bfloat16*)logits + (size_t)r * row_stride, row_stride, 1, vocab, f32); row = f32; count_launch(); }
+        rc = topk_rows_launch(1, vocab, row, vocab, fallback_top, 0, ts + (size_t)r * pitch, td + (size_t)r * pitch, tc + r, s);
+        if (rc) break;
+    }
+    if (rc == MSR_OK) {
+        const uint32_t wpb = 4;
+        quantise_map_kernel<<<(n_rows + wpb - 1) / wpb, wpb * 32, (size_t)wpb * 2 * pitch * 4, s>>>(
+            ts, td, tc, n_rows, pitch, vocab_len, token_to_term, doc_mode, (unsigned long long*)out_indptr, out_terms, out_weights);
+        count_launch();
+        if (cudaGetLastError() != cudaSuccess) { set_error("msr_quantise_candidates: launch failed"); rc = MSR_ERR_CUDA; }
+    }
+    // the host arrays were read by an async copy from pageable memory; make the call safe to return from
+    cudaStreamSynchronize(s);
+    if (f32) cudaFreeAsync(f32, s);
+    cudaFreeAsync(ts, s); cudaFreeAsync(td, s); cudaFreeAsync(tc, s); cudaFreeAsync(ci, s); cudaFreeAsync(ct, s);
     return rc;
 }

@@ -171,3 +171,18 @@ def fuse_statistic(runs, weights, device=None):
         fused[qid] = {names[fd[r, j]]: ResultRecord((np.float32(fs[r, j]) if (dense_f32 and fsrc[r, j] & 1) else float(fs[r, j])),
                                                     _TAGS[int(fsrc[r, j])]) for j in range(n)}
     return fused
+
+
+def provenance_histogram(runs, weights, depth=200, device=None):
+    """The rank-by-provenance statistic of /root/reference/src/score_statistic.py:393-417 (fuse_statistic, stable sort by
+    score, top-``depth``, 1-based ranks appended per tag) computed on the device as a by-product of kernel (d):
+    returns {'dense' | 'sparse' | 'fuse': int64 [depth]}, entry r = how many queries have a doc of that tag at rank r+1.
+    Expanding entry r into r+1 repeated that many times gives the reference's dense_list / sparse_list / fusion_list
+    up to order (they are only ever binned)."""
+    if len(runs) != 2 or len(weights) != 2:
+        raise NotImplementedError("provenance_histogram covers runs=[dense_run, sparse_run]")
+    qids, names, fs, fd, fsrc, fc, dense_f32 = _fuse_impl(runs, weights, device)
+    dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    hist = ops.provenance_hist(torch.from_numpy(fs).to(dev), torch.from_numpy(fsrc).to(dev), torch.from_numpy(fc).to(dev),
+                               depth).cpu().numpy()
+    return {"dense": hist[0], "sparse": hist[1], "fuse": hist[2]}

@@ -309,3 +309,65 @@ def quantise_topk(logits, top, token_to_term=None, vocab_len=None, doc_mode=Fals
                                             vocab_len, ptr(token_to_term), int(bool(doc_mode)), ptr(indptr), ptr(terms),
                                             ptr(weights), current_stream_ptr(di)))
     return indptr, terms, weights
+
+
+def text_token_ids(text, tokenizer, word_tokenize=None, stop_words=None):
+    """Host half of get_text_valid_tokens_values (/root/reference/src/encode.py:97-100, 103): lower-cased words minus
+    English stop-words and punctuation -> tokenizer.encode(word, add_special_tokens=False) -> list(set of token ids).
+
+    ``word_tokenize`` / ``stop_words`` default to nltk's (as in the reference); pass them explicitly where nltk is absent."""
+    import string
+    if word_tokenize is None or stop_words is None:
+        from nltk import word_tokenize as _wt                      # fails loudly when nltk is missing
+        from nltk.corpus import stopwords as _sw
+        word_tokenize = word_tokenize or _wt
+        stop_words = stop_words if stop_words is not None else _sw.words("english")
+    drop = set(list(stop_words) + list(string.punctuation))
+    words = [i for i in word_tokenize(text.lower()) if i not in drop]
+    token_ids = set()
+    for word in words:
+        token_ids.update(tokenizer.encode(word, add_special_tokens=False))
+    return list(token_ids)
+
+
+def quantise_candidates(logits, cand_lists, token_to_term=None, vocab_len=None, doc_mode=False, cap=128, fallback_top=10):
+    """Candidate branch of the text quantiser on the GPU (msr_quantise_candidates): activation rows + per-row candidate
+    token ids (``text_token_ids``) -> query CSR at pitch max(cap, fallback_top): (indptr i64 [n+1], terms i32, weights i32)."""
+    assert logits.is_cuda and logits.dim() == 2 and logits.stride(1) == 1 and logits.dtype in _DTYPES
+    n, V = logits.shape
+    assert len(cand_lists) == n
+    dev = logits.device
+    vocab_len = V if vocab_len is None else int(vocab_len)
+    if token_to_term is not None:
+        token_to_term = token_to_term.to(device=dev, dtype=torch.int32).contiguous()
+        assert token_to_term.numel() >= min(vocab_len, V)
+    c_indptr = np.zeros(n + 1, dtype=np.uint64)
+    np.cumsum([len(c) for c in cand_lists], out=c_indptr[1:])
+    c_tok = np.ascontiguousarray(np.concatenate([np.asarray(c, dtype=np.int64).reshape(-1) for c in cand_lists])
+                                 if n else np.zeros(0), dtype=np.int32)
+    pitch = max(int(cap), int(fallback_top))
+    indptr = torch.empty((n + 1,), dtype=torch.int64, device=dev)
+    terms = torch.empty((n * pitch,), dtype=torch.int32, device=dev)
+    weights = torch.empty((n * pitch,), dtype=torch.int32, device=dev)
+    di = _dev_index(dev)
+    with torch.cuda.device(di):
+        check(_lib.load().msr_quantise_candidates(
+            di, n, V, ptr(logits), _DTYPES[logits.dtype], logits.stride(0), c_indptr.ctypes.data, c_tok.ctypes.data,
+            int(cap), int(fallback_top), vocab_len, ptr(token_to_term), int(bool(doc_mode)), ptr(indptr), ptr(terms),
+            ptr(weights), current_stream_ptr(di)))
+    return indptr, terms, weights
+
+
+def provenance_hist(scores, src, counts, depth=200):
+    """score_statistic.py:406-417 on the device (msr_provenance_hist): fused (scores f64, src u8, counts) from
+    fuse_lists -> int64 [3, depth]; row 0/1/2 = dense-only / sparse-only / both, column r = rank r+1."""
+    nq = scores.shape[0]
+    dev = scores.device
+    assert scores.dtype == torch.float64 and src.dtype == torch.uint8 and scores.stride(1) == 1 and src.stride() == scores.stride()
+    hist = torch.empty((3, int(depth)), dtype=torch.int64, device=dev)
+    di = _dev_index(dev)
+    with torch.cuda.device(di):
+        check(_lib.load().msr_provenance_hist(di, nq, ptr(scores), ptr(src), scores.stride(0),
+                                              ptr(counts.to(torch.int32).contiguous()), int(depth), ptr(hist),
+                                              current_stream_ptr(di)))
+    return hist

@@ -5,7 +5,7 @@
 
 Pinned functions: hybrid.fuse / hybrid.fuse_statistic / hybrid.write_trec_run / hybrid.read_trec_run (hybrid.py),
 search.get_run_dict / search.sparse_search / search.search_queries (search.py:55-99) and
-encode.get_img_valid_tokens_values (encode.py:56-93); with ``--metrics`` RecallMetrics.sort_and_count
+encode.get_img_valid_tokens_values / get_text_valid_tokens_values (encode.py:56-153); with ``--metrics`` RecallMetrics.sort_and_count
 (metrices.py:29-84) -> reference_metrics.json.  Third-party modules that are absent here (faiss, tevatron,
 pyserini, nltk, peft) are stubbed in sys.modules exactly as SURVEY.md Appendix B describes; none of the pinned
 functions executes stub code except through the fake searcher objects handed to them below.
@@ -186,6 +186,63 @@ def make_quantiser_cases(encode, rng):
     return out
 
 
+
+class FakeTokenizer:
+    """word -> 0..3 token ids, deterministic; stands in for the HF tokenizer handed to get_text_valid_tokens_values."""
+    def __init__(self, V):
+        self.V = V
+
+    def encode(self, word, add_special_tokens=False):
+        h = sum((i + 1) * ord(c) for i, c in enumerate(word))
+        if word.startswith("oov"):
+            return []
+        n = 1 + h % 3
+        return [(h * 7 + j * 31) % self.V for j in range(n)]
+
+
+def make_text_quantiser_cases(encode):
+    """encode.get_text_valid_tokens_values (encode.py:96-153) with the stubbed nltk (word_tokenize = str.split,
+    stop-words = a/the/of) and FakeTokenizer; logits strictly positive and distinct so torch.topk has no ties."""
+    import string
+    import torch
+    rng = np.random.default_rng(20261106)
+    out = []
+    base = ["Dog", "dog", "Ġcat", "zebra", "▁Tree", "tree", "sky", "Sky", "x1", "##ing", "blue", "Blue"]
+    many = " ".join(f"w{i}" for i in range(140))
+    for text, sparse_manual, sparse_length, is_filtered, V, vlen in [
+            ("A dog of the blue Sky , runs !", False, 128, False, 200, 200),
+            ("the of a , .", False, 128, False, 200, 200),                      # no content word -> top-10 fallback
+            ("oovword the", False, 128, True, 200, 200),                       # words that tokenise to nothing
+            ("two dogs chase a zebra", True, 8, False, 200, 200),              # --sparse_manual
+            ("Trees and sky : tree Tree", False, 128, True, 200, 200),         # is_filtered
+            (many, False, 128, False, 400, 400),                               # > 128 candidates
+            ("a quick brown fox", False, 128, False, 200, 190),                # ids >= len(vocab_dict): value-shift quirk
+            ("the", False, 128, False, 200, 195)]:
+        vd = {i: (base[i] if i < len(base) else f"tok{i}") for i in range(vlen)}
+        logits = torch.tensor((np.log1p(np.abs(rng.standard_normal(V)) * 2.0) + 1e-3).astype(np.float32))
+        assert len(np.unique(logits.numpy())) == V
+        tok = FakeTokenizer(V)
+        data_args = types.SimpleNamespace(sparse_manual=sparse_manual, sparse_length=sparse_length, is_filtered=is_filtered,
+                                          num_expended_tokens=0)
+        tokens, values = encode.get_text_valid_tokens_values(text, tok, logits, vd, data_args, set())
+        # the candidate list the reference built internally, rebuilt the same way (same set -> same iteration order)
+        words = [i for i in text.lower().split() if i not in set(["a", "the", "of"] + list(string.punctuation))]
+        token_ids = set()
+        for w in words:
+            token_ids.update(tok.encode(w, add_special_tokens=False))
+        query = ""
+        for token, v in zip(tokens, values):
+            query += (" " + token) * v
+        vector = {}
+        for token, v in zip(tokens, values):
+            vector[token] = int(v)
+        out.append({"text": text, "sparse_manual": sparse_manual, "sparse_length": sparse_length, "is_filtered": is_filtered,
+                    "vocab": [vd[i] for i in range(vlen)], "logits": [float(x) for x in logits.numpy()],
+                    "token_ids": [int(t) for t in token_ids], "stop_words": ["a", "the", "of"],
+                    "tokens": tokens, "values": [int(v) for v in values], "query_string": query.strip(), "doc_vector": vector})
+    return out
+
+
 def make_metrics_cases():
     """RecallMetrics.sort_and_count (src/metrices.py:29-84) on random runs.  The class calls ``.cuda()`` on tiny tensors
     and ``dist.get_world_size()`` in its constructor; both are patched to CPU / 1 here, nothing else is touched."""
@@ -237,6 +294,7 @@ def main():
         "trec": make_trec_case(hybrid),
         "glue": make_glue_case(search),
         "quantiser": make_quantiser_cases(encode, rng),
+        "text_quantiser": make_text_quantiser_cases(encode),
     }
     with open(os.path.join(HERE, "reference_glue.json"), "w") as f:
         json.dump(golden, f)

@@ -151,3 +151,24 @@ def test_oracle_recall_counts_match_reference():
             docs = {q: (v if name == "fusion" else v["docs"]) for q, v in run.items()}
             got = oracle.recall_counts(docs, case["targets"])
             assert {str(k): v for k, v in got.items()} == case["counts"][name], (case["nq"], name)
+
+
+def test_text_quantiser_matches_reference(golden):
+    """Q2: oracle.quantise_text_row against encode.get_text_valid_tokens_values itself (all three branches, the
+    `i < len(vocab_dict)` quirk, > 128 candidates), and ops.text_token_ids against the reference's candidate set."""
+    from oracle.oracle import build_doc_vector, build_query_string, quantise_text_row
+    from mllm_sparse_retrieval_b200.ops import text_token_ids
+    sys_path_hack = os.path.join(os.path.dirname(__file__), "golden")
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("make_golden", os.path.join(sys_path_hack, "make_golden.py"))
+    mg = importlib.util.module_from_spec(spec); spec.loader.exec_module(mg)
+    assert len(golden["text_quantiser"]) >= 8
+    for c in golden["text_quantiser"]:
+        logits = np.asarray(c["logits"], dtype=np.float32)
+        cands = text_token_ids(c["text"], mg.FakeTokenizer(len(logits)), word_tokenize=lambda s: s.split(),
+                               stop_words=c["stop_words"])
+        assert cands == c["token_ids"]
+        toks, vals = quantise_text_row(logits, cands, c["vocab"], c["sparse_manual"], c["sparse_length"], c["is_filtered"])
+        assert toks == c["tokens"] and vals.tolist() == c["values"]
+        assert build_query_string(toks, vals) == c["query_string"]
+        assert build_doc_vector(toks, vals) == c["doc_vector"]

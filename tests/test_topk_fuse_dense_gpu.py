@@ -83,6 +83,17 @@ def test_fuse_matches_reference_semantics(oracle, lib_built, remove_query, alpha
         for j, doc in enumerate(e.keys()):
             tag = (1 if doc in dense_run[qid]["docs"] else 0) | (2 if doc in sparse_run[qid]["docs"] else 0)
             assert fsrc[q, j] == tag
+    # provenance histogram (score_statistic.py:406-417) of the same fused lists, quantised ties included
+    from collections import Counter
+    from mllm_sparse_retrieval_b200.ops import fuse_lists as _fl, provenance_hist
+    tags = oracle.fuse_tags([dense_run, sparse_run])
+    for depth in (200, 7):
+        fs_d, fd_d, fsrc_d, fc_d = _fl(t(d_s), t(d_d), t(d_c), t(s_s), t(s_d), t(s_c), t(self_ids), remove_query, alpha, 1 - alpha)
+        hist = provenance_hist(fs_d, fsrc_d, fc_d, depth).cpu().numpy()
+        lists = oracle.provenance_lists({qid: {doc: (exp[qid][doc], tags[qid][doc]) for doc in exp[qid]} for qid in qids}, depth)
+        for row, lst in enumerate(lists):
+            c = Counter(lst)
+            assert hist[row].tolist() == [c.get(r + 1, 0) for r in range(depth)]
 
 
 @pytest.mark.parametrize("n_docs,dim,nq,k", [(1000, 4096, 7, 10), (5000, 4096, 33, 100), (300, 100, 5, 1000), (2000, 3584, 4, 100)])
@@ -315,3 +326,54 @@ def test_recall_hits_kernel_matches_reference_fixtures(lib_built):
             hits, n_eval = recall_hits(docs.cuda(), counts.cuda(), torch.tensor(indptr), torch.tensor(flat, dtype=torch.int32))
             assert {str(k): int(h) for k, h in zip(RECALL_CUTOFFS, hits.cpu())} == case["counts"][name], (nq, name)
             assert int(n_eval) == sum(1 for x in lists if x)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+def test_quantise_candidates_matches_reference_fixtures(oracle, lib_built, dtype):
+    """msr_quantise_candidates (Q2, candidate branch + empty-caption fallback) against fixtures generated from the
+    reference's own get_text_valid_tokens_values + query-string / doc-vector builders; all captions in ONE batch."""
+    import json, os
+    from collections import Counter
+    from mllm_sparse_retrieval_b200.index import ImpactCollection
+    from mllm_sparse_retrieval_b200.ops import quantise_candidates
+    with open(os.path.join(os.path.dirname(__file__), "golden", "reference_glue.json")) as f:
+        cases = [c for c in json.load(f)["text_quantiser"] if not c["sparse_manual"]]
+    assert len(cases) >= 7
+    by_shape = {}
+    for c in cases:
+        by_shape.setdefault((len(c["logits"]), len(c["vocab"]), c["is_filtered"]), []).append(c)
+    for (V, vlen, filt), group in by_shape.items():
+        vocab = group[0]["vocab"]
+        names = sorted({v.lower() for v in vocab} | {v.lower()[1:] for v in vocab if len(v) > 1})
+        coll = ImpactCollection.from_vectors(["d"], [{n: 1 for n in names}])
+        tmap = torch.from_numpy(coll.token_to_term_map(vocab, is_filtered=filt)).cuda()
+        x = torch.tensor([c["logits"] for c in group], dtype=torch.float32).cuda().to(dtype)
+        if dtype != torch.float32:                          # the fixture is fp32: compare with the oracle on the rounded row
+            exp = []
+            for r, c in enumerate(group):
+                toks, vals = oracle.quantise_text_row(x[r].float().cpu().numpy(), c["token_ids"], vocab, False, 128, filt)
+                exp.append((oracle.build_query_string(toks, vals), oracle.build_doc_vector(toks, vals)))
+        else:
+            exp = [(c["query_string"], c["doc_vector"]) for c in group]
+        for doc_mode in (False, True):
+            ip, t, w = quantise_candidates(x, [c["token_ids"] for c in group], tmap, vocab_len=vlen, doc_mode=doc_mode)
+            ip, t, w = ip.cpu().numpy(), t.cpu().numpy(), w.cpu().numpy()
+            assert ip.tolist() == [128 * r for r in range(len(group) + 1)]
+            for r, (qs, dv) in enumerate(exp):
+                got = _csr_row_to_dict(coll, ip, t, w, r)
+                want = {k: v for k, v in dv.items() if v > 0} if doc_mode else dict(Counter(qs.split()))
+                assert got == want, (group[r]["text"], doc_mode)
+
+
+@pytest.mark.gpu
+def test_quantise_candidates_rejects_bad_input(lib_built):
+    from mllm_sparse_retrieval_b200._lib import MsrError
+    from mllm_sparse_retrieval_b200.ops import quantise_candidates
+    x = torch.rand(2, 64, device="cuda")
+    with pytest.raises(MsrError):
+        quantise_candidates(x, [[1, 2], [64]])                       # token id outside the vocabulary
+    with pytest.raises(MsrError):
+        quantise_candidates(x, [[1], [2]], fallback_top=100)          # fallback larger than the vocabulary
+    ip, t, w = quantise_candidates(x[:0], [])
+    assert ip.tolist() == [0]
