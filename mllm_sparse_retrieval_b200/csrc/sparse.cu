@@ -60,6 +60,9 @@ struct msr_sparse_index {
     uint32_t* term_maximp = nullptr;  // [n_terms]
     uint32_t* dense_id = nullptr;     // [n_terms] row of a dense term in dense_rows, kNotDense otherwise
     uint16_t* dense_rows = nullptr;   // [n_dense][dense_stride] impact of the term in every doc of the shard (0 = absent)
+    uint8_t* dense_rows8 = nullptr;   // [n_dense][dense_stride] min(impact, 255); the rest (impact - 255) is an ordinary
+                                      // posting of the term's (tile, term) bucket, so row + bucket add up to the impact
+    uint32_t* dense_cursor = nullptr; // build-time only
     uint32_t n_dense = 0;
     size_t dense_stride = 0;
     uint32_t* df_local = nullptr;     // [n_terms]
@@ -94,8 +97,8 @@ __device__ __forceinline__ uint32_t term_of_posting(const uint64_t* __restrict__
 __global__ void build_count_kernel(const uint64_t* __restrict__ indptr, const uint32_t* __restrict__ docids,
                                    const uint16_t* __restrict__ impacts, uint64_t nnz, uint32_t n_terms,
                                    uint32_t n_docs, uint32_t tile_docs, const uint32_t* __restrict__ dense_id,
-                                   uint16_t* __restrict__ dense_rows, size_t dense_stride, uint32_t* __restrict__ cnt,
-                                   uint32_t* __restrict__ maximp, uint32_t* __restrict__ bad) {
+                                   uint16_t* __restrict__ dense_rows, uint8_t* __restrict__ dense_rows8, size_t dense_stride,
+                                   uint32_t* __restrict__ cnt, uint32_t* __restrict__ maximp, uint32_t* __restrict__ bad) {
     for (uint64_t p = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; p < nnz; p += (uint64_t)gridDim.x * blockDim.x) {
         uint32_t t = term_of_posting(indptr, n_terms, p);
         uint32_t d = docids[p];
@@ -103,8 +106,13 @@ __global__ void build_count_kernel(const uint64_t* __restrict__ indptr, const ui
         if (d >= n_docs || imp == 0) { atomicOr(bad, 1u); continue; }
         if (p > indptr[t] && docids[p - 1] >= d) atomicOr(bad, 2u);
         const uint32_t di = dense_id[t];
-        if (di != kNotDense) dense_rows[(size_t)di * dense_stride + d] = (uint16_t)imp;
-        else atomicAdd(&cnt[(size_t)(d / tile_docs) * n_terms + t], 1u);
+        if (di != kNotDense) {
+            dense_rows[(size_t)di * dense_stride + d] = (uint16_t)imp;
+            dense_rows8[(size_t)di * dense_stride + d] = (uint8_t)min(imp, 255u);
+            if (imp > 255u) atomicAdd(&cnt[(size_t)(d / tile_docs) * n_terms + t], 1u);
+        } else {
+            atomicAdd(&cnt[(size_t)(d / tile_docs) * n_terms + t], 1u);
+        }
         atomicMax(&maximp[t], imp);
     }
 }
@@ -112,13 +120,24 @@ __global__ void build_count_kernel(const uint64_t* __restrict__ indptr, const ui
 __global__ void build_scatter_kernel(const uint64_t* __restrict__ indptr, const uint32_t* __restrict__ docids,
                                      const uint16_t* __restrict__ impacts, uint64_t nnz, uint32_t n_terms,
                                      uint32_t tile_docs, const uint32_t* __restrict__ dense_id,
-                                     const uint32_t* __restrict__ seg_ptr, uint32_t* __restrict__ postings) {
+                                     const uint32_t* __restrict__ seg_ptr, uint32_t* __restrict__ postings,
+                                     uint32_t n_dense, uint32_t* __restrict__ dense_cursor) {
     for (uint64_t p = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; p < nnz; p += (uint64_t)gridDim.x * blockDim.x) {
         uint32_t t = term_of_posting(indptr, n_terms, p);
-        if (dense_id[t] != kNotDense) continue;
         uint32_t d = docids[p];
         uint32_t tile = d / tile_docs;
         uint32_t tile_lo = tile * tile_docs;
+        const uint32_t di = dense_id[t];
+        if (di != kNotDense) {
+            // dense term: only the part of an impact above 255 is a posting; slot order inside the bucket is
+            // arbitrary (integer adds commute, the layout pass re-orders by bank anyway)
+            const uint32_t imp = impacts[p];
+            if (imp > 255u) {
+                const uint32_t r = atomicAdd(&dense_cursor[(size_t)tile * n_dense + di], 1u);
+                postings[seg_ptr[(size_t)tile * n_terms + t] + r] = ((imp - 255u) << 16) | (d - tile_lo);
+            }
+            continue;
+        }
         // first posting of term t whose doc >= tile_lo
         uint64_t lo = indptr[t], hi = p;   // docids[p] >= tile_lo, so the answer is in [lo, p]
         while (lo < hi) {
@@ -379,8 +398,15 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
         h->n_dense = 0;
     }
     if (h->n_dense) {
-        if ((e = cudaMalloc(&h->dense_rows, (size_t)h->n_dense * h->dense_stride * 2)) != cudaSuccess) return fail("alloc dense rows");
-        cudaMemsetAsync(h->dense_rows, 0, (size_t)h->n_dense * h->dense_stride * 2, s);
+        if ((e = cudaMalloc(&h->dense_rows, (size_t)h->n_dense * h->dense_stride * 2 + (size_t)kThreads * 16 + 16)) != cudaSuccess) return fail("alloc dense rows");
+        cudaMemsetAsync(h->dense_rows, 0, (size_t)h->n_dense * h->dense_stride * 2 + (size_t)kThreads * 16 + 16, s);
+        // the kernel loads two slots per thread, the second kThreads slots further on, without a bounds test (the
+        // values are dropped): keep those loads inside the allocations
+        const size_t pad8 = (size_t)kThreads * 8 + 16, pad16 = (size_t)kThreads * 16 + 16;
+        if ((e = cudaMalloc(&h->dense_rows8, (size_t)h->n_dense * h->dense_stride + pad8)) != cudaSuccess) return fail("alloc dense rows (u8)");
+        cudaMemsetAsync(h->dense_rows8, 0, (size_t)h->n_dense * h->dense_stride + pad8, s);
+        if ((e = cudaMalloc(&h->dense_cursor, (size_t)h->n_dense * n_tiles * 4)) != cudaSuccess) return fail("alloc dense cursor");
+        cudaMemsetAsync(h->dense_cursor, 0, (size_t)h->n_dense * n_tiles * 4, s);
     }
     if ((e = b_stage.alloc((nnz ? nnz : 1) * 4)) != cudaSuccess) return fail("alloc stage");
 
@@ -388,7 +414,7 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
     const int grid = (int)std::min<uint64_t>((nnz + bt - 1) / bt, 148ull * 32);
     if (nnz) {
         build_count_kernel<<<grid, bt, 0, s>>>(d_indptr, d_docids, d_impacts, nnz, n_terms, n_docs, tile_docs, h->dense_id,
-                                               h->dense_rows, h->dense_stride, b_cnt.as<uint32_t>(), h->term_maximp,
+                                               h->dense_rows, h->dense_rows8, h->dense_stride, b_cnt.as<uint32_t>(), h->term_maximp,
                                                b_bad.as<uint32_t>());
         count_launch();
     }
@@ -407,7 +433,8 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
     if ((e = cub::DeviceScan::ExclusiveSum(b_tmp.p, tmp_bytes, b_cnt.as<uint32_t>(), seg0, n_seg, s)) != cudaSuccess)
         return fail("bucket scan");
     if (nnz) {
-        build_scatter_kernel<<<grid, bt, 0, s>>>(d_indptr, d_docids, d_impacts, nnz, n_terms, tile_docs, h->dense_id, seg0, stage);
+        build_scatter_kernel<<<grid, bt, 0, s>>>(d_indptr, d_docids, d_impacts, nnz, n_terms, tile_docs, h->dense_id, seg0, stage,
+                                                 h->n_dense, h->dense_cursor);
         count_launch();
     }
     // 3. final layout: slots per bucket (large buckets are padded to whole conflict-free groups), scan, write
@@ -434,11 +461,12 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
     h->n_slots = n_slots64;
     if ((e = cudaMalloc(&h->postings, (h->n_slots ? h->n_slots : 1) * 4)) != cudaSuccess) return fail("alloc postings");
     h->resident_bytes = n_seg * 4 + (h->n_slots ? h->n_slots : 1) * 4 + n_terms * 13ull + 20 +
-                        (size_t)h->n_dense * h->dense_stride * 2;
+                        (size_t)h->n_dense * h->dense_stride * 3;
     build_layout_kernel<<<lgrid, kBuildWarps * 32, 0, s>>>(seg0, stage, n_buckets, h->seg_ptr, h->postings);
     count_launch();
     if ((e = cudaStreamSynchronize(s)) != cudaSuccess) return fail("build kernels");
     if ((e = cudaGetLastError()) != cudaSuccess) return fail("build kernels (launch)");
+    cudaFree(h->dense_cursor); h->dense_cursor = nullptr;
     e = cudaFuncSetAttribute(sparse_score_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              (int)search_smem_bytes(kMaxTileDocs));
     if (e != cudaSuccess) return fail("opt-in shared memory");
@@ -451,6 +479,7 @@ extern "C" int msr_sparse_index_destroy(msr_sparse_index* h) {
     cudaSetDevice(h->device);
     cudaFree(h->seg_ptr); cudaFree(h->postings); cudaFree(h->term_keep); cudaFree(h->term_maximp);
     cudaFree(h->df_local); cudaFree(h->status); cudaFree(h->work); cudaFree(h->dense_id); cudaFree(h->dense_rows);
+    cudaFree(h->dense_rows8); cudaFree(h->dense_cursor);
     h->ws.release();
     for (cudaEvent_t e : h->ev) cudaEventDestroy(e);
     delete h;
@@ -571,6 +600,7 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     P.doc_base = h->doc_base; P.q_indptr = d_qi; P.q_terms = d_qt; P.q_weights = d_qw; P.q_ok = d_ok;
     P.dense_id = h->dense_id; P.dense_rows = h->dense_rows; P.dense_stride = h->dense_stride;
     P.dense_row_bytes = (uint32_t)(h->dense_stride * 2);
+    P.dense_rows8 = h->dense_rows8;
     P.k = k; P.k_stride = k_stride;
     P.cand_keys = (uint64_t*)(base + off_keys); P.cand_cnt = (uint32_t*)(base + off_cnt);
     P.theta = (unsigned long long*)(base + off_theta); P.tlist = (uint64_t*)(base + off_tlist);

@@ -42,6 +42,7 @@ struct SearchParams {
     const uint32_t* term_maximp;
     const uint32_t* dense_id;     // [n_terms]
     const uint16_t* dense_rows;   // [n_dense][dense_stride]
+    const uint8_t* dense_rows8;   // [n_dense][dense_stride] min(impact, 255); the remainder is a bucket posting
     size_t dense_stride;
     uint32_t dense_row_bytes;     // dense_stride * 2 (all rows together stay below 4 GiB)
     const uint8_t* q_ok;          // [nq_total] 1 = inside the exact-arithmetic range
@@ -90,6 +91,11 @@ __device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t* p) {
 __device__ __forceinline__ void red_shared_add(uint32_t saddr, uint32_t val) {
     asm volatile("red.shared.add.u32 [%0], %1;" ::"r"(saddr), "r"(val) : "memory");
 }
+// One posting slot v = impact << 16 | doc offset, weight below 256 given as wb = w << 24:
+// address = acc_s + 4 * offset and value = impact * w, one dp2a each (bytes (4,0,0,w) of `wb | 4`).
+__device__ __forceinline__ void scatter_fast(uint32_t acc_s, uint32_t v, uint32_t wb4) {
+    red_shared_add(__dp2a_lo(v, wb4, acc_s), __dp2a_hi(v, wb4, 0u));
+}
 
 struct SegStage {                      // streaming phase view of the union region
     uint32_t start[kSegMax];
@@ -100,6 +106,7 @@ struct SegStage {                      // streaming phase view of the union regi
     // terms that need the per-term float32 rounding of S6 from the back.
     alignas(16) uint32_t drow[kSegMax];
     alignas(16) uint32_t dw[kSegMax];
+    alignas(16) uint4 db[kSegMax];     // front list: (w, w << 8, w << 16, w << 24), the dp4a selectors of the weight
 };
 struct SelStage {                      // radix-select view
     uint32_t hist[kBins];
@@ -123,12 +130,25 @@ __device__ __forceinline__ uint4 ld_stream_v4(const void* p) {
     return v;
 }
 
-// a[0..7] += w * (8 u16 impacts packed in v)
-__device__ __forceinline__ void dense_fma8(uint32_t (&a)[8], const uint4 v, const uint32_t w) {
+// a[0..7] += w * (8 u16 impacts packed in v), any w below 2^16: unpack (ALU pipe) + IMAD (FMA pipe) per impact
+__device__ __forceinline__ void dense_fma8_wide(uint32_t (&a)[8], const uint4 v, const uint32_t w) {
     a[0] += (v.x & 0xFFFFu) * w; a[1] += (v.x >> 16) * w;
     a[2] += (v.y & 0xFFFFu) * w; a[3] += (v.y >> 16) * w;
     a[4] += (v.z & 0xFFFFu) * w; a[5] += (v.z >> 16) * w;
     a[6] += (v.w & 0xFFFFu) * w; a[7] += (v.w >> 16) * w;
+}
+// Weight below 256 on the u8 rows: ONE instruction per impact.  dp4a multiplies the four u8 of its first operand by
+// the four u8 of the second and adds a 32-bit accumulator (SASS IDP.4A.U8.U8, same issue rate as IMAD on sm_100a --
+// scratch/idp_bench.cu); with the weight in byte i of the selector and zeros elsewhere it yields a + impact_i * w,
+// without any mask / shift instruction on the ALU pipe.  v = impacts of 8 consecutive docs.
+__device__ __forceinline__ void dense_dp4a8(uint32_t (&a)[8], const uint2 v, const uint4 b) {
+    a[0] = __dp4a(v.x, b.x, a[0]); a[1] = __dp4a(v.x, b.y, a[1]); a[2] = __dp4a(v.x, b.z, a[2]); a[3] = __dp4a(v.x, b.w, a[3]);
+    a[4] = __dp4a(v.y, b.x, a[4]); a[5] = __dp4a(v.y, b.y, a[5]); a[6] = __dp4a(v.y, b.z, a[6]); a[7] = __dp4a(v.y, b.w, a[7]);
+}
+__device__ __forceinline__ uint2 ld_stream_v2(const void* p) {
+    uint2 v;
+    asm("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
+    return v;
 }
 
 // exclusive scan of one value per thread over the CTA (kThreads threads); returns exclusive prefix, *total = sum
@@ -164,6 +184,50 @@ __device__ __forceinline__ void score_chunk_generic(const uint32_t* src, uint32_
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u)
             if (u * 32 + lane < n) red_shared_add(acc_s + (v[u] & 0xFFFFu) * 4u, (uint32_t)__uint2float_rn((v[u] >> 16) * w));
+    }
+}
+
+// chunks [0,nc) of one bucket for one warp: full chunks software-pipelined, then the lane-predicated tail.
+// FAST: w = weight << 24 | 4 (dp2a form, weight < 256); else w = weight (< 2^16) and the posting is unpacked.
+template <bool FAST>
+__device__ __forceinline__ void scatter_one(uint32_t acc_s, uint32_t v, uint32_t w) {
+    if (FAST) scatter_fast(acc_s, v, w);
+    else red_shared_add(acc_s + (v & 0xFFFFu) * 4u, (v >> 16) * w);
+}
+template <bool FAST>
+__device__ __forceinline__ void scatter_chunks(const uint32_t*& src, uint32_t& left, uint32_t& nc, const uint32_t w,
+                                               const uint32_t lane, const uint32_t acc_s) {
+    uint32_t nfull = min(nc, left / kChunk);
+    if (nfull) {
+        uint32_t v[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) v[u] = ld_stream_u32(src + u * 32);
+        for (uint32_t c = 1; c < nfull; ++c) {                  // software pipeline: next chunk's loads in flight
+            uint32_t nx[kUnroll];
+            src += kChunk;
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u) nx[u] = ld_stream_u32(src + u * 32);
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u) scatter_one<FAST>(acc_s, v[u], w);
+#pragma unroll
+            for (int u = 0; u < kUnroll; ++u) v[u] = nx[u];
+        }
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) scatter_one<FAST>(acc_s, v[u], w);
+        src += kChunk;
+        left -= nfull * kChunk;
+        nc -= nfull;
+    }
+    for (; nc; --nc) {                                          // bucket tail / small bucket
+        const uint32_t n = min((uint32_t)kChunk, left);
+        uint32_t v[kUnroll];
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) v[u] = (u * 32 + lane < n) ? ld_stream_u32(src + u * 32) : 0u;
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+            if (u * 32 + lane < n) scatter_one<FAST>(acc_s, v[u], w);
+        src += kChunk;
+        left -= n;
     }
 }
 
@@ -214,9 +278,21 @@ sparse_score_topk_kernel(const SearchParams P) {
                         // S6: float32(boost*freq) rounds once a product can reach 2^24 -> flag the term (bit 31)
                         if ((uint64_t)w * mi >= (1u << 24)) w |= 0x80000000u;
                         if (di != kNotDense) {
-                            const uint32_t pos = (w >> 31) ? kSegMax - 1 - atomicAdd(&S->n_dense_f, 1u) : atomicAdd(&S->n_dense, 1u);
-                            U->seg.drow[pos] = di * P.dense_row_bytes;
-                            U->seg.dw[pos] = w & 0x7FFFFFFFu;
+                            // front list: weights below 256 (dp2a form, stored as w | w << 24); back list: wider
+                            // weights (IMAD form) and S6 terms (bit 31 kept)
+                            // back list: u16 rows hold the whole impact.  Front list: u8 rows hold min(impact, 255)
+                            // and the term's bucket the rest, so the bucket is scattered as well.
+                            const bool fast = w < 256u;
+                            const uint32_t pos = fast ? atomicAdd(&S->n_dense, 1u) : kSegMax - 1 - atomicAdd(&S->n_dense_f, 1u);
+                            if (fast) {
+                                U->seg.drow[pos] = di * (P.dense_row_bytes >> 1);
+                                U->seg.db[pos] = make_uint4(w, w << 8, w << 16, w << 24);
+                                start = s0;
+                                len = s1 - s0;
+                            } else {
+                                U->seg.drow[pos] = di * P.dense_row_bytes;
+                                U->seg.dw[pos] = w;
+                            }
                         } else {
                             start = s0;
                             len = s1 - s0;
@@ -240,45 +316,74 @@ sparse_score_topk_kernel(const SearchParams P) {
             if (first || nd || ndf) {
                 const uint32_t nslots = (tl + 7) >> 3;          // 8 docs per thread and step
                 const char* rows = reinterpret_cast<const char*>(P.dense_rows + tile_lo);
-                for (uint32_t slot = tid; slot < nslots; slot += kThreads) {
-                    uint32_t a[8];
+                const char* rows8 = reinterpret_cast<const char*>(P.dense_rows8 + tile_lo);
+                // Two slots per thread and step (slot, slot + kThreads): the second one is reached with an immediate
+                // offset, so one address computation serves two loads and 8 loads are in flight per thread.
+                for (uint32_t slot = tid; slot < nslots; slot += 2 * kThreads) {
+                    const bool two = slot + kThreads < nslots;  // else the second slot's loads are dummies (row padding)
+                    uint32_t a[8], c[8];
                     uint4* ap = reinterpret_cast<uint4*>(acc + 8 * slot);
+                    uint4* cp = ap + 2 * kThreads;
                     if (first) {
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) a[i] = 0;
+                        for (int i = 0; i < 8; ++i) { a[i] = 0; c[i] = 0; }
                     } else {
                         const uint4 x = ap[0], y = ap[1];
                         a[0] = x.x; a[1] = x.y; a[2] = x.z; a[3] = x.w; a[4] = y.x; a[5] = y.y; a[6] = y.z; a[7] = y.w;
+                        if (two) {
+                            const uint4 x2 = cp[0], y2 = cp[1];
+                            c[0] = x2.x; c[1] = x2.y; c[2] = x2.z; c[3] = x2.w; c[4] = y2.x; c[5] = y2.y; c[6] = y2.z; c[7] = y2.w;
+                        }
                     }
-                    const uint32_t so = slot * 16u;             // row offsets are 32-bit byte offsets (checked at build)
+                    const char* r8 = rows8 + slot * 8u;         // u8 rows: 8 docs = 8 bytes
+                    constexpr uint32_t kB8 = kThreads * 8u;     // byte distance of the second slot in a u8 row
                     uint32_t d = 0;
-                    for (; d + 4 <= nd; d += 4) {               // 4 independent 16-byte loads in flight per thread
+                    for (; d + 4 <= nd; d += 4) {
                         const uint4 r = *reinterpret_cast<const uint4*>(&U->seg.drow[d]);
-                        const uint4 w = *reinterpret_cast<const uint4*>(&U->seg.dw[d]);
-                        const uint4 v0 = ld_stream_v4(rows + (r.x + so)), v1 = ld_stream_v4(rows + (r.y + so));
-                        const uint4 v2 = ld_stream_v4(rows + (r.z + so)), v3 = ld_stream_v4(rows + (r.w + so));
-                        dense_fma8(a, v0, w.x); dense_fma8(a, v1, w.y); dense_fma8(a, v2, w.z); dense_fma8(a, v3, w.w);
+                        const uint2 v0 = ld_stream_v2(r8 + r.x), v1 = ld_stream_v2(r8 + r.y);
+                        const uint2 v2 = ld_stream_v2(r8 + r.z), v3 = ld_stream_v2(r8 + r.w);
+                        const uint2 u0 = ld_stream_v2(r8 + r.x + kB8), u1 = ld_stream_v2(r8 + r.y + kB8);
+                        const uint2 u2 = ld_stream_v2(r8 + r.z + kB8), u3 = ld_stream_v2(r8 + r.w + kB8);
+                        uint4 b = U->seg.db[d];
+                        dense_dp4a8(a, v0, b); dense_dp4a8(c, u0, b);
+                        b = U->seg.db[d + 1];
+                        dense_dp4a8(a, v1, b); dense_dp4a8(c, u1, b);
+                        b = U->seg.db[d + 2];
+                        dense_dp4a8(a, v2, b); dense_dp4a8(c, u2, b);
+                        b = U->seg.db[d + 3];
+                        dense_dp4a8(a, v3, b); dense_dp4a8(c, u3, b);
                     }
-                    if (nd & 2) {
-                        const uint2 r = *reinterpret_cast<const uint2*>(&U->seg.drow[d]);
-                        const uint2 w = *reinterpret_cast<const uint2*>(&U->seg.dw[d]);
-                        const uint4 v0 = ld_stream_v4(rows + (r.x + so)), v1 = ld_stream_v4(rows + (r.y + so));
-                        dense_fma8(a, v0, w.x); dense_fma8(a, v1, w.y);
-                        d += 2;
+                    for (; d < nd; ++d) {
+                        const uint32_t r = U->seg.drow[d];
+                        const uint2 v0 = ld_stream_v2(r8 + r), u0 = ld_stream_v2(r8 + r + kB8);
+                        const uint4 b = U->seg.db[d];
+                        dense_dp4a8(a, v0, b); dense_dp4a8(c, u0, b);
                     }
-                    if (nd & 1) dense_fma8(a, ld_stream_v4(rows + (U->seg.drow[d] + so)), U->seg.dw[d]);
-                    for (uint32_t f = 0; f < ndf; ++f) {        // S6: float32(boost*freq) per term
-                        const uint4 v = ld_stream_v4(rows + (U->seg.drow[kSegMax - 1 - f] + so));
-                        const uint32_t w = U->seg.dw[kSegMax - 1 - f];
-                        const uint32_t e[4] = {v.x, v.y, v.z, v.w};
+                    const char* r16 = rows + slot * 16u;        // u16 rows (row offsets are 32-bit byte offsets)
+                    constexpr uint32_t kB16 = kThreads * 16u;
+                    for (uint32_t f = 0; f < ndf; ++f) {        // weights of 256 and more; S6 terms
+                        const uint32_t r = U->seg.drow[kSegMax - 1 - f];
+                        const uint4 v = ld_stream_v4(r16 + r), u = ld_stream_v4(r16 + r + kB16);
+                        const uint32_t wr = U->seg.dw[kSegMax - 1 - f], w = wr & 0x7FFFFFFFu;
+                        if (!(wr >> 31)) {
+                            dense_fma8_wide(a, v, w); dense_fma8_wide(c, u, w);
+                        } else {                                // S6: float32(boost*freq) per term
+                            const uint32_t e[4] = {v.x, v.y, v.z, v.w}, g[4] = {u.x, u.y, u.z, u.w};
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) {
-                            a[2 * i] += (uint32_t)__uint2float_rn((e[i] & 0xFFFFu) * w);
-                            a[2 * i + 1] += (uint32_t)__uint2float_rn((e[i] >> 16) * w);
+                            for (int i = 0; i < 4; ++i) {
+                                a[2 * i] += (uint32_t)__uint2float_rn((e[i] & 0xFFFFu) * w);
+                                a[2 * i + 1] += (uint32_t)__uint2float_rn((e[i] >> 16) * w);
+                                c[2 * i] += (uint32_t)__uint2float_rn((g[i] & 0xFFFFu) * w);
+                                c[2 * i + 1] += (uint32_t)__uint2float_rn((g[i] >> 16) * w);
+                            }
                         }
                     }
                     ap[0] = make_uint4(a[0], a[1], a[2], a[3]);
                     ap[1] = make_uint4(a[4], a[5], a[6], a[7]);
+                    if (two) {
+                        cp[0] = make_uint4(c[0], c[1], c[2], c[3]);
+                        cp[1] = make_uint4(c[4], c[5], c[6], c[7]);
+                    }
                 }
             }
         }
@@ -312,28 +417,9 @@ sparse_score_topk_kernel(const SearchParams P) {
             g = sb + c1;
             ++seg;
             if (!(wraw >> 31)) {
-                const uint32_t w = wraw;
-                uint32_t nfull = min(nc, left / kChunk);
-                if (nfull) {
-                    uint32_t v[kUnroll];
-#pragma unroll
-                    for (int u = 0; u < kUnroll; ++u) v[u] = ld_stream_u32(src + u * 32);
-                    for (uint32_t c = 1; c < nfull; ++c) {      // software pipeline: next chunk's loads in flight
-                        uint32_t nx[kUnroll];
-                        src += kChunk;
-#pragma unroll
-                        for (int u = 0; u < kUnroll; ++u) nx[u] = ld_stream_u32(src + u * 32);
-#pragma unroll
-                        for (int u = 0; u < kUnroll; ++u) red_shared_add(acc_s + (v[u] & 0xFFFFu) * 4u, (v[u] >> 16) * w);
-#pragma unroll
-                        for (int u = 0; u < kUnroll; ++u) v[u] = nx[u];
-                    }
-#pragma unroll
-                    for (int u = 0; u < kUnroll; ++u) red_shared_add(acc_s + (v[u] & 0xFFFFu) * 4u, (v[u] >> 16) * w);
-                    src += kChunk;
-                    left -= nfull * kChunk;
-                    nc -= nfull;
-                }
+                // weight below 256 (the common case): dp2a form; wider weights: mask / shift / IMAD form
+                if (wraw < 256u) scatter_chunks<true>(src, left, nc, (wraw << 24) | 4u, lane, acc_s);
+                else scatter_chunks<false>(src, left, nc, wraw, lane, acc_s);
             }
             for (; nc; --nc) {
                 const uint32_t n = min((uint32_t)kChunk, left);
