@@ -6,6 +6,7 @@ import os
 
 PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(PKG, "libmsr.so")
+LIB_PATH = os.environ.get("MSR_LIB_PATH", LIB_PATH)      # developer knob: a variant build of the same library
 
 MSR_HOST, MSR_DEVICE = 0, 1
 MSR_MAX_K = 4096

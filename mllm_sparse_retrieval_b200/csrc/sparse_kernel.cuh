@@ -19,7 +19,13 @@
 
 namespace msr {
 
-constexpr int kThreads = 512;
+#ifndef MSR_SPARSE_THREADS
+#define MSR_SPARSE_THREADS 512
+#endif
+#ifndef MSR_SPARSE_MIN_CTAS
+#define MSR_SPARSE_MIN_CTAS 2
+#endif
+constexpr int kThreads = MSR_SPARSE_THREADS;
 constexpr int kWarps = kThreads / 32;
 constexpr int kSegMax = 256;      // query terms staged per pass
 constexpr int kUnroll = 8;        // loads in flight per lane
@@ -29,6 +35,7 @@ constexpr int kBinBits = 11;
 constexpr int kCandMax = 1024;
 constexpr uint32_t kNotDense = 0xFFFFFFFFu;   // dense_id of a term that is stored as posting buckets
 constexpr int kUnionMax = 2048;   // keys the threshold merge can sort (own candidates + k)
+constexpr int kPer = 2048 / kThreads;   // bins / union keys per thread in the CTA-wide scans
 
 struct SearchParams {
     const uint32_t* seg_ptr;
@@ -119,7 +126,8 @@ union StageUnion {
 };
 struct SmallState {
     uint32_t vmax, hits, out_cnt, cand_cnt, sel_b, sel_clt, sel_bcount, n_dense;
-    uint32_t n_dense_f, pad[3];
+    uint32_t n_dense_f, pad;
+    unsigned long long theta;          // the query's threshold as ONE thread read it (see phase 2a)
     uint32_t wsum[kWarps];
 };
 static_assert(sizeof(SmallState) % 16 == 0 && sizeof(StageUnion) % 16 == 0, "accumulators must stay 16-byte aligned");
@@ -169,69 +177,46 @@ __device__ __forceinline__ uint32_t block_excl_scan(uint32_t v, uint32_t* wsum, 
     return base + inc - v;
 }
 
-// one chunk of <= kChunk posting slots of one bucket, lane-predicated (bucket tails, small buckets, S6 terms)
-__device__ __forceinline__ void score_chunk_generic(const uint32_t* src, uint32_t n, uint32_t wraw, uint32_t lane,
-                                                    uint32_t acc_s) {
-    const uint32_t w = wraw & 0x7FFFFFFFu;
-    uint32_t v[kUnroll];
-#pragma unroll
-    for (int u = 0; u < kUnroll; ++u) v[u] = (u * 32 + lane < n) ? ld_stream_u32(src + u * 32) : 0u;
-    if (!(wraw >> 31)) {
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u)
-            if (u * 32 + lane < n) red_shared_add(acc_s + (v[u] & 0xFFFFu) * 4u, (v[u] >> 16) * w);
-    } else {                                                    // S6: float32(boost*freq) per term
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u)
-            if (u * 32 + lane < n) red_shared_add(acc_s + (v[u] & 0xFFFFu) * 4u, (uint32_t)__uint2float_rn((v[u] >> 16) * w));
-    }
-}
-
-// chunks [0,nc) of one bucket for one warp: full chunks software-pipelined, then the lane-predicated tail.
-// FAST: w = weight << 24 | 4 (dp2a form, weight < 256); else w = weight (< 2^16) and the posting is unpacked.
-template <bool FAST>
-__device__ __forceinline__ void scatter_one(uint32_t acc_s, uint32_t v, uint32_t w) {
-    if (FAST) scatter_fast(acc_s, v, w);
-    else red_shared_add(acc_s + (v & 0xFFFFu) * 4u, (v >> 16) * w);
-}
-template <bool FAST>
-__device__ __forceinline__ void scatter_chunks(const uint32_t*& src, uint32_t& left, uint32_t& nc, const uint32_t w,
-                                               const uint32_t lane, const uint32_t acc_s) {
-    uint32_t nfull = min(nc, left / kChunk);
-    if (nfull) {
-        uint32_t v[kUnroll];
+// One chunk = kChunk consecutive posting slots of a bucket (the bucket's last chunk holds n < kChunk).  A warp loads
+// chunk i+1 -- of the same bucket or of the next one -- before it applies chunk i, so the L2 round trip of a small
+// bucket hides behind the previous chunk instead of serialising.
+__device__ __forceinline__ void chunk_load(uint32_t (&v)[kUnroll], const uint32_t* src, uint32_t n, uint32_t lane) {
+    if (n == (uint32_t)kChunk) {
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) v[u] = ld_stream_u32(src + u * 32);
-        for (uint32_t c = 1; c < nfull; ++c) {                  // software pipeline: next chunk's loads in flight
-            uint32_t nx[kUnroll];
-            src += kChunk;
-#pragma unroll
-            for (int u = 0; u < kUnroll; ++u) nx[u] = ld_stream_u32(src + u * 32);
-#pragma unroll
-            for (int u = 0; u < kUnroll; ++u) scatter_one<FAST>(acc_s, v[u], w);
-#pragma unroll
-            for (int u = 0; u < kUnroll; ++u) v[u] = nx[u];
-        }
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u) scatter_one<FAST>(acc_s, v[u], w);
-        src += kChunk;
-        left -= nfull * kChunk;
-        nc -= nfull;
-    }
-    for (; nc; --nc) {                                          // bucket tail / small bucket
-        const uint32_t n = min((uint32_t)kChunk, left);
-        uint32_t v[kUnroll];
+    } else {
 #pragma unroll
         for (int u = 0; u < kUnroll; ++u) v[u] = (u * 32 + lane < n) ? ld_stream_u32(src + u * 32) : 0u;
-#pragma unroll
-        for (int u = 0; u < kUnroll; ++u)
-            if (u * 32 + lane < n) scatter_one<FAST>(acc_s, v[u], w);
-        src += kChunk;
-        left -= n;
     }
 }
+// KIND 0: weight below 256, dp2a form (w = weight << 24 | 4); 1: weight below 2^16, mask / shift / IMAD form;
+// 2: S6 term, float32(boost*freq) per posting.
+template <int KIND>
+__device__ __forceinline__ void posting_apply(uint32_t acc_s, uint32_t v, uint32_t w) {
+    if (KIND == 0) scatter_fast(acc_s, v, w);
+    else if (KIND == 1) red_shared_add(acc_s + (v & 0xFFFFu) * 4u, (v >> 16) * w);
+    else red_shared_add(acc_s + (v & 0xFFFFu) * 4u, (uint32_t)__uint2float_rn((v >> 16) * w));
+}
+template <int KIND>
+__device__ __forceinline__ void chunk_apply_kind(const uint32_t (&v)[kUnroll], uint32_t n, uint32_t w, uint32_t lane,
+                                                 uint32_t acc_s) {
+    if (n == (uint32_t)kChunk) {
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u) posting_apply<KIND>(acc_s, v[u], w);
+    } else {
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+            if (u * 32 + lane < n) posting_apply<KIND>(acc_s, v[u], w);
+    }
+}
+__device__ __forceinline__ void chunk_apply(const uint32_t (&v)[kUnroll], uint32_t n, uint32_t wraw, uint32_t lane,
+                                            uint32_t acc_s) {
+    if (wraw < 256u) chunk_apply_kind<0>(v, n, (wraw << 24) | 4u, lane, acc_s);
+    else if (!(wraw >> 31)) chunk_apply_kind<1>(v, n, wraw, lane, acc_s);
+    else chunk_apply_kind<2>(v, n, wraw & 0x7FFFFFFFu, lane, acc_s);
+}
 
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, MSR_SPARSE_MIN_CTAS)
 sparse_score_topk_kernel(const SearchParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     StageUnion* U = reinterpret_cast<StageUnion*>(smem_raw);
@@ -393,42 +378,60 @@ sparse_score_topk_kernel(const SearchParams P) {
         if (tid == 0) U->seg.pref[kSegMax] = total;
         __syncthreads();
 
-        // each warp takes a contiguous range of chunk numbers, so it mostly walks inside one bucket
+        // each warp takes a contiguous range of chunk numbers [g, g1) of the batch, so it mostly walks inside one bucket
         uint32_t g = (uint32_t)(((uint64_t)total * warp) / kWarps);
         const uint32_t g1 = (uint32_t)(((uint64_t)total * (warp + 1)) / kWarps);
-        if (g >= g1) continue;                                  // (the do-while condition is evaluated)
-        uint32_t seg;
-        {                                                       // last seg with pref[seg] <= g
-            uint32_t lo = 0, hi = kSegMax;
-            while (hi - lo > 1) {
-                const uint32_t mid = (lo + hi) >> 1;
-                if (U->seg.pref[mid] <= g) lo = mid; else hi = mid;
+        if (g < g1) {
+            uint32_t seg;
+            {                                                   // last seg with pref[seg] <= g
+                uint32_t lo = 0, hi = kSegMax;
+                while (hi - lo > 1) {
+                    const uint32_t mid = (lo + hi) >> 1;
+                    if (U->seg.pref[mid] <= g) lo = mid; else hi = mid;
+                }
+                seg = lo;
             }
-            seg = lo;
-        }
-        while (g < g1) {
-            const uint32_t sb = U->seg.pref[seg], se = U->seg.pref[seg + 1];
-            if (se <= g) { ++seg; continue; }                   // empty buckets
-            const uint32_t len = U->seg.len[seg], wraw = U->seg.w[seg];
-            const uint32_t c0 = g - sb, c1 = min(se, g1) - sb;  // chunks [c0,c1) of this bucket are ours
-            const uint32_t* src = P.postings + U->seg.start[seg] + (size_t)c0 * kChunk + lane;
-            uint32_t left = len - c0 * kChunk;                  // slots from chunk c0 to the bucket's end
-            uint32_t nc = c1 - c0;
-            g = sb + c1;
-            ++seg;
-            if (!(wraw >> 31)) {
-                // weight below 256 (the common case): dp2a form; wider weights: mask / shift / IMAD form
-                if (wraw < 256u) scatter_chunks<true>(src, left, nc, (wraw << 24) | 4u, lane, acc_s);
-                else scatter_chunks<false>(src, left, nc, wraw, lane, acc_s);
+            // chunk stream: (source, valid slots, weight) of chunk number g, then ++g
+            uint32_t b_sb = 0, b_se = 0, b_len = 0, b_w = 0;
+            const uint32_t* b_src = nullptr;
+            auto next_chunk = [&](const uint32_t*& src, uint32_t& n, uint32_t& w) {
+                while (g >= b_se) {                             // enter the bucket that holds chunk g
+                    b_sb = U->seg.pref[seg];
+                    b_se = U->seg.pref[seg + 1];
+                    if (b_se > g) {
+                        b_len = U->seg.len[seg];
+                        b_w = U->seg.w[seg];
+                        b_src = P.postings + U->seg.start[seg] + lane;
+                    }
+                    ++seg;
+                }
+                const uint32_t c = g - b_sb;
+                src = b_src + (size_t)c * kChunk;
+                n = min((uint32_t)kChunk, b_len - c * kChunk);
+                w = b_w;
+                ++g;
+            };
+            const uint32_t* src;
+            uint32_t n, w, v[kUnroll];
+            next_chunk(src, n, w);
+            chunk_load(v, src, n, lane);
+            while (g < g1) {
+                const uint32_t* src2;
+                uint32_t n2, w2, nx[kUnroll];
+                next_chunk(src2, n2, w2);
+                chunk_load(nx, src2, n2, lane);                 // in flight while chunk g-1 is applied
+                chunk_apply(v, n, w, lane, acc_s);
+                n = n2; w = w2;
+#pragma unroll
+                for (int u = 0; u < kUnroll; ++u) v[u] = nx[u];
             }
-            for (; nc; --nc) {
-                const uint32_t n = min((uint32_t)kChunk, left);
-                score_chunk_generic(src, n, wraw, lane, acc_s);
-                src += kChunk;
-                left -= n;
-            }
+            chunk_apply(v, n, w, lane, acc_s);
         }
     } while ((batch += kSegMax) < qe);
+    // The threshold is read ONCE per CTA and broadcast: theta rises while other tiles of the query publish, and
+    // threads reading it on their own could disagree -- some still seeing 0 (exact select, with its barriers)
+    // while others already take the threshold path.
+    if (tid == 0) S->theta = P.use_theta ? *(volatile unsigned long long*)(P.theta + q) : 0ull;
     __syncthreads();
 
     // ---- phase 2: candidates of the tile by (float32(score) desc, doc asc) ----
@@ -438,7 +441,7 @@ sparse_score_topk_kernel(const SearchParams P) {
     uint64_t* tlist = P.tlist + (size_t)q * P.k;
 
     // 2a. threshold mode: one pass, emit the docs whose key reaches theta
-    const unsigned long long theta = P.use_theta ? *(volatile unsigned long long*)theta_p : 0ull;
+    const unsigned long long theta = S->theta;
     if (theta) {
         const float tf = key_score(theta);                      // an integer-valued float32 in (0, 2^31)
         uint32_t amin = (uint32_t)tf;                           // smallest integer score whose float32 image is >= tf
@@ -498,12 +501,12 @@ sparse_score_topk_kernel(const SearchParams P) {
             while (n2 < n) n2 <<= 1;
             for (uint32_t i = n + tid; i < n2; i += kThreads) U->keys[i] = 0;
             bitonic_sort_desc(U->keys, n2);
-            uint64_t e[4];
-            uint32_t f[4], ls = 0;
-            uint64_t prev = (tid > 0 && 4 * tid - 1 < n2) ? U->keys[4 * tid - 1] : ~0ull;
+            uint64_t e[kPer];
+            uint32_t f[kPer], ls = 0;
+            uint64_t prev = (tid > 0 && kPer * tid - 1 < n2) ? U->keys[kPer * tid - 1] : ~0ull;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
-                const uint32_t idx = 4 * tid + j;
+            for (int j = 0; j < kPer; ++j) {
+                const uint32_t idx = kPer * tid + j;
                 e[j] = idx < n2 ? U->keys[idx] : 0ull;
                 f[j] = (e[j] != 0ull && e[j] != prev) ? 1u : 0u;
                 prev = e[j];
@@ -512,7 +515,7 @@ sparse_score_topk_kernel(const SearchParams P) {
             uint32_t total;
             uint32_t ex = block_excl_scan(ls, S->wsum, &total);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < kPer; ++j) {
                 if (f[j]) {
                     if (ex < P.k) {
                         tlist[ex] = e[j];
@@ -576,15 +579,15 @@ sparse_score_topk_kernel(const SearchParams P) {
         }
         __syncthreads();
         {
-            uint32_t h4[4], ls = 0;
+            uint32_t h4[kPer], ls = 0;
 #pragma unroll
-            for (int j = 0; j < 4; ++j) { h4[j] = U->sel.hist[tid * 4 + j]; ls += h4[j]; }
+            for (int j = 0; j < kPer; ++j) { h4[j] = U->sel.hist[tid * kPer + j]; ls += h4[j]; }
             uint32_t total;
             uint32_t ex = block_excl_scan(ls, S->wsum, &total);
 #pragma unroll
-            for (int j = 0; j < 4; ++j) {
+            for (int j = 0; j < kPer; ++j) {
                 if (ex < remaining && ex + h4[j] >= remaining) {
-                    S->sel_b = tid * 4 + j; S->sel_clt = ex; S->sel_bcount = h4[j];
+                    S->sel_b = tid * kPer + j; S->sel_clt = ex; S->sel_bcount = h4[j];
                 }
                 ex += h4[j];
             }

@@ -214,3 +214,28 @@ def test_tile_size_not_multiple_of_8(oracle, lib_built):
     indptr, docids, impacts = random_csr(rng, 3001, 300, 30)
     qi, qt, qw = random_queries(rng, 400, 300, 10)
     _check(oracle, indptr, docids, impacts, 3001, qi, qt, qw, 20, tile_docs=501)
+
+
+def test_threshold_read_is_uniform_per_cta_under_cold_timing(oracle, lib_built):
+    """Regression: every thread used to read the query's shared threshold on its own; with the tiles of a query running
+    skewed in time (cold L2 / TLB: first search after a build, or an L2 flush) some threads of a CTA could still see 0
+    (exact select) while others took the threshold path.  All CTAs of this case are co-resident, k is close to the
+    tile size and L2 is flushed before every search; 1 in ~30 searches failed before the fix."""
+    from mllm_sparse_retrieval_b200.ops import SparseIndex
+    rng = np.random.default_rng(6)
+    n_docs, n_terms, k = 5000, 4096, 1000
+    indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 128)
+    qi, qt, qw = random_queries(rng, 8, n_terms, 300, dup=True)
+    exp = oracle.impact_search_c(indptr, docids, impacts, n_docs, qi, qt, qw, k, threads=4)
+    dq = _dev_queries(qi, qt, qw)
+    for b in range(6):
+        idx = SparseIndex(indptr, docids, impacts, n_docs, tile_docs=1024)
+        for r in range(25):
+            flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+            flush.fill_(r)
+            del flush
+            s, d, c = idx.search(*dq, k)
+            idx.status()
+            np.testing.assert_array_equal(d.cpu().numpy(), exp[1])
+            np.testing.assert_array_equal(s.cpu().numpy(), exp[0])
+        idx.close()
