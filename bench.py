@@ -65,8 +65,12 @@ def parse_args():
 
 
 def workload_config(a, world):
+    named = {(1_000_000, 10_000, 32): "BASELINE.json configs[3]", (1000, 5000, 12): "configs[0], Flickr-1K shape",
+             (1000, 5000, 128): "configs[0], Flickr-1K shape, --sparse_manual", (5000, 25000, 12): "configs[1], COCO-5K t->i shape",
+             (5000, 25000, 128): "configs[1], COCO-5K t->i shape, --sparse_manual",
+             (25000, 5000, 128): "configs[1], COCO-5K i->t shape"}.get((a.n_docs, a.nq, a.q_len), "parity-test size")
     return {"workload": f"synthetic {a.n_docs}-doc vocab-sparse index (Zipf s=1, V={a.vocab}, {a.nnz_per_doc} nnz/doc), "
-                        f"{a.nq} queries x {a.q_len} terms, top-{a.k} (BASELINE.json configs[3])",
+                        f"{a.nq} queries x {a.q_len} terms, top-{a.k} ({named})",
             "n_docs": a.n_docs, "nq": a.nq, "q_len": a.q_len, "k": a.k, "vocab": a.vocab, "seed": a.seed,
             "sharding": f"doc-range x{world} + NCCL all-gather merge, {a.chunks}-chunk pipelined exchange" if world > 1 else "single GPU",
             "l2": "index (4 B/posting physical, >= 512 MB) is larger than the 126 MB L2; no explicit flush"}
@@ -367,6 +371,9 @@ def run_ours(a, rank, world, local_rank):
                           "pinned host lists on rank 0"},
            "gpu_launches": int(launches), "roofline": roof, "clocks": clocks, "parity_check": check,
            "index": {"n_tiles": idx.n_tiles, "tile_docs": idx.tile_docs, "nnz_shard": idx.nnz, "resident_bytes": idx.resident_bytes}}
+    if idx.resident_bytes * world < (126 << 20):
+        res["config"]["l2"] = (f"index ({idx.resident_bytes * world >> 20} MB) fits the 126 MB L2: launch / latency-bound, "
+                               "not a roofline configuration (SURVEY 8(d)); QPS and exactness only")
     if world == 1 and not a.no_cpu_baseline:
         cb, _, _ = cpu_baseline(a, coll_np, a.n_docs, qs.numpy(), a.cpu_seconds)
         res["cpu_baseline"] = cb
