@@ -35,7 +35,44 @@ topk_merge_kernel(const MergeParams P) {
     uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
     const uint32_t q = blockIdx.x, tid = threadIdx.x;
     uint32_t fill = 0;
-    for (uint32_t j = 0; j < P.n_lists; ++j) {
+    // Common case: all candidates of the query fit the buffer at once.  Every warp then reserves room for its lists
+    // with one shared atomic and copies them in parallel (the order inside the buffer is irrelevant, it is sorted next).
+    __shared__ uint32_t s_total, s_fill;
+    if (tid == 0) { s_total = 0; s_fill = 0; }
+    __syncthreads();
+    {
+        uint32_t mine = 0;
+        for (uint32_t j = tid; j < P.n_lists; j += kMergeThreads) {
+            const size_t li = P.mode == 0 ? (size_t)q * P.n_lists + j : (size_t)j * P.nq + q;
+            mine += min(P.cnts[li], P.stride);
+        }
+        mine = warp_reduce_add(mine);
+        if ((tid & 31) == 0 && mine) atomicAdd(&s_total, mine);
+    }
+    __syncthreads();
+    const bool all_fit = s_total <= P.cap;
+    if (all_fit) {
+        const uint32_t lane = tid & 31, warp = tid >> 5;
+        for (uint32_t j = warp; j < P.n_lists; j += kMergeThreads / 32) {
+            const size_t li = P.mode == 0 ? (size_t)q * P.n_lists + j : (size_t)j * P.nq + q;
+            const uint32_t c = min(P.cnts[li], P.stride);
+            if (c == 0) continue;
+            uint32_t base = 0;
+            if (lane == 0) base = atomicAdd(&s_fill, c);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (P.mode == 0) {
+                const uint64_t* src = P.keys + li * P.stride;
+                for (uint32_t i = lane; i < c; i += 32) buf[base + i] = src[i];
+            } else {
+                const float* ss = P.scores + li * P.stride;
+                const int32_t* dd = P.docs + li * P.stride;
+                for (uint32_t i = lane; i < c; i += 32) buf[base + i] = make_key(ss[i], (uint32_t)dd[i]);
+            }
+        }
+        __syncthreads();
+        fill = s_total;
+    }
+    for (uint32_t j = 0; j < P.n_lists && !all_fit; ++j) {
         const size_t li = P.mode == 0 ? (size_t)q * P.n_lists + j : (size_t)j * P.nq + q;
         const uint32_t c = min(P.cnts[li], P.stride);
         if (c == 0) continue;
