@@ -341,7 +341,17 @@ sparse_score_topk_kernel(const SearchParams P) {
                         b = U->seg.db[d + 3];
                         dense_dp4a8(a, v3, b); dense_dp4a8(c, u3, b);
                     }
-                    for (; d < nd; ++d) {
+                    if (nd & 2) {
+                        const uint2 r = *reinterpret_cast<const uint2*>(&U->seg.drow[d]);
+                        const uint2 v0 = ld_stream_v2(r8 + r.x), v1 = ld_stream_v2(r8 + r.y);
+                        const uint2 u0 = ld_stream_v2(r8 + r.x + kB8), u1 = ld_stream_v2(r8 + r.y + kB8);
+                        uint4 b = U->seg.db[d];
+                        dense_dp4a8(a, v0, b); dense_dp4a8(c, u0, b);
+                        b = U->seg.db[d + 1];
+                        dense_dp4a8(a, v1, b); dense_dp4a8(c, u1, b);
+                        d += 2;
+                    }
+                    if (nd & 1) {
                         const uint32_t r = U->seg.drow[d];
                         const uint2 v0 = ld_stream_v2(r8 + r), u0 = ld_stream_v2(r8 + r + kB8);
                         const uint4 b = U->seg.db[d];
