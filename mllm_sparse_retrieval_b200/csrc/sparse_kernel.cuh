@@ -22,9 +22,6 @@ namespace msr {
 #ifndef MSR_SPARSE_THREADS
 #define MSR_SPARSE_THREADS 512
 #endif
-#ifndef MSR_SPARSE_MERGE_SHIFT
-#define MSR_SPARSE_MERGE_SHIFT 3     // a tile re-publishes the query's threshold list when it adds >= k >> shift candidates
-#endif
 #ifndef MSR_SPARSE_MIN_CTAS
 #define MSR_SPARSE_MIN_CTAS 2
 #endif
@@ -62,6 +59,7 @@ struct SearchParams {
     unsigned long long* theta;    // [nq]
     uint64_t* tlist;              // [nq][k]
     uint32_t use_theta;
+    uint32_t merge_min;           // a tile re-publishes the query's threshold list when it adds >= this many candidates
 };
 
 // One warp per query: exact-arithmetic range check over the kept terms (see msr.h), done once instead of per tile.
@@ -485,7 +483,7 @@ sparse_score_topk_kernel(const SearchParams P) {
             if (tid == 0) *cnt_out = c;
             // merge with the published list: best k distinct keys of (own candidates U tlist) -> new list, new theta.
             // Skipped while the tile adds little (theta would hardly move) or the union does not fit.
-            if (c < max(1u, P.k >> MSR_SPARSE_MERGE_SHIFT) || c + P.k > (uint32_t)kUnionMax) return;
+            if (c < P.merge_min || c + P.k > (uint32_t)kUnionMax) return;
             for (uint32_t r = tid; r < P.k; r += kThreads) U->keys[c + r] = ((volatile const uint64_t*)tlist)[r];
             const uint32_t n = c + P.k;
             if (n <= (uint32_t)kThreads) {
