@@ -542,12 +542,15 @@ sparse_score_topk_kernel(const SearchParams P) {
     }
 
     // 2b. exact radix select of the tile's top-k
+    const uint4* acc4 = reinterpret_cast<const uint4*>(acc);
+    const uint32_t nvec4 = (tl + 3) >> 2;
     {
+        // (accumulator slots past tl hold 0, so whole 16-byte vectors are read in all passes of the select)
         uint32_t m = 0, h = 0;
-        for (uint32_t i = tid; i < tl; i += kThreads) {
-            uint32_t a = acc[i];
-            m = max(m, a);
-            h += (a != 0);
+        for (uint32_t j = tid; j < nvec4; j += kThreads) {
+            const uint4 x = acc4[j];
+            m = max(max(m, max(x.x, x.y)), max(x.z, x.w));
+            h += (x.x != 0) + (x.y != 0) + (x.z != 0) + (x.w != 0);
         }
         m = warp_reduce_max(m);
         h = warp_reduce_add(h);
@@ -580,12 +583,17 @@ sparse_score_topk_kernel(const SearchParams P) {
         const uint32_t width = sh_prev - s;
         for (uint32_t i = tid; i < kBins; i += kThreads) U->sel.hist[i] = 0;
         __syncthreads();
-        for (uint32_t i = tid; i < tl; i += kThreads) {
-            uint32_t a = acc[i];
-            if (a) {
-                uint32_t d = kmax - MSR_SELKEY(a);
-                uint32_t hi = sh_prev >= 32 ? 0u : (d >> sh_prev);
-                if (hi == pref) atomicAdd(&U->sel.hist[(d >> s) & ((1u << width) - 1u)], 1u);
+        for (uint32_t j = tid; j < nvec4; j += kThreads) {
+            const uint4 x = acc4[j];
+            const uint32_t e[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t a = e[u];
+                if (a) {
+                    uint32_t d = kmax - MSR_SELKEY(a);
+                    uint32_t hi = sh_prev >= 32 ? 0u : (d >> sh_prev);
+                    if (hi == pref) atomicAdd(&U->sel.hist[(d >> s) & ((1u << width) - 1u)], 1u);
+                }
             }
         }
         __syncthreads();
@@ -612,16 +620,21 @@ sparse_score_topk_kernel(const SearchParams P) {
     }
     const uint32_t n_def = kq - remaining;                      // docs strictly better than the candidate bin
     const bool collect = cand_count <= (uint32_t)kCandMax;
-    for (uint32_t i = tid; i < tl; i += kThreads) {
-        uint32_t a = acc[i];
-        if (a) {
-            uint32_t d = kmax - MSR_SELKEY(a);
-            uint32_t x = d >> s;
-            if (x < pref) {
-                keys_out[atomicAdd(&S->out_cnt, 1u)] = make_key(__uint2float_rn(a), gdoc0 + i);
-            } else if (x == pref && collect) {
-                // descending sort of ~((d<<32)|i)  ==  ascending (d, i)  ==  best first
-                U->sel.cand[atomicAdd(&S->cand_cnt, 1u)] = ~(((uint64_t)d << 32) | i);
+    for (uint32_t j = tid; j < nvec4; j += kThreads) {
+        const uint4 v = acc4[j];
+        const uint32_t e[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t a = e[u], i = 4 * j + u;
+            if (a && i < tl) {
+                uint32_t d = kmax - MSR_SELKEY(a);
+                uint32_t x = d >> s;
+                if (x < pref) {
+                    keys_out[atomicAdd(&S->out_cnt, 1u)] = make_key(__uint2float_rn(a), gdoc0 + i);
+                } else if (x == pref && collect) {
+                    // descending sort of ~((d<<32)|i)  ==  ascending (d, i)  ==  best first
+                    U->sel.cand[atomicAdd(&S->cand_cnt, 1u)] = ~(((uint64_t)d << 32) | i);
+                }
             }
         }
     }
