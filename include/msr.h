@@ -198,13 +198,20 @@ int msr_quantise_topk(int device, uint32_t n_rows, uint32_t vocab, const void* l
  * by (value desc, candidate position asc) -- the reference uses cap = 128; a row WITHOUT candidates falls back to the
  * top-`fallback_top` of the whole vocabulary (the reference uses 10).  Quantisation, the `id < vocab_len` skip with
  * its value shift, the token -> term map and the duplicate rule are those of msr_quantise_topk.  Output pitch =
- * max(cap, fallback_top) entries per row.  logits / token_to_term / out_* are device pointers; at most 4096 candidates
+ * max(cap, fallback_top) (+ n_expand) entries per row.  logits / token_to_term / out_* are device pointers; at most 4096 candidates
  * per row; candidate ids must be < vocab.  The call synchronises `stream` before returning (it reads pageable host
- * arrays).  Expansion terms (num_expended_tokens > 0; every script of the reference passes 0) are not provided.
+ * arrays).
+ * Expansion terms (num_expended_tokens > 0, encode.py:137-152): with n_expand > 0 every row also gets the top-n_expand of
+ * its logits over `filtered_ids - token_ids` = the tokens with expand_mask[v] != 0 (device u8[vocab], the reference's
+ * get_filtered_ids, encode.py:38-47) minus the row's own candidates, appended behind the main entries exactly as the
+ * reference appends them (so the value shift of skipped ids carries over); rows with fewer eligible tokens get fewer.
+ * Output pitch = max(cap, fallback_top) + n_expand.  expand_mask NULL / n_expand 0 = off (what every script of the
+ * reference passes).  The --sparse_manual and image variants of the expansion are not provided.
  */
 int msr_quantise_candidates(int device, uint32_t n_rows, uint32_t vocab, const void* logits, int dtype, size_t row_stride,
                             const uint64_t* cand_indptr_host, const int32_t* cand_tokens_host, uint32_t cap,
                             uint32_t fallback_top, uint32_t vocab_len, const int32_t* token_to_term, int doc_mode,
+                            const uint8_t* expand_mask, uint32_t n_expand,
                             uint64_t* out_indptr, uint32_t* out_terms, uint32_t* out_weights, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------

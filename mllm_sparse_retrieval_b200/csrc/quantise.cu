@@ -20,6 +20,7 @@
 #include <cuda_fp16.h>
 
 #include <algorithm>
+#include <cmath>
 #include <vector>
 
 #include "common.cuh"
@@ -142,6 +143,42 @@ cand_select_kernel(const T* __restrict__ logits, size_t row_stride, const unsign
     if (threadIdx.x == 0) cnt[row] = keep;
 }
 
+
+// Expansion terms of get_text_valid_tokens_values (/root/reference/src/encode.py:137-152): the top-n of the logits over
+// `filtered_ids - token_ids`.  masked rows: -inf outside the expansion vocabulary, then -inf at the row's own candidates.
+template <class T>
+__global__ void expand_mask_rows_kernel(const T* __restrict__ logits, size_t row_stride, uint32_t row0, uint32_t n_rows,
+                                        uint32_t vocab, const uint8_t* __restrict__ mask, float* __restrict__ dst) {
+    const size_t total = (size_t)n_rows * vocab;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        const size_t r = i / vocab, c = i - r * vocab;
+        dst[i] = mask[c] ? to_f32<T>(logits[(row0 + r) * row_stride + c]) : -INFINITY;
+    }
+}
+__global__ void expand_exclude_kernel(const unsigned long long* __restrict__ c_indptr, const int32_t* __restrict__ c_tok,
+                                      uint32_t row0, uint32_t vocab, float* __restrict__ dst) {
+    const uint32_t r = blockIdx.x;
+    const unsigned long long lo = c_indptr[row0 + r], hi = c_indptr[row0 + r + 1];
+    for (unsigned long long j = lo + threadIdx.x; j < hi; j += blockDim.x) dst[(size_t)r * vocab + c_tok[j]] = -INFINITY;
+}
+// appends the finite expansion entries (already in descending order) behind the row's main entries
+__global__ void expand_append_kernel(const float* __restrict__ es, const int32_t* __restrict__ ed, uint32_t n_expand,
+                                     uint32_t row0, uint32_t n_rows, uint32_t pitch, float* __restrict__ ts,
+                                     int32_t* __restrict__ td, uint32_t* __restrict__ cnt) {
+    const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r >= n_rows) return;
+    const size_t row = (size_t)row0 + r;
+    uint32_t n = cnt[row];
+    for (uint32_t j = 0; j < n_expand && n < pitch; ++j) {
+        const float v = es[(size_t)r * n_expand + j];
+        if (v == -INFINITY) break;
+        ts[row * pitch + n] = v;
+        td[row * pitch + n] = ed[(size_t)r * n_expand + j];
+        ++n;
+    }
+    cnt[row] = n;
+}
+
 }  // namespace msr
 
 using namespace msr;
@@ -194,8 +231,8 @@ extern "C" int msr_quantise_topk(int device, uint32_t n_rows, uint32_t vocab, co
 extern "C" int msr_quantise_candidates(int device, uint32_t n_rows, uint32_t vocab, const void* logits, int dtype,
                                        size_t row_stride, const uint64_t* cand_indptr_host, const int32_t* cand_tokens_host,
                                        uint32_t cap, uint32_t fallback_top, uint32_t vocab_len, const int32_t* token_to_term,
-                                       int doc_mode, uint64_t* out_indptr, uint32_t* out_terms, uint32_t* out_weights,
-                                       void* stream) {
+                                       int doc_mode, const uint8_t* expand_mask, uint32_t n_expand, uint64_t* out_indptr,
+                                       uint32_t* out_terms, uint32_t* out_weights, void* stream) {
     MSR_REQUIRE(dtype >= 0 && dtype <= 2, "msr_quantise_candidates: dtype %d outside {0 f32, 1 f16, 2 bf16}", dtype);
     MSR_REQUIRE(cap >= 1 && cap <= (uint32_t)kQuantMaxTop && fallback_top >= 1 && fallback_top <= (uint32_t)kQuantMaxTop,
                 "msr_quantise_candidates: cap=%u / fallback_top=%u outside [1,%d]", cap, fallback_top, kQuantMaxTop);
@@ -222,7 +259,9 @@ extern "C" int msr_quantise_candidates(int device, uint32_t n_rows, uint32_t voc
     for (uint64_t i = 0; i < n_c; ++i)
         MSR_REQUIRE(cand_tokens_host[i] >= 0 && (uint32_t)cand_tokens_host[i] < vocab,
                     "msr_quantise_candidates: candidate token id %d outside [0,%u)", cand_tokens_host[i], vocab);
-    const uint32_t pitch = std::max(cap, fallback_top);
+    MSR_REQUIRE(n_expand == 0 || expand_mask, "msr_quantise_candidates: n_expand > 0 needs expand_mask");
+    MSR_REQUIRE(n_expand <= (uint32_t)kQuantMaxTop && n_expand <= vocab, "msr_quantise_candidates: n_expand=%u above min(%d, vocab)", n_expand, kQuantMaxTop);
+    const uint32_t pitch = std::max(cap, fallback_top) + n_expand;
     float* ts = nullptr; int32_t* td = nullptr; uint32_t* tc = nullptr; unsigned long long* ci = nullptr; int32_t* ct = nullptr;
     float* f32 = nullptr;
     MSR_CUDA_CHECK(cudaMallocAsync(&ts, (size_t)n_rows * pitch * 4, s));
@@ -244,6 +283,29 @@ extern "C" int msr_quantise_candidates(int device, uint32_t n_rows, uint32_t voc
         if (dtype == 2) { rows_to_f32_kernel<__nv_bfloat16><<<148, 256, 0, s>>>((const __nv_bfloat16*)logits + (size_t)r * row_stride, row_stride, 1, vocab, f32); row = f32; count_launch(); }
         rc = topk_rows_launch(1, vocab, row, vocab, fallback_top, 0, ts + (size_t)r * pitch, td + (size_t)r * pitch, tc + r, s);
         if (rc) break;
+    }
+    if (rc == MSR_OK && n_expand) {
+        // expansion terms, a block of rows at a time (scratch: masked fp32 rows, <= 256 MB)
+        const uint32_t rows_per = (uint32_t)std::max<size_t>(1, std::min<size_t>(n_rows, ((size_t)256 << 20) / ((size_t)vocab * 4)));
+        float* masked = nullptr; float* es = nullptr; int32_t* ed = nullptr; uint32_t* ec = nullptr;
+        MSR_CUDA_CHECK(cudaMallocAsync(&masked, (size_t)rows_per * vocab * 4, s));
+        MSR_CUDA_CHECK(cudaMallocAsync(&es, (size_t)rows_per * n_expand * 4, s));
+        MSR_CUDA_CHECK(cudaMallocAsync(&ed, (size_t)rows_per * n_expand * 4, s));
+        MSR_CUDA_CHECK(cudaMallocAsync(&ec, (size_t)rows_per * 4, s));
+        for (uint32_t r0 = 0; r0 < n_rows && rc == MSR_OK; r0 += rows_per) {
+            const uint32_t nr = std::min(rows_per, n_rows - r0);
+            const unsigned g = (unsigned)std::min<size_t>(((size_t)nr * vocab + 255) / 256, 148 * 32);
+            if (dtype == 0) expand_mask_rows_kernel<float><<<g, 256, 0, s>>>((const float*)logits, row_stride, r0, nr, vocab, expand_mask, masked);
+            else if (dtype == 1) expand_mask_rows_kernel<__half><<<g, 256, 0, s>>>((const __half*)logits, row_stride, r0, nr, vocab, expand_mask, masked);
+            else expand_mask_rows_kernel<__nv_bfloat16><<<g, 256, 0, s>>>((const __nv_bfloat16*)logits, row_stride, r0, nr, vocab, expand_mask, masked);
+            expand_exclude_kernel<<<nr, 128, 0, s>>>(ci, ct, r0, vocab, masked);
+            count_launch(2);
+            rc = topk_rows_launch(nr, vocab, masked, vocab, n_expand, 0, es, ed, ec, s);
+            if (rc) break;
+            expand_append_kernel<<<(nr + 127) / 128, 128, 0, s>>>(es, ed, n_expand, r0, nr, pitch, ts, td, tc);
+            count_launch();
+        }
+        cudaFreeAsync(masked, s); cudaFreeAsync(es, s); cudaFreeAsync(ed, s); cudaFreeAsync(ec, s);
     }
     if (rc == MSR_OK) {
         const uint32_t wpb = 4;

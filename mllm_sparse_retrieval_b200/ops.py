@@ -330,9 +330,26 @@ def text_token_ids(text, tokenizer, word_tokenize=None, stop_words=None):
     return list(token_ids)
 
 
-def quantise_candidates(logits, cand_lists, token_to_term=None, vocab_len=None, doc_mode=False, cap=128, fallback_top=10):
+def get_filtered_ids(tokenizer):
+    """/root/reference/src/encode.py:38-47: ids of the vocabulary entries that are alphabetic or numeric words starting
+    with a lower-case ASCII letter (after a leading '▁' / ' ' is dropped) -- the expansion vocabulary."""
+    filtered_ids = set()
+    for token, id in tokenizer.get_vocab().items():
+        if token[0] == '▁' or token[0] == ' ':
+            token = token[1:]
+        if not token.isalpha() and not token.isdigit():
+            continue
+        if ord('a') <= ord(token[0]) <= ord('z'):
+            filtered_ids.add(id)
+    return filtered_ids
+
+
+def quantise_candidates(logits, cand_lists, token_to_term=None, vocab_len=None, doc_mode=False, cap=128, fallback_top=10,
+                        filtered_ids=None, num_expended_tokens=0):
     """Candidate branch of the text quantiser on the GPU (msr_quantise_candidates): activation rows + per-row candidate
-    token ids (``text_token_ids``) -> query CSR at pitch max(cap, fallback_top): (indptr i64 [n+1], terms i32, weights i32)."""
+    token ids (``text_token_ids``) -> query CSR at pitch max(cap, fallback_top) + num_expended_tokens:
+    (indptr i64 [n+1], terms i32, weights i32).  ``filtered_ids`` (``get_filtered_ids``) + ``num_expended_tokens`` > 0 add
+    the reference's expansion terms (encode.py:137-152)."""
     assert logits.is_cuda and logits.dim() == 2 and logits.stride(1) == 1 and logits.dtype in _DTYPES
     n, V = logits.shape
     assert len(cand_lists) == n
@@ -345,7 +362,14 @@ def quantise_candidates(logits, cand_lists, token_to_term=None, vocab_len=None, 
     np.cumsum([len(c) for c in cand_lists], out=c_indptr[1:])
     c_tok = np.ascontiguousarray(np.concatenate([np.asarray(c, dtype=np.int64).reshape(-1) for c in cand_lists])
                                  if n else np.zeros(0), dtype=np.int32)
-    pitch = max(int(cap), int(fallback_top))
+    n_expand = min(int(num_expended_tokens), V, 1024) if filtered_ids is not None else 0      # top_k = min(n, eligible)
+    mask = None
+    if n_expand > 0:
+        m = np.zeros(V, dtype=np.uint8)
+        ids = np.fromiter((i for i in filtered_ids if 0 <= i < V), dtype=np.int64)
+        m[ids] = 1
+        mask = torch.from_numpy(m).to(dev)
+    pitch = max(int(cap), int(fallback_top)) + n_expand
     indptr = torch.empty((n + 1,), dtype=torch.int64, device=dev)
     terms = torch.empty((n * pitch,), dtype=torch.int32, device=dev)
     weights = torch.empty((n * pitch,), dtype=torch.int32, device=dev)
@@ -353,8 +377,8 @@ def quantise_candidates(logits, cand_lists, token_to_term=None, vocab_len=None, 
     with torch.cuda.device(di):
         check(_lib.load().msr_quantise_candidates(
             di, n, V, ptr(logits), _DTYPES[logits.dtype], logits.stride(0), c_indptr.ctypes.data, c_tok.ctypes.data,
-            int(cap), int(fallback_top), vocab_len, ptr(token_to_term), int(bool(doc_mode)), ptr(indptr), ptr(terms),
-            ptr(weights), current_stream_ptr(di)))
+            int(cap), int(fallback_top), vocab_len, ptr(token_to_term), int(bool(doc_mode)), ptr(mask), n_expand,
+            ptr(indptr), ptr(terms), ptr(weights), current_stream_ptr(di)))
     return indptr, terms, weights
 
 

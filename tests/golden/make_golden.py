@@ -209,22 +209,28 @@ def make_text_quantiser_cases(encode):
     out = []
     base = ["Dog", "dog", "Ġcat", "zebra", "▁Tree", "tree", "sky", "Sky", "x1", "##ing", "blue", "Blue"]
     many = " ".join(f"w{i}" for i in range(140))
-    for text, sparse_manual, sparse_length, is_filtered, V, vlen in [
-            ("A dog of the blue Sky , runs !", False, 128, False, 200, 200),
-            ("the of a , .", False, 128, False, 200, 200),                      # no content word -> top-10 fallback
-            ("oovword the", False, 128, True, 200, 200),                       # words that tokenise to nothing
-            ("two dogs chase a zebra", True, 8, False, 200, 200),              # --sparse_manual
-            ("Trees and sky : tree Tree", False, 128, True, 200, 200),         # is_filtered
-            (many, False, 128, False, 400, 400),                               # > 128 candidates
-            ("a quick brown fox", False, 128, False, 200, 190),                # ids >= len(vocab_dict): value-shift quirk
-            ("the", False, 128, False, 200, 195)]:
+    for text, sparse_manual, sparse_length, is_filtered, V, vlen, n_exp in [
+            ("A dog of the blue Sky , runs !", False, 128, False, 200, 200, 0),
+            ("the of a , .", False, 128, False, 200, 200, 0),                   # no content word -> top-10 fallback
+            ("oovword the", False, 128, True, 200, 200, 0),                    # words that tokenise to nothing
+            ("two dogs chase a zebra", True, 8, False, 200, 200, 0),           # --sparse_manual
+            ("Trees and sky : tree Tree", False, 128, True, 200, 200, 0),      # is_filtered
+            (many, False, 128, False, 400, 400, 0),                            # > 128 candidates
+            ("a quick brown fox", False, 128, False, 200, 190, 0),             # ids >= len(vocab_dict): value-shift quirk
+            ("the", False, 128, False, 200, 195, 0),
+            # expansion terms (num_expended_tokens > 0, encode.py:137-152); filtered_ids = every third id below 180
+            ("A dog of the blue Sky , runs !", False, 128, False, 200, 200, 5),
+            ("the of a , .", False, 128, False, 200, 200, 7),                   # fallback top-10 + expansion (overlap sums)
+            ("a quick brown fox", False, 128, False, 200, 190, 4),             # value shift carries into the expansion
+            ("Trees and sky : tree Tree", False, 128, True, 200, 200, 300)]:   # more requested than eligible
         vd = {i: (base[i] if i < len(base) else f"tok{i}") for i in range(vlen)}
         logits = torch.tensor((np.log1p(np.abs(rng.standard_normal(V)) * 2.0) + 1e-3).astype(np.float32))
         assert len(np.unique(logits.numpy())) == V
         tok = FakeTokenizer(V)
         data_args = types.SimpleNamespace(sparse_manual=sparse_manual, sparse_length=sparse_length, is_filtered=is_filtered,
-                                          num_expended_tokens=0)
-        tokens, values = encode.get_text_valid_tokens_values(text, tok, logits, vd, data_args, set())
+                                          num_expended_tokens=n_exp)
+        filtered_ids = set(range(0, 180, 3)) if n_exp else set()
+        tokens, values = encode.get_text_valid_tokens_values(text, tok, logits, vd, data_args, set(filtered_ids))
         # the candidate list the reference built internally, rebuilt the same way (same set -> same iteration order)
         words = [i for i in text.lower().split() if i not in set(["a", "the", "of"] + list(string.punctuation))]
         token_ids = set()
@@ -239,6 +245,7 @@ def make_text_quantiser_cases(encode):
         out.append({"text": text, "sparse_manual": sparse_manual, "sparse_length": sparse_length, "is_filtered": is_filtered,
                     "vocab": [vd[i] for i in range(vlen)], "logits": [float(x) for x in logits.numpy()],
                     "token_ids": [int(t) for t in token_ids], "stop_words": ["a", "the", "of"],
+                    "num_expended_tokens": n_exp, "filtered_ids": sorted(filtered_ids),
                     "tokens": tokens, "values": [int(v) for v in values], "query_string": query.strip(), "doc_vector": vector})
     return out
 

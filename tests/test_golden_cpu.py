@@ -162,13 +162,14 @@ def test_text_quantiser_matches_reference(golden):
     import importlib.util
     spec = importlib.util.spec_from_file_location("make_golden", os.path.join(sys_path_hack, "make_golden.py"))
     mg = importlib.util.module_from_spec(spec); spec.loader.exec_module(mg)
-    assert len(golden["text_quantiser"]) >= 8
+    assert len(golden["text_quantiser"]) >= 12 and sum(c["num_expended_tokens"] > 0 for c in golden["text_quantiser"]) >= 4
     for c in golden["text_quantiser"]:
         logits = np.asarray(c["logits"], dtype=np.float32)
         cands = text_token_ids(c["text"], mg.FakeTokenizer(len(logits)), word_tokenize=lambda s: s.split(),
                                stop_words=c["stop_words"])
         assert cands == c["token_ids"]
-        toks, vals = quantise_text_row(logits, cands, c["vocab"], c["sparse_manual"], c["sparse_length"], c["is_filtered"])
+        toks, vals = quantise_text_row(logits, cands, c["vocab"], c["sparse_manual"], c["sparse_length"], c["is_filtered"],
+                                       filtered_ids=c["filtered_ids"], num_expended_tokens=c["num_expended_tokens"])
         assert toks == c["tokens"] and vals.tolist() == c["values"]
         assert build_query_string(toks, vals) == c["query_string"]
         assert build_doc_vector(toks, vals) == c["doc_vector"]

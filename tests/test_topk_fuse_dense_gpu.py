@@ -342,8 +342,10 @@ def test_quantise_candidates_matches_reference_fixtures(oracle, lib_built, dtype
     assert len(cases) >= 7
     by_shape = {}
     for c in cases:
-        by_shape.setdefault((len(c["logits"]), len(c["vocab"]), c["is_filtered"]), []).append(c)
-    for (V, vlen, filt), group in by_shape.items():
+        by_shape.setdefault((len(c["logits"]), len(c["vocab"]), c["is_filtered"], c["num_expended_tokens"]), []).append(c)
+    assert sum(k[3] > 0 for k in by_shape) >= 3                 # expansion terms (encode.py:137-152) are covered
+    for (V, vlen, filt, n_exp), group in by_shape.items():
+        f_ids = group[0]["filtered_ids"]
         vocab = group[0]["vocab"]
         names = sorted({v.lower() for v in vocab} | {v.lower()[1:] for v in vocab if len(v) > 1})
         coll = ImpactCollection.from_vectors(["d"], [{n: 1 for n in names}])
@@ -352,14 +354,16 @@ def test_quantise_candidates_matches_reference_fixtures(oracle, lib_built, dtype
         if dtype != torch.float32:                          # the fixture is fp32: compare with the oracle on the rounded row
             exp = []
             for r, c in enumerate(group):
-                toks, vals = oracle.quantise_text_row(x[r].float().cpu().numpy(), c["token_ids"], vocab, False, 128, filt)
+                toks, vals = oracle.quantise_text_row(x[r].float().cpu().numpy(), c["token_ids"], vocab, False, 128, filt,
+                                                      filtered_ids=f_ids, num_expended_tokens=n_exp)
                 exp.append((oracle.build_query_string(toks, vals), oracle.build_doc_vector(toks, vals)))
         else:
             exp = [(c["query_string"], c["doc_vector"]) for c in group]
         for doc_mode in (False, True):
-            ip, t, w = quantise_candidates(x, [c["token_ids"] for c in group], tmap, vocab_len=vlen, doc_mode=doc_mode)
+            ip, t, w = quantise_candidates(x, [c["token_ids"] for c in group], tmap, vocab_len=vlen, doc_mode=doc_mode,
+                                           filtered_ids=f_ids if n_exp else None, num_expended_tokens=n_exp)
             ip, t, w = ip.cpu().numpy(), t.cpu().numpy(), w.cpu().numpy()
-            assert ip.tolist() == [128 * r for r in range(len(group) + 1)]
+            assert ip.tolist() == [(128 + min(n_exp, V)) * r for r in range(len(group) + 1)]
             for r, (qs, dv) in enumerate(exp):
                 got = _csr_row_to_dict(coll, ip, t, w, r)
                 want = {k: v for k, v in dv.items() if v > 0} if doc_mode else dict(Counter(qs.split()))
