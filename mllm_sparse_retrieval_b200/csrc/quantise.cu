@@ -32,6 +32,21 @@ int topk_rows_launch(uint32_t nq, uint32_t n, const float* scores, size_t row_st
 
 constexpr int kQuantMaxTop = 1024;
 
+// stream-ordered scratch buffers of one API call: freed (cudaFreeAsync on the call's stream) on every exit path
+struct AsyncScratch {
+    cudaStream_t s;
+    std::vector<void*> ptrs;
+    explicit AsyncScratch(cudaStream_t stream) : s(stream) {}
+    ~AsyncScratch() { for (void* p : ptrs) cudaFreeAsync(p, s); }
+    template <class T> cudaError_t alloc(T** out, size_t bytes) {
+        void* p = nullptr;
+        cudaError_t e = cudaMallocAsync(&p, bytes ? bytes : 1, s);
+        if (e == cudaSuccess) ptrs.push_back(p);
+        *out = reinterpret_cast<T*>(p);
+        return e;
+    }
+};
+
 template <class T> __device__ __forceinline__ float to_f32(T x);
 template <> __device__ __forceinline__ float to_f32<float>(float x) { return x; }
 template <> __device__ __forceinline__ float to_f32<__half>(__half x) { return __half2float(x); }
@@ -201,11 +216,12 @@ extern "C" int msr_quantise_topk(int device, uint32_t n_rows, uint32_t vocab, co
     MSR_REQUIRE(logits && out_terms && out_weights, "msr_quantise_topk: NULL buffer");
     const uint32_t kk = top;
     // stream-ordered scratch: fp32 rows (when converting), top values / ids / counts
+    AsyncScratch scratch(s);
     float* f32 = nullptr; float* ts = nullptr; int32_t* td = nullptr; uint32_t* tc = nullptr;
-    if (dtype != 0) MSR_CUDA_CHECK(cudaMallocAsync(&f32, (size_t)n_rows * vocab * 4, s));
-    MSR_CUDA_CHECK(cudaMallocAsync(&ts, (size_t)n_rows * top * 4, s));
-    MSR_CUDA_CHECK(cudaMallocAsync(&td, (size_t)n_rows * top * 4, s));
-    MSR_CUDA_CHECK(cudaMallocAsync(&tc, (size_t)n_rows * 4, s));
+    if (dtype != 0) MSR_CUDA_CHECK(scratch.alloc(&f32, (size_t)n_rows * vocab * 4));
+    MSR_CUDA_CHECK(scratch.alloc(&ts, (size_t)n_rows * top * 4));
+    MSR_CUDA_CHECK(scratch.alloc(&td, (size_t)n_rows * top * 4));
+    MSR_CUDA_CHECK(scratch.alloc(&tc, (size_t)n_rows * 4));
     const float* rows = (const float*)logits;
     size_t stride = row_stride;
     if (dtype != 0) {
@@ -223,8 +239,6 @@ extern "C" int msr_quantise_topk(int device, uint32_t n_rows, uint32_t vocab, co
         count_launch();
         if (cudaGetLastError() != cudaSuccess) { set_error("msr_quantise_topk: launch failed"); rc = MSR_ERR_CUDA; }
     }
-    if (f32) cudaFreeAsync(f32, s);
-    cudaFreeAsync(ts, s); cudaFreeAsync(td, s); cudaFreeAsync(tc, s);
     return rc;
 }
 
@@ -262,13 +276,14 @@ extern "C" int msr_quantise_candidates(int device, uint32_t n_rows, uint32_t voc
     MSR_REQUIRE(n_expand == 0 || expand_mask, "msr_quantise_candidates: n_expand > 0 needs expand_mask");
     MSR_REQUIRE(n_expand <= (uint32_t)kQuantMaxTop && n_expand <= vocab, "msr_quantise_candidates: n_expand=%u above min(%d, vocab)", n_expand, kQuantMaxTop);
     const uint32_t pitch = std::max(cap, fallback_top) + n_expand;
+    AsyncScratch scratch(s);
     float* ts = nullptr; int32_t* td = nullptr; uint32_t* tc = nullptr; unsigned long long* ci = nullptr; int32_t* ct = nullptr;
     float* f32 = nullptr;
-    MSR_CUDA_CHECK(cudaMallocAsync(&ts, (size_t)n_rows * pitch * 4, s));
-    MSR_CUDA_CHECK(cudaMallocAsync(&td, (size_t)n_rows * pitch * 4, s));
-    MSR_CUDA_CHECK(cudaMallocAsync(&tc, (size_t)n_rows * 4, s));
-    MSR_CUDA_CHECK(cudaMallocAsync(&ci, (size_t)(n_rows + 1) * 8, s));
-    MSR_CUDA_CHECK(cudaMallocAsync(&ct, (size_t)std::max<uint64_t>(n_c, 1) * 4, s));
+    MSR_CUDA_CHECK(scratch.alloc(&ts, (size_t)n_rows * pitch * 4));
+    MSR_CUDA_CHECK(scratch.alloc(&td, (size_t)n_rows * pitch * 4));
+    MSR_CUDA_CHECK(scratch.alloc(&tc, (size_t)n_rows * 4));
+    MSR_CUDA_CHECK(scratch.alloc(&ci, (size_t)(n_rows + 1) * 8));
+    MSR_CUDA_CHECK(scratch.alloc(&ct, (size_t)std::max<uint64_t>(n_c, 1) * 4));
     MSR_CUDA_CHECK(cudaMemcpyAsync(ci, cand_indptr_host, (size_t)(n_rows + 1) * 8, cudaMemcpyHostToDevice, s));
     if (n_c) MSR_CUDA_CHECK(cudaMemcpyAsync(ct, cand_tokens_host, (size_t)n_c * 4, cudaMemcpyHostToDevice, s));
     if (dtype == 0) cand_select_kernel<float><<<n_rows, 128, 0, s>>>((const float*)logits, row_stride, ci, ct, cap, pitch, ts, td, tc);
@@ -276,7 +291,7 @@ extern "C" int msr_quantise_candidates(int device, uint32_t n_rows, uint32_t voc
     else cand_select_kernel<__nv_bfloat16><<<n_rows, 128, 0, s>>>((const __nv_bfloat16*)logits, row_stride, ci, ct, cap, pitch, ts, td, tc);
     count_launch();
     // rows without a candidate (encode.py:103-112): top-`fallback_top` of the whole vocabulary
-    if (!empty_rows.empty() && dtype != 0) MSR_CUDA_CHECK(cudaMallocAsync(&f32, (size_t)vocab * 4, s));
+    if (!empty_rows.empty() && dtype != 0) MSR_CUDA_CHECK(scratch.alloc(&f32, (size_t)vocab * 4));
     for (uint32_t r : empty_rows) {
         const float* row = (const float*)logits + (size_t)r * row_stride;
         if (dtype == 1) { rows_to_f32_kernel<__half><<<148, 256, 0, s>>>((const __half*)logits + (size_t)r * row_stride, row_stride, 1, vocab, f32); row = f32; count_launch(); }
@@ -288,10 +303,10 @@ extern "C" int msr_quantise_candidates(int device, uint32_t n_rows, uint32_t voc
         // expansion terms, a block of rows at a time (scratch: masked fp32 rows, <= 256 MB)
         const uint32_t rows_per = (uint32_t)std::max<size_t>(1, std::min<size_t>(n_rows, ((size_t)256 << 20) / ((size_t)vocab * 4)));
         float* masked = nullptr; float* es = nullptr; int32_t* ed = nullptr; uint32_t* ec = nullptr;
-        MSR_CUDA_CHECK(cudaMallocAsync(&masked, (size_t)rows_per * vocab * 4, s));
-        MSR_CUDA_CHECK(cudaMallocAsync(&es, (size_t)rows_per * n_expand * 4, s));
-        MSR_CUDA_CHECK(cudaMallocAsync(&ed, (size_t)rows_per * n_expand * 4, s));
-        MSR_CUDA_CHECK(cudaMallocAsync(&ec, (size_t)rows_per * 4, s));
+        MSR_CUDA_CHECK(scratch.alloc(&masked, (size_t)rows_per * vocab * 4));
+        MSR_CUDA_CHECK(scratch.alloc(&es, (size_t)rows_per * n_expand * 4));
+        MSR_CUDA_CHECK(scratch.alloc(&ed, (size_t)rows_per * n_expand * 4));
+        MSR_CUDA_CHECK(scratch.alloc(&ec, (size_t)rows_per * 4));
         for (uint32_t r0 = 0; r0 < n_rows && rc == MSR_OK; r0 += rows_per) {
             const uint32_t nr = std::min(rows_per, n_rows - r0);
             const unsigned g = (unsigned)std::min<size_t>(((size_t)nr * vocab + 255) / 256, 148 * 32);
@@ -305,7 +320,6 @@ extern "C" int msr_quantise_candidates(int device, uint32_t n_rows, uint32_t voc
             expand_append_kernel<<<(nr + 127) / 128, 128, 0, s>>>(es, ed, n_expand, r0, nr, pitch, ts, td, tc);
             count_launch();
         }
-        cudaFreeAsync(masked, s); cudaFreeAsync(es, s); cudaFreeAsync(ed, s); cudaFreeAsync(ec, s);
     }
     if (rc == MSR_OK) {
         const uint32_t wpb = 4;
@@ -316,7 +330,5 @@ extern "C" int msr_quantise_candidates(int device, uint32_t n_rows, uint32_t voc
     }
     // the host arrays were read by an async copy from pageable memory; make the call safe to return from
     cudaStreamSynchronize(s);
-    if (f32) cudaFreeAsync(f32, s);
-    cudaFreeAsync(ts, s); cudaFreeAsync(td, s); cudaFreeAsync(tc, s); cudaFreeAsync(ci, s); cudaFreeAsync(ct, s);
     return rc;
 }
