@@ -49,6 +49,9 @@ def parse_args():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="budget of the cpu_baseline leg")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--chunks", type=int, default=1, help="query chunks of the pipelined multi-GPU exchange (1 = score -> gather -> merge; more was not faster)")
+    ap.add_argument("--exchange", default="auto", choices=["auto", "p2p", "nccl"],
+                    help="multi-GPU exchange: p2p = fused into the tile-merge epilogue over symmetric memory (PeerExchange); "
+                         "nccl = all-gather (PipelinedExchange); auto = p2p when it can be set up")
     ap.add_argument("--check", type=int, default=32, help="queries verified against the oracle after the run")
     ap.add_argument("--workload", default="sparse", choices=["sparse", "dense", "hybrid", "config5"],
                     help="sparse = the headline metric (default); dense / hybrid = the other kernels of the path (bench_extra.py)")
@@ -72,7 +75,7 @@ def workload_config(a, world):
     return {"workload": f"synthetic {a.n_docs}-doc vocab-sparse index (Zipf s=1, V={a.vocab}, {a.nnz_per_doc} nnz/doc), "
                         f"{a.nq} queries x {a.q_len} terms, top-{a.k} ({named})",
             "n_docs": a.n_docs, "nq": a.nq, "q_len": a.q_len, "k": a.k, "vocab": a.vocab, "seed": a.seed,
-            "sharding": f"doc-range x{world} + NCCL all-gather merge, {a.chunks}-chunk pipelined exchange" if world > 1 else "single GPU",
+            "sharding": f"doc-range x{world}, exchange={a.exchange}" if world > 1 else "single GPU",
             "l2": "index (4 B/posting physical, >= 512 MB) is larger than the 126 MB L2; no explicit flush"}
 
 
@@ -263,7 +266,26 @@ def run_ours(a, rank, world, local_rank):
     ex = PipelinedExchange(nq, k, dev, world, chunks=a.chunks if world > 1 else 1)
     q_chunks = [qs.slice(lo, hi) for lo, hi in ex.chunks()]
 
+    # fused exchange over peer memory when available (one chunk): no NCCL call on the path
+    px = None
+    if world > 1 and a.exchange != "nccl" and a.chunks == 1:
+        try:
+            from mllm_sparse_retrieval_b200.sharded import PeerExchange
+            px = PeerExchange(nq, k, dev, world, rank)
+        except Exception as e:                                   # symmetric memory unavailable: NCCL all-gather instead
+            if a.exchange == "p2p":
+                raise
+            sys.stderr.write(f"[bench] rank {rank}: PeerExchange unavailable ({type(e).__name__}: {e}); using NCCL\n")
+            px = None
+        # all ranks must agree (a rendezvous that failed on one rank fails on all, but be explicit)
+        flag = torch.tensor([1 if px is not None else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        if int(flag.item()) == 0:
+            px = None
+
     def step_device():
+        if px is not None:
+            return px.run(idx, lambda o: idx.search(qs.indptr, qs.terms, qs.weights, k, out=o))
         return ex.run(lambda i, lo, hi, o: idx.search(q_chunks[i].indptr, q_chunks[i].terms, q_chunks[i].weights, k, out=o))
 
     # e2e: pinned host buffers.  1 GPU: the MSR_HOST path of the C ABI.  N GPUs: every rank copies the pinned query CSR
@@ -285,7 +307,7 @@ def run_ours(a, rank, world, local_rank):
         def chunk(i, lo, hi, o):
             a0, a1 = cuts[i]
             idx.search(d_q[0][lo:hi + 1] - a0, d_q[1][a0:a1], d_q[2][a0:a1], k, out=o)
-        m = ex.run(chunk)
+        m = px.run(idx, lambda o: idx.search(d_q[0], d_q[1], d_q[2], k, out=o)) if px is not None else ex.run(chunk)
         if rank == 0:
             for dst, src in zip(h_out, m):
                 dst.copy_(src, non_blocking=True)
@@ -367,9 +389,13 @@ def run_ours(a, rank, world, local_rank):
            "vs_baseline": None, "dtype": "u32", "data": "synthetic", "config": workload_config(a, world),
            "e2e": {"value": nq * a.steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                    "api": "msr_sparse_search(MSR_HOST) with pinned host buffers" if world == 1 else
-                          "pinned query CSR -> msr_sparse_search(MSR_DEVICE) per shard -> NCCL all-gather -> msr_topk_merge -> "
-                          "pinned host lists on rank 0"},
+                          ("pinned query CSR -> msr_sparse_search(MSR_DEVICE) per shard with the exchange fused into the tile-merge "
+                           "epilogue (peer stores over NVLink, symmetric memory) -> barrier -> msr_topk_merge_strided -> pinned host "
+                           "lists on rank 0" if px is not None else
+                           "pinned query CSR -> msr_sparse_search(MSR_DEVICE) per shard -> NCCL all-gather -> msr_topk_merge -> "
+                           "pinned host lists on rank 0")},
            "gpu_launches": int(launches), "roofline": roof, "clocks": clocks, "parity_check": check,
+           "exchange": "single GPU" if world == 1 else ("p2p: fused peer stores + signal-pad barrier" if px is not None else "nccl all-gather"),
            "index": {"n_tiles": idx.n_tiles, "tile_docs": idx.tile_docs, "nnz_shard": idx.nnz, "resident_bytes": idx.resident_bytes}}
     if idx.resident_bytes * world < (126 << 20):
         res["config"]["l2"] = (f"index ({idx.resident_bytes * world >> 20} MB) fits the 126 MB L2: launch / latency-bound, "

@@ -120,6 +120,26 @@ int msr_topk_merge(int device, uint32_t n_lists, uint32_t nq, uint32_t k_in,
                    uint32_t k, float* out_scores, int32_t* out_docs, uint32_t* out_counts, void* stream);
 
 /*
+ * msr_topk_merge over lists that are not packed back to back: list j starts list_stride elements after list j-1
+ * (scores and docs) and count_list_stride elements (counts).  This is the layout of a symmetric-memory result buffer
+ * [world][scores nq*k | docs nq*k | counts nq] that the fused exchange below fills.
+ */
+int msr_topk_merge_strided(int device, uint32_t n_lists, uint32_t nq, uint32_t k_in, const float* scores,
+                           const int32_t* docs, const uint32_t* counts, size_t list_stride, size_t count_list_stride,
+                           uint32_t k, float* out_scores, int32_t* out_docs, uint32_t* out_counts, void* stream);
+
+/*
+ * Fused exchange of the doc-sharded search: after this call every MSR_DEVICE search on the handle stores
+ * its merged result rows not only into out_* but ALSO into peer_scores[p] / peer_docs[p] / peer_counts[p] for p < n_peers
+ * -- [nq,k] / [nq,k] / [nq] slots in the memory of other GPUs (peer pointers, e.g. from torch symmetric memory),
+ * written by the epilogue of the tile-merge kernel over NVLink.  It replaces the all-gather that would follow the
+ * search; the caller still has to synchronise the GPUs (a signal-pad barrier) before it merges the slots with
+ * msr_topk_merge_strided.  n_peers = 0 switches it off.  At most 16 peers.
+ */
+int msr_sparse_set_peer_outputs(msr_sparse_index* h, uint32_t n_peers, float* const* peer_scores,
+                                int32_t* const* peer_docs, uint32_t* const* peer_counts);
+
+/*
  * Stand-alone radix-select top-k over dense score rows (kernel (b) on its own): scores [nq, n] row-major
  * fp32 on the device; output k best per row by (score desc, column asc), columns offset by col_base.
  * Entries equal to -inf are never returned (counts < k possible).

@@ -48,6 +48,8 @@ def _declare(lib):
         "msr_quantise_topk": (I, [I, U32, U32, P, I, ctypes.c_size_t, U32, U32, P, I, P, P, P, P]),
         "msr_quantise_candidates": (I, [I, U32, U32, P, I, ctypes.c_size_t, P, P, U32, U32, U32, P, I, P, U32, P, P, P, P]),
         "msr_provenance_hist": (I, [I, U32, P, P, ctypes.c_size_t, P, U32, P, P]),
+        "msr_topk_merge_strided": (I, [I, U32, U32, U32, P, P, P, ctypes.c_size_t, ctypes.c_size_t, U32, P, P, P, P]),
+        "msr_sparse_set_peer_outputs": (I, [P, U32, P, P, P]),
         "msr_jsonl_parse": (I, [ctypes.POINTER(ctypes.c_char_p), U32, ctypes.POINTER(P)]),
         "msr_collection_info": (I, [P, P]),
         "msr_collection_export": (I, [P, P, P, P, P, P, P, P, P]),

@@ -46,7 +46,8 @@ constexpr int kBuildWarps = 8;                 // warps per CTA of the bucket la
 
 int topk_merge_keys_launch(uint32_t nq, uint32_t n_lists, uint32_t stride, const uint64_t* keys,
                            const uint32_t* cnts, uint32_t k, float* out_scores, int32_t* out_docs,
-                           uint32_t* out_counts, cudaStream_t s);
+                           uint32_t* out_counts, cudaStream_t s, uint32_t n_peers, float* const* peer_scores,
+                           int32_t* const* peer_docs, uint32_t* const* peer_counts, size_t peer_row0);
 
 }  // namespace msr
 
@@ -76,6 +77,11 @@ struct msr_sparse_index {
     bool profiling = false;
     std::vector<cudaEvent_t> ev;      // triples: before score, after score, after merge
     size_t ev_used = 0;
+    // fused exchange (msr_sparse_set_peer_outputs): result slots on other GPUs that device-path searches also fill
+    uint32_t n_peers = 0;
+    float* peer_scores[16] = {};
+    int32_t* peer_docs[16] = {};
+    uint32_t* peer_counts[16] = {};
 };
 
 namespace msr {
@@ -633,7 +639,8 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
         MSR_CUDA_CHECK(cudaGetLastError());
         if (evs) MSR_CUDA_CHECK(cudaEventRecord(evs[1], s));
         rc = topk_merge_keys_launch(n, h->n_tiles, k_stride, P.cand_keys, P.cand_cnt, k, d_os + (size_t)q0 * k,
-                                    d_od + (size_t)q0 * k, d_oc + q0, s);
+                                    d_od + (size_t)q0 * k, d_oc + q0, s, where == MSR_DEVICE ? h->n_peers : 0u,
+                                    h->peer_scores, h->peer_docs, h->peer_counts, q0);
         if (rc) return rc;
         if (evs) MSR_CUDA_CHECK(cudaEventRecord(evs[2], s));
     }
@@ -682,5 +689,18 @@ extern "C" int msr_sparse_query_work(msr_sparse_index* h, uint32_t nq, const uin
     MSR_CUDA_CHECK(cudaMemcpyAsync(res, h->work, 16, cudaMemcpyDeviceToHost, s));
     MSR_CUDA_CHECK(cudaStreamSynchronize(s));
     *postings = res[0]; *kept_terms = res[1];
+    return MSR_OK;
+}
+
+extern "C" int msr_sparse_set_peer_outputs(msr_sparse_index* h, uint32_t n_peers, float* const* peer_scores,
+                                           int32_t* const* peer_docs, uint32_t* const* peer_counts) {
+    MSR_REQUIRE(h, "msr_sparse_set_peer_outputs: NULL handle");
+    MSR_REQUIRE(n_peers <= 16, "msr_sparse_set_peer_outputs: at most 16 peers");
+    MSR_REQUIRE(n_peers == 0 || (peer_scores && peer_docs && peer_counts), "msr_sparse_set_peer_outputs: NULL pointer table");
+    for (uint32_t p = 0; p < n_peers; ++p) {
+        MSR_REQUIRE(peer_scores[p] && peer_docs[p] && peer_counts[p], "msr_sparse_set_peer_outputs: NULL peer pointer %u", p);
+        h->peer_scores[p] = peer_scores[p]; h->peer_docs[p] = peer_docs[p]; h->peer_counts[p] = peer_counts[p];
+    }
+    h->n_peers = n_peers;
     return MSR_OK;
 }

@@ -10,6 +10,7 @@
 namespace msr {
 
 constexpr int kMergeThreads = 256;
+constexpr int kMaxPeers = 16;
 
 struct MergeParams {
     uint32_t nq, n_lists, stride, k, mode;   // mode 0: packed keys [nq][n_lists][stride]; 1: arrays [n_lists][nq][stride]
@@ -21,6 +22,14 @@ struct MergeParams {
     int32_t* out_docs;
     uint32_t* out_counts;
     uint32_t cap;                            // shared-memory capacity in keys (power of two, >= k + stride)
+    size_t list_stride;                      // mode 1: elements between consecutive lists (0 = nq * stride, packed)
+    size_t cnt_list_stride;                  // mode 1: elements between the count rows of consecutive lists (0 = nq)
+    // Fused exchange (doc-sharded search): the merged rows are ALSO stored into the result slots of up to kMaxPeers
+    // other GPUs over NVLink (peer pointers from symmetric memory), so no separate all-gather follows.
+    uint32_t n_peers;
+    float* peer_scores[kMaxPeers];
+    int32_t* peer_docs[kMaxPeers];
+    uint32_t* peer_counts[kMaxPeers];
 };
 
 __device__ __forceinline__ uint32_t pow2_ceil(uint32_t x) {
@@ -44,7 +53,8 @@ topk_merge_kernel(const MergeParams P) {
         uint32_t mine = 0;
         for (uint32_t j = tid; j < P.n_lists; j += kMergeThreads) {
             const size_t li = P.mode == 0 ? (size_t)q * P.n_lists + j : (size_t)j * P.nq + q;
-            mine += min(P.cnts[li], P.stride);
+            const size_t ci = (P.mode == 1 && P.cnt_list_stride) ? (size_t)j * P.cnt_list_stride + q : li;
+            mine += min(P.cnts[ci], P.stride);
         }
         mine = warp_reduce_add(mine);
         if ((tid & 31) == 0 && mine) atomicAdd(&s_total, mine);
@@ -55,7 +65,9 @@ topk_merge_kernel(const MergeParams P) {
         const uint32_t lane = tid & 31, warp = tid >> 5;
         for (uint32_t j = warp; j < P.n_lists; j += kMergeThreads / 32) {
             const size_t li = P.mode == 0 ? (size_t)q * P.n_lists + j : (size_t)j * P.nq + q;
-            const uint32_t c = min(P.cnts[li], P.stride);
+            const size_t ci = (P.mode == 1 && P.cnt_list_stride) ? (size_t)j * P.cnt_list_stride + q : li;
+            const size_t ro = (P.mode == 1 && P.list_stride) ? (size_t)j * P.list_stride + (size_t)q * P.stride : li * P.stride;
+            const uint32_t c = min(P.cnts[ci], P.stride);
             if (c == 0) continue;
             uint32_t base = 0;
             if (lane == 0) base = atomicAdd(&s_fill, c);
@@ -64,8 +76,8 @@ topk_merge_kernel(const MergeParams P) {
                 const uint64_t* src = P.keys + li * P.stride;
                 for (uint32_t i = lane; i < c; i += 32) buf[base + i] = src[i];
             } else {
-                const float* ss = P.scores + li * P.stride;
-                const int32_t* dd = P.docs + li * P.stride;
+                const float* ss = P.scores + ro;
+                const int32_t* dd = P.docs + ro;
                 for (uint32_t i = lane; i < c; i += 32) buf[base + i] = make_key(ss[i], (uint32_t)dd[i]);
             }
         }
@@ -74,7 +86,9 @@ topk_merge_kernel(const MergeParams P) {
     }
     for (uint32_t j = 0; j < P.n_lists && !all_fit; ++j) {
         const size_t li = P.mode == 0 ? (size_t)q * P.n_lists + j : (size_t)j * P.nq + q;
-        const uint32_t c = min(P.cnts[li], P.stride);
+        const size_t ci = (P.mode == 1 && P.cnt_list_stride) ? (size_t)j * P.cnt_list_stride + q : li;
+        const size_t ro = (P.mode == 1 && P.list_stride) ? (size_t)j * P.list_stride + (size_t)q * P.stride : li * P.stride;
+        const uint32_t c = min(P.cnts[ci], P.stride);
         if (c == 0) continue;
         if (fill + c > P.cap) {
             const uint32_t n2 = pow2_ceil(fill);
@@ -86,8 +100,8 @@ topk_merge_kernel(const MergeParams P) {
             const uint64_t* src = P.keys + li * P.stride;
             for (uint32_t i = tid; i < c; i += kMergeThreads) buf[fill + i] = src[i];
         } else {
-            const float* ss = P.scores + li * P.stride;
-            const int32_t* dd = P.docs + li * P.stride;
+            const float* ss = P.scores + ro;
+            const int32_t* dd = P.docs + ro;
             for (uint32_t i = tid; i < c; i += kMergeThreads) buf[fill + i] = make_key(ss[i], (uint32_t)dd[i]);
         }
         fill += c;
@@ -104,10 +118,19 @@ topk_merge_kernel(const MergeParams P) {
     for (uint32_t r = tid; r < P.k; r += kMergeThreads) {
         const bool ok = r < n;
         const uint64_t key = ok ? buf[r] : 0;
-        P.out_scores[(size_t)q * P.k + r] = ok ? key_score(key) : 0.0f;
-        P.out_docs[(size_t)q * P.k + r] = ok ? (int32_t)key_doc(key) : -1;
+        const float sc = ok ? key_score(key) : 0.0f;
+        const int32_t dc = ok ? (int32_t)key_doc(key) : -1;
+        P.out_scores[(size_t)q * P.k + r] = sc;
+        P.out_docs[(size_t)q * P.k + r] = dc;
+        for (uint32_t p = 0; p < P.n_peers; ++p) {               // the exchange: same row into every peer's slot
+            P.peer_scores[p][(size_t)q * P.k + r] = sc;
+            P.peer_docs[p][(size_t)q * P.k + r] = dc;
+        }
     }
-    if (tid == 0) P.out_counts[q] = n;
+    if (tid == 0) {
+        P.out_counts[q] = n;
+        for (uint32_t p = 0; p < P.n_peers; ++p) P.peer_counts[p][q] = n;
+    }
 }
 
 static int merge_launch(MergeParams P, cudaStream_t s) {
@@ -131,10 +154,18 @@ static int merge_launch(MergeParams P, cudaStream_t s) {
 }
 
 int topk_merge_keys_launch(uint32_t nq, uint32_t n_lists, uint32_t stride, const uint64_t* keys, const uint32_t* cnts,
-                           uint32_t k, float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s) {
+                           uint32_t k, float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s,
+                           uint32_t n_peers, float* const* peer_scores, int32_t* const* peer_docs,
+                           uint32_t* const* peer_counts, size_t peer_row0) {
     MergeParams P{};
     P.nq = nq; P.n_lists = n_lists; P.stride = stride; P.k = k; P.mode = 0;
     P.keys = keys; P.cnts = cnts; P.out_scores = out_scores; P.out_docs = out_docs; P.out_counts = out_counts;
+    P.n_peers = n_peers;
+    for (uint32_t p = 0; p < n_peers; ++p) {                      // peer_row0: first query of this launch in the batch
+        P.peer_scores[p] = peer_scores[p] + peer_row0 * k;
+        P.peer_docs[p] = peer_docs[p] + peer_row0 * k;
+        P.peer_counts[p] = peer_counts[p] + peer_row0;
+    }
     return merge_launch(P, s);
 }
 
@@ -352,6 +383,24 @@ extern "C" int msr_topk_merge(int device, uint32_t n_lists, uint32_t nq, uint32_
     MergeParams P{};
     P.nq = nq; P.n_lists = n_lists; P.stride = k_in; P.k = k; P.mode = 1;
     P.scores = scores; P.docs = docs; P.cnts = counts;
+    P.out_scores = out_scores; P.out_docs = out_docs; P.out_counts = out_counts;
+    return merge_launch(P, (cudaStream_t)stream);
+}
+
+extern "C" int msr_topk_merge_strided(int device, uint32_t n_lists, uint32_t nq, uint32_t k_in, const float* scores,
+                                      const int32_t* docs, const uint32_t* counts, size_t list_stride,
+                                      size_t count_list_stride, uint32_t k, float* out_scores, int32_t* out_docs,
+                                      uint32_t* out_counts, void* stream) {
+    MSR_REQUIRE(n_lists >= 1 && k >= 1 && k_in >= 1, "msr_topk_merge_strided: n_lists, k, k_in must be >= 1");
+    MSR_REQUIRE(k <= MSR_MAX_K && k_in <= MSR_MAX_K, "msr_topk_merge_strided: k/k_in above %u", MSR_MAX_K);
+    MSR_REQUIRE(list_stride >= (size_t)nq * k_in && count_list_stride >= nq, "msr_topk_merge_strided: list strides too small");
+    if (nq == 0) return MSR_OK;
+    MSR_REQUIRE(scores && docs && counts && out_scores && out_docs && out_counts, "msr_topk_merge_strided: NULL buffer");
+    int rc = use_device(device);
+    if (rc) return rc;
+    MergeParams P{};
+    P.nq = nq; P.n_lists = n_lists; P.stride = k_in; P.k = k; P.mode = 1;
+    P.scores = scores; P.docs = docs; P.cnts = counts; P.list_stride = list_stride; P.cnt_list_stride = count_list_stride;
     P.out_scores = out_scores; P.out_docs = out_docs; P.out_counts = out_counts;
     return merge_launch(P, (cudaStream_t)stream);
 }

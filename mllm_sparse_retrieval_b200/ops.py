@@ -82,6 +82,14 @@ class SparseIndex:
                                                 current_stream_ptr(self.device)))
         return out
 
+    def set_peer_outputs(self, peer_scores=(), peer_docs=(), peer_counts=()):
+        """Fused exchange (msr_sparse_set_peer_outputs): device-path searches also store their merged rows into these
+        raw device addresses (ints: [nq,k] f32 / [nq,k] i32 / [nq] i32 slots on other GPUs).  Empty = off."""
+        n = len(peer_scores)
+        assert n == len(peer_docs) == len(peer_counts)
+        arr = lambda xs: (ctypes.c_void_p * max(1, n))(*[ctypes.c_void_p(int(x)) for x in xs])
+        check(_lib.load().msr_sparse_set_peer_outputs(self._h, n, arr(peer_scores), arr(peer_docs), arr(peer_counts)))
+
     def status(self):
         """Synchronise and raise MsrError(MSR_ERR_RANGE) if an earlier device-path search left the exact range."""
         with torch.cuda.device(self.device):
@@ -139,6 +147,16 @@ def topk_merge(scores, docs, counts, k, out=None):
         check(_lib.load().msr_topk_merge(di, n_lists, nq, k_in, ptr(scores.contiguous()), ptr(docs.contiguous()),
                                          ptr(counts.contiguous()), int(k), ptr(out[0]), ptr(out[1]), ptr(out[2]),
                                          current_stream_ptr(di)))
+    return out
+
+
+def topk_merge_strided(scores_ptr, docs_ptr, counts_ptr, n_lists, nq, k_in, list_stride, count_list_stride, k, out, device):
+    """msr_topk_merge_strided over raw device addresses (a symmetric-memory result buffer); ``out`` = (f32, i32, i32)."""
+    di = _dev_index(device)
+    with torch.cuda.device(di):
+        check(_lib.load().msr_topk_merge_strided(di, n_lists, nq, k_in, ctypes.c_void_p(scores_ptr), ctypes.c_void_p(docs_ptr),
+                                                 ctypes.c_void_p(counts_ptr), list_stride, count_list_stride, int(k),
+                                                 ptr(out[0]), ptr(out[1]), ptr(out[2]), current_stream_ptr(di)))
     return out
 
 

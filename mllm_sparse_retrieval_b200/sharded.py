@@ -72,3 +72,53 @@ class PipelinedExchange:
                 ops.topk_merge(g_s, g_d, g_c, self.k, out=tuple(t[lo:hi] for t in self.final))
         main.wait_stream(self.side)
         return self.final
+
+
+class PeerExchange:
+    """The same exchange with the transfer FUSED into the scorer's last kernel: the tile-merge epilogue of every rank
+    stores its [nq,k] result rows straight into that rank's slot of a symmetric-memory buffer on every other GPU (NVLink
+    peer stores, ``msr_sparse_set_peer_outputs``), a signal-pad barrier follows, and ``msr_topk_merge_strided`` merges
+    the slots in place.  No NCCL call is on the path.  Two buffers alternate, so a rank that runs ahead writes the slots of
+    step n+1 while a slower peer still merges step n; the barrier of step n+1 orders the reuse two steps later.
+
+    Buffer of one step, in 4-byte units: [world][ scores nq*k | docs nq*k | counts nq ].  Raises (RuntimeError / ImportError)
+    when symmetric memory cannot be set up; callers fall back to ``PipelinedExchange`` (NCCL)."""
+
+    def __init__(self, nq, k, device, world, rank, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.nq, self.k, self.device, self.world, self.rank = nq, k, torch.device(device), world, rank
+        group = group if group is not None else dist.group.WORLD
+        self.slot = 2 * nq * k + nq                                   # 4-byte units per (step buffer, rank)
+        self.buf = symm_mem.empty((2 * world * self.slot,), dtype=torch.int32, device=self.device)
+        self.hdl = symm_mem.rendezvous(self.buf, group)
+        self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        self.final = (torch.empty((nq, k), dtype=torch.float32, device=self.device),
+                      torch.empty((nq, k), dtype=torch.int32, device=self.device),
+                      torch.empty((nq,), dtype=torch.int32, device=self.device))
+        self.step = 0
+        self.hdl.barrier(channel=0)
+
+    def _slot_ptrs(self, base, parity, who):
+        b = base + 4 * ((parity * self.world + who) * self.slot)
+        return b, b + 4 * self.nq * self.k, b + 8 * self.nq * self.k
+
+    def run(self, index, search):
+        """search(out_views) runs ONE device-path search of the whole batch on ``index`` (a ``SparseIndex``) writing
+        (scores, ids, counts) into out_views; returns the merged result of all shards on the current stream."""
+        par = self.step & 1
+        self.step += 1
+        peers = [self._slot_ptrs(self.ptrs[r], par, self.rank) for r in range(self.world) if r != self.rank]
+        index.set_peer_outputs([p[0] for p in peers], [p[1] for p in peers], [p[2] for p in peers])
+        try:
+            # the local slot is the search's own output: views into the symmetric buffer
+            o = self.slot * (par * self.world + self.rank)
+            nk = self.nq * self.k
+            out = (self.buf[o:o + nk].view(torch.float32).view(self.nq, self.k), self.buf[o + nk:o + 2 * nk].view(self.nq, self.k),
+                   self.buf[o + 2 * nk:o + 2 * nk + self.nq])
+            search(out)
+        finally:
+            index.set_peer_outputs()
+        self.hdl.barrier(channel=0)                                     # every rank's rows have landed everywhere
+        s0, d0, c0 = self._slot_ptrs(self.ptrs[self.rank], par, 0)
+        ops.topk_merge_strided(s0, d0, c0, self.world, self.nq, self.k, self.slot, self.slot, self.k, self.final, self.device)
+        return self.final

@@ -1,0 +1,82 @@
+"""Two-GPU test of the fused exchange: PeerExchange (peer stores from the tile-merge epilogue into
+symmetric memory + signal-pad barrier + msr_topk_merge_strided) must equal the NCCL all-gather exchange and the unsharded
+oracle, bit for bit, over several steps (the two step buffers alternate).  Skipped on a one-GPU box."""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from helpers import random_csr, random_queries
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _problem():
+    rng = np.random.default_rng(77)
+    n_docs, n_terms = 9000, 1500
+    indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 48)
+    qs = [random_queries(rng, 64, n_terms, 16) for _ in range(3)]         # a different batch per step
+    return n_docs, n_terms, indptr, docids, impacts, qs
+
+
+def _worker(rank, world, port, k, out_path):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        from mllm_sparse_retrieval_b200.ops import SparseIndex
+        from mllm_sparse_retrieval_b200.sharded import PeerExchange, PipelinedExchange
+        n_docs, n_terms, indptr, docids, impacts, qs = _problem()
+        df = np.diff(indptr.astype(np.int64)).astype(np.uint32)
+        lo, hi = n_docs * rank // world, n_docs * (rank + 1) // world
+        m = (docids >= lo) & (docids < hi)
+        ip = np.zeros(n_terms + 1, dtype=np.uint64)
+        np.cumsum(np.bincount(np.repeat(np.arange(n_terms), df)[m], minlength=n_terms), out=ip[1:])
+        idx = SparseIndex(ip, docids[m] - lo, impacts[m], hi - lo, n_docs_global=n_docs, df_global=df, doc_base=lo,
+                          tile_docs=700, device=rank)
+        nq = 64
+        px = PeerExchange(nq, k, dev, world, rank)
+        ex = PipelinedExchange(nq, k, dev, world)
+        res = {}
+        for step, (qi, qt, qw) in enumerate(qs):
+            dq = (torch.from_numpy(qi.astype(np.int64)).to(dev), torch.from_numpy(qt.astype(np.int32)).to(dev),
+                  torch.from_numpy(qw.astype(np.int32)).to(dev))
+            a = [t.clone() for t in px.run(idx, lambda o: idx.search(*dq, k, out=o))]
+            b = [t.clone() for t in ex.run(lambda i, l, h, o: idx.search(*dq, k, out=o))]
+            torch.cuda.synchronize()
+            for x, y in zip(a, b):
+                assert torch.equal(x, y), f"rank {rank} step {step}: p2p exchange != NCCL exchange"
+            res[f"s{step}"], res[f"d{step}"], res[f"c{step}"] = (t.cpu().numpy() for t in a)
+        np.savez(out_path + f".{rank}.npz", **res)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs with peer access")
+@pytest.mark.parametrize("k", [100])
+def test_peer_exchange_two_gpus(oracle, lib_built, tmp_path, k):
+    out = str(tmp_path / "px")
+    mp.spawn(_worker, args=(2, _free_port(), k, out), nprocs=2, join=True)
+    n_docs, n_terms, indptr, docids, impacts, qs = _problem()
+    for r in range(2):                                                    # every rank ends with the full result
+        got = np.load(out + f".{r}.npz")
+        for step, (qi, qt, qw) in enumerate(qs):
+            es, ed, ec = oracle.impact_search_c(indptr, docids, impacts, n_docs, qi, qt, qw, k, threads=4)
+            np.testing.assert_array_equal(got[f"c{step}"].astype(np.uint32), ec)
+            np.testing.assert_array_equal(got[f"d{step}"], ed)
+            np.testing.assert_array_equal(got[f"s{step}"], es)

@@ -239,3 +239,69 @@ def test_threshold_read_is_uniform_per_cta_under_cold_timing(oracle, lib_built):
             np.testing.assert_array_equal(d.cpu().numpy(), exp[1])
             np.testing.assert_array_equal(s.cpu().numpy(), exp[0])
         idx.close()
+
+
+def test_fused_exchange_slots_and_strided_merge(oracle, lib_built):
+    """SURVEY.md 8(e), fused exchange: with msr_sparse_set_peer_outputs every shard's tile-merge epilogue also stores its
+    rows into its slot of the other "GPUs'" exchange buffers ([world][scores nq*k | docs nq*k | counts nq], here all on one
+    device), and msr_topk_merge_strided over any of those buffers equals the unsharded search.  Bit-exact."""
+    from mllm_sparse_retrieval_b200.ops import SparseIndex, topk_merge_strided
+    rng = np.random.default_rng(23)
+    n_docs, n_terms, k, nq, G = 6000, 1200, 100, 37, 3
+    indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 40)
+    qi, qt, qw = random_queries(rng, nq, n_terms, 16)
+    ref = oracle.impact_search_c(indptr, docids, impacts, n_docs, qi, qt, qw, k, threads=4)
+    df = np.diff(indptr.astype(np.int64)).astype(np.uint32)
+    term_of = np.repeat(np.arange(n_terms), df)
+    dq = _dev_queries(qi, qt, qw)
+    dev = torch.device("cuda")
+    slot = 2 * nq * k + nq + 5                                            # padded: strides need not be tight
+    bufs = [torch.full((G * slot,), -7, dtype=torch.int32, device=dev) for _ in range(G)]   # one per emulated GPU
+
+    def slot_ptrs(b, who):
+        p = b.data_ptr() + 4 * who * slot
+        return p, p + 4 * nq * k, p + 8 * nq * k
+
+    bounds = np.linspace(0, n_docs, G + 1).astype(int)
+    for g in range(G):
+        lo, hi = bounds[g], bounds[g + 1]
+        m = (docids >= lo) & (docids < hi)
+        ip = np.zeros(n_terms + 1, dtype=np.uint64)
+        np.cumsum(np.bincount(term_of[m], minlength=n_terms), out=ip[1:])
+        idx = SparseIndex(ip, docids[m] - lo, impacts[m], hi - lo, n_docs_global=n_docs, df_global=df,
+                          doc_base=int(lo), tile_docs=500)
+        peers = [slot_ptrs(bufs[r], g) for r in range(G) if r != g]
+        idx.set_peer_outputs([p[0] for p in peers], [p[1] for p in peers], [p[2] for p in peers])
+        o = g * slot
+        own = (bufs[g][o:o + nq * k].view(torch.float32).view(nq, k), bufs[g][o + nq * k:o + 2 * nq * k].view(nq, k),
+               bufs[g][o + 2 * nq * k:o + 2 * nq * k + nq])
+        idx.search(*dq, k, out=own)
+        idx.set_peer_outputs()                                            # off again: the next search must not touch the slots
+        before = [b.clone() for b in bufs]
+        idx.search(*dq, k)
+        torch.cuda.synchronize()
+        for b, b0 in zip(bufs, before):
+            assert torch.equal(b, b0)
+        idx.close()
+    for r in range(G):                                                    # every "GPU" holds the same G lists
+        assert torch.equal(bufs[r], bufs[0])
+        out = (torch.empty((nq, k), dtype=torch.float32, device=dev), torch.empty((nq, k), dtype=torch.int32, device=dev),
+               torch.empty((nq,), dtype=torch.int32, device=dev))
+        s0, d0, c0 = slot_ptrs(bufs[r], 0)
+        topk_merge_strided(s0, d0, c0, G, nq, k, slot, slot, k, out, dev)
+        np.testing.assert_array_equal(out[2].cpu().numpy().astype(np.uint32), ref[2])
+        np.testing.assert_array_equal(out[1].cpu().numpy(), ref[1])
+        np.testing.assert_array_equal(out[0].cpu().numpy(), ref[0])
+    pad = bufs[0].view(G, slot)[:, 2 * nq * k + nq:]
+    assert bool((pad == -7).all())                                        # nothing written past a slot
+
+
+def test_strided_merge_rejects_short_strides(lib_built):
+    from mllm_sparse_retrieval_b200._lib import MsrError
+    from mllm_sparse_retrieval_b200.ops import topk_merge_strided
+    dev = torch.device("cuda")
+    b = torch.zeros(4096, dtype=torch.int32, device=dev)
+    out = (torch.empty((4, 10), dtype=torch.float32, device=dev), torch.empty((4, 10), dtype=torch.int32, device=dev),
+           torch.empty((4,), dtype=torch.int32, device=dev))
+    with pytest.raises(MsrError):
+        topk_merge_strided(b.data_ptr(), b.data_ptr(), b.data_ptr(), 2, 4, 10, 39, 4, 10, out, dev)
