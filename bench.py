@@ -75,7 +75,7 @@ def workload_config(a, world):
     return {"workload": f"synthetic {a.n_docs}-doc vocab-sparse index (Zipf s=1, V={a.vocab}, {a.nnz_per_doc} nnz/doc), "
                         f"{a.nq} queries x {a.q_len} terms, top-{a.k} ({named})",
             "n_docs": a.n_docs, "nq": a.nq, "q_len": a.q_len, "k": a.k, "vocab": a.vocab, "seed": a.seed,
-            "sharding": f"doc-range x{world}, exchange={a.exchange}" if world > 1 else "single GPU",
+            "sharding": f"doc-range x{world}, per-GPU top-k lists exchanged over NVLink and merged" if world > 1 else "single GPU",
             "l2": "index (4 B/posting physical, >= 512 MB) is larger than the 126 MB L2; no explicit flush"}
 
 

@@ -1,4 +1,8 @@
-"""Doc-sharded exchange step: per-GPU top-k lists -> one all-gather -> merge, pipelined.
+"""Doc-sharded exchange step: per-GPU top-k lists -> every GPU -> merge.
+
+Two implementations: ``PeerExchange`` (default at N > 1 in bench.py) fuses the transfer into the scorer's tile-merge
+epilogue as NVLink peer stores into symmetric memory, with no collective call on the path; ``PipelinedExchange`` is the
+NCCL all-gather form, pipelined over query chunks, and the fallback when symmetric memory cannot be set up.
 
 The document collection is split into contiguous internal-id ranges, one per GPU (the precedent in the reference is
 FAISS ``IndexShards`` behind ``GpuMultipleClonerOptions.shard=True``, src/search.py:265-270).  Every rank scores the
