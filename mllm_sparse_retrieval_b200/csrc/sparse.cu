@@ -74,6 +74,7 @@ struct msr_sparse_index {
     size_t resident_bytes = 0;
     // optional per-kernel timing (msr_sparse_profile): events bracket every score / merge launch on the stream
     bool use_theta = true;            // cross-tile threshold sharing (MSR_SPARSE_NO_THETA=1 in the environment disables)
+    bool fast_select = true;          // exact select bounded by the per-thread maxima first (MSR_SPARSE_FAST_SELECT=0 disables)
     bool profiling = false;
     std::vector<cudaEvent_t> ev;      // triples: before score, after score, after merge
     size_t ev_used = 0;
@@ -350,6 +351,7 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
     h->device = device; h->n_docs = n_docs; h->n_terms = n_terms; h->tile_docs = tile_docs; h->n_tiles = n_tiles;
     h->n_docs_global = n_docs_global; h->doc_base = doc_base; h->nnz = nnz;
     { const char* e = getenv("MSR_SPARSE_NO_THETA"); h->use_theta = !(e && e[0] == '1'); }
+    { const char* e = getenv("MSR_SPARSE_FAST_SELECT"); h->fast_select = !(e && e[0] == '0'); }
     const size_t n_seg = (size_t)n_tiles * n_terms + 1;
     DevBuf b_cnt, b_bad, b_tmp;
     cudaError_t e = cudaSuccess;
@@ -619,6 +621,7 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     // Re-publishing costs a rank count over c + k keys; it pays while the list is still loose.  Measured (k = 100):
     // 6 tiles k/2 3.47 ms, k/4 3.63, k/8 3.68; 21 tiles 10.36 / 10.45 / 10.70; 41 tiles 19.84 (+0.5 ms final merge) / 19.78 / 19.96.
     P.merge_min = std::max(1u, k >> (h->n_tiles <= 24 ? 1 : 2));
+    P.fast_select = h->fast_select ? 1u : 0u;
     const size_t smem = search_smem_bytes(h->tile_docs);
     for (uint32_t q0 = 0; q0 < nq; q0 += qc) {
         const uint32_t n = std::min(qc, nq - q0);

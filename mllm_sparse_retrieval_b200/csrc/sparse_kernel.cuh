@@ -60,6 +60,7 @@ struct SearchParams {
     uint64_t* tlist;              // [nq][k]
     uint32_t use_theta;
     uint32_t merge_min;           // a tile re-publishes the query's threshold list when it adds >= this many candidates
+    uint32_t fast_select;         // exact select through the per-thread-maxima bound first (MSR_SPARSE_FAST_SELECT, default 1)
 };
 
 // One warp per query: exact-arithmetic range check over the kept terms (see msr.h), done once instead of per tile.
@@ -544,6 +545,7 @@ sparse_score_topk_kernel(const SearchParams P) {
     // 2b. exact radix select of the tile's top-k
     const uint4* acc4 = reinterpret_cast<const uint4*>(acc);
     const uint32_t nvec4 = (tl + 3) >> 2;
+    uint32_t tmax = 0;
     {
         // (accumulator slots past tl hold 0, so whole 16-byte vectors are read in all passes of the select)
         uint32_t m = 0, h = 0;
@@ -552,6 +554,7 @@ sparse_score_topk_kernel(const SearchParams P) {
             m = max(max(m, max(x.x, x.y)), max(x.z, x.w));
             h += (x.x != 0) + (x.y != 0) + (x.z != 0) + (x.w != 0);
         }
+        tmax = m;                                               // best score among this thread's own docs
         m = warp_reduce_max(m);
         h = warp_reduce_add(h);
         if (lane == 0) {
@@ -572,6 +575,54 @@ sparse_score_topk_kernel(const SearchParams P) {
         }
         if (tid == 0) *cnt_out = hits;
         return;
+    }
+    // Fast path (k <= threads, scores below 2^24): the threads own disjoint docs, so the k-th largest of the per-thread
+    // maxima is a score g that at least k docs of the tile reach -- and, the maxima being order statistics of ~tl/threads
+    // docs each, only a few more than k do (about 112 of 20 K for k = 100).  g is found by a bitwise search with one
+    // __syncthreads_count per bit; ONE compare pass then collects the docs with score >= g (all of the top k are among
+    // them) and rank counting orders them.  No histogram, no shared atomics on the bulk of the accumulators.
+    if (P.fast_select && P.k <= (uint32_t)kThreads && vmax < (1u << 24)) {
+        uint32_t g = 0;
+        for (int b = 31 - __clz(vmax); b >= 0; --b) {
+            const uint32_t t = g | (1u << b);
+            if ((uint32_t)__syncthreads_count(tmax >= t) >= P.k) g = t;
+        }
+        if (g) {
+            for (uint32_t j = tid; j < nvec4; j += kThreads) {
+                const uint4 x = acc4[j];
+                if (max(max(x.x, x.y), max(x.z, x.w)) >= g) {
+                    const uint32_t e[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const uint32_t i = 4 * j + u;
+                        if (e[u] >= g && i < tl) {
+                            const uint32_t pos = atomicAdd(&S->cand_cnt, 1u);
+                            if (pos < (uint32_t)kThreads) U->keys[pos] = make_key(__uint2float_rn(e[u]), gdoc0 + i);
+                        }
+                    }
+                }
+            }
+            __syncthreads();
+            const uint32_t c = S->cand_cnt;                     // >= k by construction
+            if (c <= (uint32_t)kThreads) {
+                const uint64_t mine = tid < c ? U->keys[tid] : 0ull;
+                uint32_t gt = 0;
+                if (mine) {
+                    for (uint32_t j = 0; j < c; ++j) gt += U->keys[j] > mine;     // distinct docs: distinct keys
+                    if (gt < P.k) {
+                        keys_out[gt] = mine;
+                        if (P.use_theta) {
+                            tlist[gt] = mine;
+                            if (gt == P.k - 1) atomicMax(theta_p, (unsigned long long)mine);
+                        }
+                    }
+                }
+                if (tid == 0) *cnt_out = P.k;
+                return;
+            }
+            __syncthreads();                                    // too many ties at g: the radix select below
+            if (tid == 0) S->cand_cnt = 0;
+        }
     }
     // selection key: integers below 2^24 are their own float32 image; above, rank by the rounded float (S6)
     const bool use_f = vmax >= (1u << 24);
