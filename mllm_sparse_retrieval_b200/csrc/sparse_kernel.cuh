@@ -218,6 +218,24 @@ __device__ __forceinline__ void chunk_apply(const uint32_t (&v)[kUnroll], uint32
     else chunk_apply_kind<2>(v, n, wraw & 0x7FFFFFFFu, lane, acc_s);
 }
 
+// Rank by counting with all threads busy: key i = tid >> pl is shared by 2^pl adjacent lanes, each counting the keys
+// greater than it in its own part of [0, n); the partial counts are summed with shuffles.  Every thread of the CTA calls
+// (n << pl <= kThreads); `mine` returns the key (0 = none), the result is the number of keys greater than it.
+__device__ __forceinline__ uint32_t count_greater(const uint64_t* keys, uint32_t n, uint32_t pl, uint32_t tid, uint64_t& mine) {
+    const uint32_t i = tid >> pl, parts = 1u << pl, part = tid & (parts - 1u);
+    mine = i < n ? keys[i] : 0ull;
+    uint32_t gt = 0;
+    if (mine) {
+        const uint32_t per = (n + parts - 1u) >> pl, lo = part * per, hi = min(n, lo + per);
+        for (uint32_t j = lo; j < hi; ++j) gt += keys[j] > mine;
+    }
+    for (uint32_t o = 1; o < parts; o <<= 1) gt += __shfl_xor_sync(0xffffffffu, gt, o);
+    return gt;
+}
+__device__ __forceinline__ uint32_t parts_log2_for(uint32_t n) {        // largest pl <= 2 with (n << pl) <= kThreads
+    return (n << 2) <= (uint32_t)kThreads ? 2u : ((n << 1) <= (uint32_t)kThreads ? 1u : 0u);
+}
+
 __global__ void __launch_bounds__(kThreads, MSR_SPARSE_MIN_CTAS)
 sparse_score_topk_kernel(const SearchParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -491,16 +509,15 @@ sparse_score_topk_kernel(const SearchParams P) {
                 // rank by counting: one key per thread against all n (broadcast reads).  Own candidates and list
                 // entries come from different tiles, so equal keys only appear when two tiles of the query raced
                 // on the list; that case takes the sorting path below.
+                // Equal keys get equal ranks, so a rank claimed twice (bitmap in wsum) reveals them.
+                if (tid < (uint32_t)kWarps) S->wsum[tid] = 0;
                 __syncthreads();
-                const uint64_t mine = tid < n ? U->keys[tid] : 0ull;
-                uint32_t gt = 0, dup = 0;
-                if (mine) {
-                    for (uint32_t j = 0; j < n; ++j) {
-                        const uint64_t kj = U->keys[j];
-                        gt += kj > mine;
-                        dup |= (kj == mine) & (j < tid);
-                    }
-                }
+                const uint32_t pl = parts_log2_for(n);
+                uint64_t mine;
+                const uint32_t gt = count_greater(U->keys, n, pl, tid, mine);
+                uint32_t dup = 0;
+                if ((tid & ((1u << pl) - 1u)) != 0) mine = 0ull;        // one writer per key
+                if (mine) dup = (atomicOr(&S->wsum[gt >> 5], 1u << (gt & 31)) >> (gt & 31)) & 1u;
                 if (!__syncthreads_or((int)dup)) {
                     if (mine && gt < P.k) {
                         tlist[gt] = mine;
@@ -605,10 +622,10 @@ sparse_score_topk_kernel(const SearchParams P) {
             __syncthreads();
             const uint32_t c = S->cand_cnt;                     // >= k by construction
             if (c <= (uint32_t)kThreads) {
-                const uint64_t mine = tid < c ? U->keys[tid] : 0ull;
-                uint32_t gt = 0;
-                if (mine) {
-                    for (uint32_t j = 0; j < c; ++j) gt += U->keys[j] > mine;     // distinct docs: distinct keys
+                const uint32_t pl = parts_log2_for(c);
+                uint64_t mine;
+                const uint32_t gt = count_greater(U->keys, c, pl, tid, mine);      // distinct docs: distinct keys
+                if (mine && (tid & ((1u << pl) - 1u)) == 0) {
                     if (gt < P.k) {
                         keys_out[gt] = mine;
                         if (P.use_theta) {
