@@ -197,10 +197,10 @@ def test_threshold_overflow_falls_back(oracle, lib_built):
     assert d[0].tolist() == list(range(50))
 
 
-@pytest.mark.parametrize("env", ["MSR_SPARSE_NO_THETA", "MSR_SPARSE_NO_DENSE"])
-def test_layout_switches_do_not_change_results(oracle, lib_built, monkeypatch, env):
-    """Dense impact rows and threshold sharing are pure optimisations: switching either off changes nothing."""
-    monkeypatch.setenv(env, "1")
+@pytest.mark.parametrize("env,val", [("MSR_SPARSE_NO_THETA", "1"), ("MSR_SPARSE_NO_DENSE", "1"), ("MSR_SPARSE_FAST_SELECT", "0")])
+def test_layout_switches_do_not_change_results(oracle, lib_built, monkeypatch, env, val):
+    """Dense impact rows, threshold sharing and the bounded select are pure optimisations: switching any off changes nothing."""
+    monkeypatch.setenv(env, val)
     rng = np.random.default_rng(5)
     n_docs, n_terms = 5000, 800
     indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 48, max_impact=65535)
@@ -305,3 +305,46 @@ def test_strided_merge_rejects_short_strides(lib_built):
            torch.empty((4,), dtype=torch.int32, device=dev))
     with pytest.raises(MsrError):
         topk_merge_strided(b.data_ptr(), b.data_ptr(), b.data_ptr(), 2, 4, 10, 39, 4, 10, out, dev)
+
+
+def _one_term_index(scores):
+    """Index whose only term gives doc d the impact scores[d] (0 = no posting): with query weight 1 the score IS scores[d]."""
+    docs = np.nonzero(scores)[0].astype(np.uint32)
+    return (np.array([0, len(docs)], dtype=np.uint64), docs, scores[docs].astype(np.uint16))
+
+
+@pytest.mark.parametrize("tile", [8192, 2048])
+def test_bounded_select_edges(oracle, lib_built, tile):
+    """The exact select first bounds the top-k by the k-th largest per-thread maximum (g) and collects score >= g.
+    Edges: ties at g that fit the 512-key buffer (order by doc id), ties that do not (radix fallback), hits owned by
+    fewer than k threads (g = 0, radix fallback), k = 1 and k = 512 (the largest k the bound handles)."""
+    rng = np.random.default_rng(41)
+    n = 8192
+    qi = np.array([0, 1], dtype=np.uint64)
+    qt = np.array([0], dtype=np.uint32)
+    qw = np.array([1], dtype=np.uint32)
+    # (a) 50 docs at 9, 300 at 7, the rest at 5: the bound lands on 7, 350 candidates, the last 50 places are ties
+    sc = np.full(n, 5, dtype=np.int64)
+    perm = rng.permutation(n)
+    sc[perm[:50]] = 9
+    sc[perm[50:350]] = 7
+    sc[perm[-2:]] = 0                                       # df = N - 2: the term survives the S5 filter
+    s, d, c = _check(oracle, *_one_term_index(sc), n, qi, qt, qw, 100, tile_docs=tile)
+    assert (s[0, :50] == 9).all() and (s[0, 50:] == 7).all() and (np.diff(d[0, 50:]) > 0).all()
+    # (b) same, but every other doc ties at the k-th score: more than 512 candidates
+    sc[:] = 5
+    sc[perm[:50]] = 9
+    sc[perm[-2:]] = 0
+    s, d, c = _check(oracle, *_one_term_index(sc), n, qi, qt, qw, 100, tile_docs=tile)
+    assert (s[0, 50:] == 5).all() and (np.diff(d[0, 50:]) > 0).all()
+    # (c) hits only on docs that 40 of the 512 threads own (thread t reads 16-byte vectors t, t + 512, ...): more than
+    #     k hits, fewer than k non-zero thread maxima
+    docs = np.arange(n)
+    sc = np.where((docs // 4) % 512 < 40, rng.integers(1, 400, n), 0)
+    assert np.count_nonzero(sc[:tile]) > 100
+    _check(oracle, *_one_term_index(sc), n, qi, qt, qw, 100, tile_docs=tile)
+    # (d) distinct-ish random scores, k = 1 / 512 / 513
+    sc = rng.integers(1, 60000, n)
+    sc[perm[-2:]] = 0
+    for k in (1, 512, 513):
+        _check(oracle, *_one_term_index(sc), n, qi, qt, qw, k, tile_docs=tile)
