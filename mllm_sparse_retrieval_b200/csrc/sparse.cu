@@ -621,6 +621,7 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     // Re-publishing costs a rank count over c + k keys; it pays while the list is still loose.  Measured (k = 100):
     // 6 tiles k/2 3.47 ms, k/4 3.63, k/8 3.68; 21 tiles 10.36 / 10.45 / 10.70; 41 tiles 19.84 (+0.5 ms final merge) / 19.78 / 19.96.
     P.merge_min = std::max(1u, k >> (h->n_tiles <= 24 ? 1 : 2));
+    if (const char* e = getenv("MSR_SPARSE_MERGE_SHIFT")) P.merge_min = std::max(1u, k >> (uint32_t)std::min(10, std::max(0, atoi(e))));
     P.fast_select = h->fast_select ? 1u : 0u;
     const size_t smem = search_smem_bytes(h->tile_docs);
     for (uint32_t q0 = 0; q0 < nq; q0 += qc) {
