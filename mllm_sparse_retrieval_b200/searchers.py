@@ -8,8 +8,10 @@
 
 Both run on libmsr.so (CUDA, sm_100a) only; constructing either without a usable B200 raises.
 With ``shard=True`` under an initialised torch.distributed process group the collection is doc-sharded over the
-ranks and per-rank top-k lists are merged after one NCCL all-gather; every rank then holds the
-full result for the queries it passed (all ranks must pass the SAME queries in that mode).
+ranks and the per-rank top-k lists are exchanged and merged: by peer stores fused into the scorer's
+last kernel when symmetric memory is available (``sharded.PeerExchange``), else by one NCCL all-gather
+(``MSR_EXCHANGE`` = auto | p2p | nccl).  Every rank then holds the full result for the queries it passed (all ranks
+must pass the SAME queries in that mode).
 """
 from __future__ import annotations
 
@@ -21,7 +23,7 @@ import torch
 
 from . import ops
 from .index import ImpactCollection
-from .sharded import PipelinedExchange
+from .sharded import PipelinedExchange, make_peer_exchange
 
 
 class Hit:
@@ -67,6 +69,7 @@ class LuceneImpactSearcher:
         c = self.collection
         self.num_docs = c.n_docs
         self.rank, self.world = _dist_info(shard)
+        self._px, self._px_failed = {}, False
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
         self.device = dev
         if self.world > 1:
@@ -80,6 +83,21 @@ class LuceneImpactSearcher:
     def set_analyzer(self, analyzer):
         return None
 
+    def _peer_exchange(self, nq, k):
+        """One ``PeerExchange`` per k, grown when a larger batch arrives (every rank sees the same batch sizes, so the
+        ranks take the same decisions).  ``MSR_EXCHANGE`` = auto (default) | p2p | nccl."""
+        kind = os.environ.get("MSR_EXCHANGE", "auto")
+        if kind == "nccl" or self._px_failed:
+            return None
+        px = self._px.get(k)
+        if px is None or px.nq < nq:
+            px = make_peer_exchange(max(nq, 64), k, self.device, self.world, self.rank, kind=kind)
+            if px is None:
+                self._px_failed = True
+                return None
+            self._px[k] = px
+        return px
+
     # -- array-level API (used by the CLI, the fusion path and the benchmarks) --------------------------------
     def search_arrays(self, queries, k):
         """queries: list of strings / token->count maps.  Returns host arrays (scores f32, docs i32 internal ids, counts)."""
@@ -89,12 +107,17 @@ class LuceneImpactSearcher:
         dev = self.device
         t = lambda a, dt: torch.from_numpy(a.astype(dt)).to(dev)
         d_qi, d_qt, d_qw = t(qi, np.int64), t(qt, np.int32), t(qw, np.int32)
-        ex = PipelinedExchange(len(queries), k, dev, self.world)
+        nq = len(queries)
+        px = self._peer_exchange(nq, k)
+        if px is not None:          # exchange fused into the scorer's last kernel (peer stores), no collective call
+            ms, md, mc = px.run(self.index, lambda o: self.index.search(d_qi, d_qt, d_qw, k, out=o), nq=nq)
+        else:                       # NCCL all-gather + merge
+            ex = PipelinedExchange(nq, k, dev, self.world)
 
-        def chunk(i, lo, hi, o):
-            a0, a1 = int(qi[lo]), int(qi[hi])
-            self.index.search(d_qi[lo:hi + 1] - a0, d_qt[a0:a1], d_qw[a0:a1], k, out=o)
-        ms, md, mc = ex.run(chunk)
+            def chunk(i, lo, hi, o):
+                a0, a1 = int(qi[lo]), int(qi[hi])
+                self.index.search(d_qi[lo:hi + 1] - a0, d_qt[a0:a1], d_qw[a0:a1], k, out=o)
+            ms, md, mc = ex.run(chunk)
         self.index.status()
         return ms.cpu().numpy(), md.cpu().numpy(), mc.cpu().numpy().astype(np.uint32)
 

@@ -106,9 +106,13 @@ class PeerExchange:
         b = base + 4 * ((parity * self.world + who) * self.slot)
         return b, b + 4 * self.nq * self.k, b + 8 * self.nq * self.k
 
-    def run(self, index, search):
+    def run(self, index, search, nq=None):
         """search(out_views) runs ONE device-path search of the whole batch on ``index`` (a ``SparseIndex``) writing
-        (scores, ids, counts) into out_views; returns the merged result of all shards on the current stream."""
+        (scores, ids, counts) into out_views; returns the merged result of all shards on the current stream.
+        ``nq`` <= the capacity given at construction (default: the capacity) is the batch size of THIS call and must be
+        the same on every rank; the slots keep their capacity-sized layout and only the first ``nq`` rows are used."""
+        if nq is not None and nq != self.nq:
+            return self._run_partial(index, search, int(nq))
         par = self.step & 1
         self.step += 1
         peers = [self._slot_ptrs(self.ptrs[r], par, self.rank) for r in range(self.world) if r != self.rank]
@@ -126,3 +130,43 @@ class PeerExchange:
         s0, d0, c0 = self._slot_ptrs(self.ptrs[self.rank], par, 0)
         ops.topk_merge_strided(s0, d0, c0, self.world, self.nq, self.k, self.slot, self.slot, self.k, self.final, self.device)
         return self.final
+
+    def _run_partial(self, index, search, nq):
+        assert 0 < nq < self.nq
+        par = self.step & 1
+        self.step += 1
+        peers = [self._slot_ptrs(self.ptrs[r], par, self.rank) for r in range(self.world) if r != self.rank]
+        index.set_peer_outputs([p[0] for p in peers], [p[1] for p in peers], [p[2] for p in peers])
+        try:
+            o = self.slot * (par * self.world + self.rank)
+            cap_nk = self.nq * self.k
+            out = (self.buf[o:o + nq * self.k].view(torch.float32).view(nq, self.k),
+                   self.buf[o + cap_nk:o + cap_nk + nq * self.k].view(nq, self.k),
+                   self.buf[o + 2 * cap_nk:o + 2 * cap_nk + nq])
+            search(out)
+        finally:
+            index.set_peer_outputs()
+        self.hdl.barrier(channel=0)
+        s0, d0, c0 = self._slot_ptrs(self.ptrs[self.rank], par, 0)
+        final = tuple(t[:nq] for t in self.final)
+        ops.topk_merge_strided(s0, d0, c0, self.world, nq, self.k, self.slot, self.slot, self.k, final, self.device)
+        return final
+
+
+def make_peer_exchange(nq, k, device, world, rank, kind="auto", group=None):
+    """``PeerExchange`` if every rank of the group can set it up, else None (``kind='auto'``) or an error (``'p2p'``);
+    ``kind='nccl'`` returns None at once.  Collective: every rank must call it with the same arguments."""
+    if world == 1 or kind == "nccl":
+        return None
+    px, err = None, None
+    try:
+        px = PeerExchange(nq, k, device, world, rank, group=group)
+    except Exception as e:                                          # no symmetric memory / no peer access
+        err = e
+    ok = torch.tensor([1 if px is not None else 0], device=torch.device(device))
+    dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+    if int(ok.item()) == 0:
+        if kind == "p2p":
+            raise RuntimeError(f"fused peer exchange unavailable on rank {rank}: {err!r}") from err
+        return None
+    return px

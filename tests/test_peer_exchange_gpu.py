@@ -80,3 +80,49 @@ def test_peer_exchange_two_gpus(oracle, lib_built, tmp_path, k):
             np.testing.assert_array_equal(got[f"c{step}"].astype(np.uint32), ec)
             np.testing.assert_array_equal(got[f"d{step}"], ed)
             np.testing.assert_array_equal(got[f"s{step}"], es)
+
+
+def _searcher_worker(rank, world, port, k, out_path):
+    sys.path.insert(0, ROOT)
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        from test_sharding_cpu import _make_collection, _queries
+        from mllm_sparse_retrieval_b200.searchers import LuceneImpactSearcher
+        coll = _make_collection()
+        qs = _queries(coll, nq=90)
+        res = {}
+        for kind in ("p2p", "nccl"):
+            os.environ["MSR_EXCHANGE"] = kind
+            S = LuceneImpactSearcher(None, collection=coll, shard=True, device=dev)
+            for n in (40, 25, 90):                                        # a smaller batch reuses the slots, a larger one regrows them
+                s, d, c = S.search_arrays(qs[:n], k)
+                res[f"{kind}_s{n}"], res[f"{kind}_d{n}"], res[f"{kind}_c{n}"] = s, d, c
+            assert (kind == "p2p") == bool(S._px), "the fused exchange was not the path taken"
+            S.close()
+        np.savez(out_path + f".{rank}.npz", **res)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs with peer access")
+def test_sharded_searcher_uses_fused_exchange(oracle, lib_built, tmp_path):
+    """LuceneImpactSearcher(shard=True) on two GPUs: fused peer exchange == NCCL exchange == unsharded oracle."""
+    from test_sharding_cpu import _make_collection, _queries
+    k = 20
+    out = str(tmp_path / "sx")
+    mp.spawn(_searcher_worker, args=(2, _free_port(), k, out), nprocs=2, join=True)
+    coll = _make_collection()
+    qs = _queries(coll, nq=90)
+    for n in (40, 25, 90):
+        qi, qt, qw = coll.encode_queries(qs[:n])
+        es, ed, ec = oracle.impact_search_c(coll.indptr, coll.post_docs, coll.post_impacts, coll.n_docs, qi, qt, qw, k)
+        for r in range(2):
+            got = np.load(out + f".{r}.npz")
+            for kind in ("p2p", "nccl"):
+                np.testing.assert_array_equal(got[f"{kind}_c{n}"], ec)
+                np.testing.assert_array_equal(got[f"{kind}_d{n}"], ed)
+                np.testing.assert_array_equal(got[f"{kind}_s{n}"], es)
