@@ -108,6 +108,8 @@ class LuceneImpactSearcher:
         t = lambda a, dt: torch.from_numpy(a.astype(dt)).to(dev)
         d_qi, d_qt, d_qw = t(qi, np.int64), t(qt, np.int32), t(qw, np.int32)
         nq = len(queries)
+        if nq == 0:
+            return (np.empty((0, k), np.float32), np.empty((0, k), np.int32), np.empty((0,), np.uint32))
         px = self._peer_exchange(nq, k)
         if px is not None:          # exchange fused into the scorer's last kernel (peer stores), no collective call
             ms, md, mc = px.run(self.index, lambda o: self.index.search(d_qi, d_qt, d_qw, k, out=o), nq=nq)
