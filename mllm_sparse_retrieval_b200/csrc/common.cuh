@@ -38,6 +38,19 @@ inline void count_launch(uint64_t n = 1) { g_launches.fetch_add(n, std::memory_o
 
 int use_device(int device);   // cudaSetDevice + sm_100 check; returns msr_status
 
+// cudaFuncSetAttribute is per DEVICE, not per process: launch helpers remember, per call site, on which devices the
+// attribute has been set (bit = device index), so a process that drives several GPUs sets it on each.
+inline bool attr_needed(const std::atomic<uint64_t>& done) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return dev > 63 || !((done.load(std::memory_order_relaxed) >> dev) & 1ull);
+}
+inline void attr_mark(std::atomic<uint64_t>& done) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev <= 63) done.fetch_or(1ull << dev, std::memory_order_relaxed);
+}
+
 // RAII device buffer used for temporaries inside API calls
 struct DevBuf {
     void* p = nullptr;

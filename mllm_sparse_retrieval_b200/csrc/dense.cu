@@ -238,10 +238,10 @@ static int dense_search_exact(msr_dense_index* h, uint32_t nq, const float* d_q,
     int32_t* td = (int32_t*)((unsigned char*)ts + align_up((size_t)qc * kk * 4, 256));
     uint32_t* tc = (uint32_t*)((unsigned char*)td + align_up((size_t)qc * kk * 4, 256));
     const size_t smem = (size_t)kIpQ * h->dim * 4;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<uint64_t> attr_set{0};
+    if (attr_needed(attr_set)) {
         MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_ip_exact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kIpQ * 8192 * 4));
-        attr_set = true;
+        attr_mark(attr_set);
     }
     for (uint32_t q0 = 0; q0 < nq; q0 += qc) {
         const uint32_t n = std::min(qc, nq - q0);
@@ -506,11 +506,11 @@ static TcLayout make_tc_layout(const msr_dense_index* h, uint32_t nq, uint32_t k
 static int dense_search_tc(msr_dense_index* h, uint32_t nq, const float* d_q, uint32_t k, float* d_os, int64_t* d_oi,
                            unsigned char* base, const TcLayout& L, cudaStream_t s, uint32_t* n_fallback) {
     std::vector<uint32_t> flags, fail;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<uint64_t> attr_set{0};
+    if (attr_needed(attr_set)) {
         MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_select_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8));
         MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_final_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8));
-        attr_set = true;
+        attr_mark(attr_set);
     }
     for (uint32_t q0 = 0; q0 < nq; q0 += L.nqb) {
         const uint32_t n = std::min(L.nqb, nq - q0);

@@ -299,11 +299,11 @@ static int make_map_f16(CUtensorMap* map, const void* ptr, uint64_t rows, uint64
 
 static int tc_launch_common(const CUtensorMap& mq, const CUtensorMap& mx, TcParams& P, uint32_t nq, uint32_t n_docs,
                             uint32_t dim, bool filter, cudaStream_t s) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<uint64_t> attr_set{0};
+    if (attr_needed(attr_set)) {
         MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_tc_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
         MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_tc_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES));
-        attr_set = true;
+        attr_mark(attr_set);
     }
     P.nq = nq; P.n_docs = n_docs; P.n_qblk = (nq + BM - 1) / BM; P.n_dblk = (n_docs + BN - 1) / BN;
     P.n_kslab = (dim + BK - 1) / BK;

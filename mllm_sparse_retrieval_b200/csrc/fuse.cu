@@ -202,10 +202,10 @@ extern "C" int msr_fuse(int device, uint32_t nq, uint32_t k_d, const float* d_sc
     P.self_ids = self_ids; P.remove_query = remove_query; P.dense_f32 = dense_f32; P.w_dense = w_dense; P.w_sparse = w_sparse;
     P.out_scores = out_scores; P.out_docs = out_docs; P.out_src = out_src; P.out_counts = out_counts;
     const size_t smem = sizeof(FuseSmall) + kFuseWarps * 4 + (size_t)P.table * 8 + ((k_s + 15) & ~15u);
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<uint64_t> attr_set{0};
+    if (attr_needed(attr_set)) {
         MSR_CUDA_CHECK(cudaFuncSetAttribute(fuse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        attr_set = true;
+        attr_mark(attr_set);
     }
     fuse_kernel<<<nq, kFuseThreads, smem, (cudaStream_t)stream>>>(P);
     count_launch();

@@ -142,10 +142,10 @@ static int merge_launch(MergeParams P, cudaStream_t s) {
     if (cap > 8192) { set_error("topk merge: k + k_in = %u exceeds 8192", need); return MSR_ERR_INVALID; }
     P.cap = cap;
     const size_t smem = (size_t)cap * 8;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<uint64_t> attr_set{0};
+    if (attr_needed(attr_set)) {
         MSR_CUDA_CHECK(cudaFuncSetAttribute(topk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8));
-        attr_set = true;
+        attr_mark(attr_set);
     }
     topk_merge_kernel<<<P.nq, kMergeThreads, smem, s>>>(P);
     count_launch();
@@ -355,11 +355,11 @@ int topk_rows_launch(uint32_t nq, uint32_t n, const float* scores, size_t row_st
     uint32_t n2 = 2;
     while (n2 < k) n2 <<= 1;
     const size_t smem = sizeof(RowsSmem) + (size_t)n2 * 8;
-    static bool attr_set = false;
-    if (!attr_set) {
+    static std::atomic<uint64_t> attr_set{0};
+    if (attr_needed(attr_set)) {
         MSR_CUDA_CHECK(cudaFuncSetAttribute(topk_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)(sizeof(RowsSmem) + MSR_MAX_K * 8)));
-        attr_set = true;
+        attr_mark(attr_set);
     }
     topk_rows_kernel<<<nq, kRowThreads, smem, s>>>(P);
     count_launch();

@@ -126,3 +126,36 @@ def test_sharded_searcher_uses_fused_exchange(oracle, lib_built, tmp_path):
                 np.testing.assert_array_equal(got[f"{kind}_c{n}"], ec)
                 np.testing.assert_array_equal(got[f"{kind}_d{n}"], ed)
                 np.testing.assert_array_equal(got[f"{kind}_s{n}"], es)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_one_process_drives_two_devices(oracle, lib_built):
+    """Opt-in shared memory (cudaFuncSetAttribute) is per device: a process that searched on cuda:0 must still be able
+    to launch the > 48 KB tile merge, the row top-k and the dense kernels on cuda:1."""
+    from mllm_sparse_retrieval_b200.ops import DenseIndex, SparseIndex, topk_rows
+    rng = np.random.default_rng(88)
+    n_docs, n_terms, k = 30000, 2000, 200
+    indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 32)
+    qi, qt, qw = random_queries(rng, 16, n_terms, 12)
+    exp = oracle.impact_search_c(indptr, docids, impacts, n_docs, qi, qt, qw, k, threads=4)
+    x = rng.standard_normal((3000, 256)).astype(np.float32)
+    xq = rng.standard_normal((8, 256)).astype(np.float32)
+    for d in (0, 1):
+        dev = torch.device("cuda", d)
+        idx = SparseIndex(indptr, docids, impacts, n_docs, tile_docs=1024, device=dev)   # 30 tiles x 200: 64 KB merge buffer
+        s, dd, c = idx.search(torch.from_numpy(qi.astype(np.int64)).to(dev), torch.from_numpy(qt.astype(np.int32)).to(dev),
+                              torch.from_numpy(qw.astype(np.int32)).to(dev), k)
+        idx.status()
+        np.testing.assert_array_equal(dd.cpu().numpy(), exp[1])
+        np.testing.assert_array_equal(s.cpu().numpy(), exp[0])
+        idx.close()
+        rows = torch.from_numpy(rng.standard_normal((4, 50000)).astype(np.float32)).to(dev)
+        ts, td, _ = topk_rows(rows, 100)
+        ref = torch.topk(rows, 100, dim=1)
+        assert torch.equal(ts, ref.values)
+        D = DenseIndex(256, device=dev)
+        D.add(x)
+        ds, di = D.search(xq, 10)
+        ref_i = np.argsort(-(xq.astype(np.float64) @ x.T.astype(np.float64)), axis=1, kind="stable")[:, :10]
+        np.testing.assert_array_equal(np.asarray(di), ref_i)
+        D.close()
