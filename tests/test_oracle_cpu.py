@@ -118,3 +118,28 @@ def test_flat_ip_c_matches_numpy(oracle):
     b = oracle.flat_ip_search_numpy(docs, q, 20)
     np.testing.assert_array_equal(a[1], b[1])
     np.testing.assert_array_equal(a[0], b[0])
+
+
+def test_c_matches_scipy_property(oracle):
+    """Property form of the cross-check: hypothesis draws ragged collections (empty docs, empty queries, out-of-vocabulary
+    and zero-weight query terms, k above the hit count, heavy ties from a tiny impact range) and the two independent
+    restatements must agree bit for bit."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=40, deadline=None)
+    @given(st.integers(0, 2 ** 32 - 1), st.integers(3, 120), st.integers(1, 40), st.integers(0, 12),
+           st.integers(0, 9), st.integers(1, 3), st.sampled_from([1, 7, 130]))
+    def prop(seed, n_docs, n_terms, nnz, nq, max_imp, k):
+        rng = np.random.default_rng(seed)
+        indptr, docids, impacts = random_csr(rng, n_docs, n_terms, (0, min(nnz, n_terms) + 1), max_impact=max_imp, zipf=False)
+        qi, qt, qw = random_queries(rng, nq, n_terms, (0, 8), max_w=3, dup=True, zipf=False)
+        if len(qt):
+            qt = qt.copy(); qw = qw.copy()
+            qt[rng.random(len(qt)) < 0.1] = n_terms + 5          # a term the index has never seen
+            qw[rng.random(len(qw)) < 0.1] = 0
+        a = oracle.impact_search_c(indptr, docids, impacts, n_docs, qi, qt, qw, k, threads=2)
+        b = oracle.impact_search_numpy(indptr, docids, impacts, n_docs, qi, qt, qw, k)
+        for x, y in zip(a, b):
+            np.testing.assert_array_equal(x, y)
+
+    prop()
