@@ -101,3 +101,26 @@ def test_shard_keeps_global_term_filter():
     s, d, c = oracle.impact_search_c(indptr, docs, imps, coll.n_docs // 2, qi, qt, qw, 5, n_docs_global=coll.n_docs,
                                      df_global=coll.df, doc_base=0)
     assert int(c[0]) == 0                                                # ... but filtered by the global df
+
+
+def test_peer_exchange_slot_layout_tiles_the_buffer():
+    """Host arithmetic of the fused exchange (no GPU): the (step buffer, rank) slots and their scores / docs / counts
+    sections are disjoint and tile the symmetric buffer exactly; slot strides are what msr_topk_merge_strided is given."""
+    from mllm_sparse_retrieval_b200.sharded import PeerExchange
+    for nq, k, world in ((50, 7, 4), (1, 1, 2), (64, 100, 8)):
+        px = object.__new__(PeerExchange)                               # layout only: no symmetric memory on this box
+        px.nq, px.k, px.world = nq, k, world
+        px.slot = 2 * nq * k + nq
+        base = 4096
+        regions = []
+        for par in (0, 1):
+            for who in range(world):
+                s, d, c = px._slot_ptrs(base, par, who)
+                assert d - s == 4 * nq * k and c - d == 4 * nq * k
+                regions += [(s, s + 4 * nq * k), (d, d + 4 * nq * k), (c, c + 4 * nq)]
+                if who:
+                    assert s - px._slot_ptrs(base, par, who - 1)[0] == 4 * px.slot      # the list stride of the merge
+        regions.sort()
+        assert regions[0][0] == base and regions[-1][1] == base + 4 * 2 * world * px.slot
+        for (a0, a1), (b0, b1) in zip(regions[:-1], regions[1:]):
+            assert a1 == b0                                             # no gap, no overlap
