@@ -103,6 +103,16 @@ int msr_sparse_query_work(msr_sparse_index* h, uint32_t nq, const uint64_t* q_in
                           int where, void* stream);
 
 /*
+ * PHYSICAL index bytes a query batch touches (device-path pointers): every distinct kept term of the batch counted
+ * once -- a dense term as its u8 impact row (n_docs bytes; the u16 row too when some query weighs it >= 256) plus its
+ * remainder postings, any other term as 4 bytes per posting slot over all tiles.  This is the DRAM floor of a batch
+ * that starts with a cold L2 (bench.py's small-batch lines divide it by the measured time); it replaces no
+ * reference call.
+ */
+int msr_sparse_query_traffic(msr_sparse_index* h, uint32_t nq, const uint64_t* q_indptr, const uint32_t* q_terms,
+                             const uint32_t* q_weights, uint64_t* bytes, void* stream);
+
+/*
  * Per-kernel timing for bench.py's roofline: synchronises `stream`, returns the summed CUDA-event durations (ms)
  * of the score kernel and of the merge kernel over all launches since the previous call plus their count, then
  * switches event recording on (enable != 0) or off for later searches.
@@ -304,6 +314,19 @@ int msr_recall_hits(int device, uint32_t nq, const int32_t* docs, size_t row_str
  */
 int msr_provenance_hist(int device, uint32_t nq, const double* scores, const uint8_t* src, size_t row_stride,
                         const uint32_t* counts, uint32_t depth, uint64_t* hist, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
+ * Measured ceilings for `roofline.binding` (csrc/microbench.cu; replaces no reference call).  The sparse scorer shares
+ * postings across the query batch through L2, so HBM does not bound it; bench.py reports it against these numbers,
+ * measured on the same GPU in the same run.  *units_per_s: bytes/s for the two read benchmarks (`bytes` = buffer size;
+ * L2: choose <= 64 MiB so it stays L2-resident, HBM: >= 1 GiB), warp instructions/s for the other two (`bytes` unused).
+ * Synchronous.
+ */
+#define MSR_MB_L2_READ 0      /* ld.global.nc.L1::no_allocate.v2.u32, 8 in flight per thread, L2-resident buffer */
+#define MSR_MB_HBM_READ 1     /* the same loop over a buffer far larger than L2 */
+#define MSR_MB_RED_SHARED 2   /* red.shared.add.u32, one bank per lane */
+#define MSR_MB_ISSUE 3        /* independent dp4a chains: issue-slot ceiling */
+int msr_microbench(int device, int what, uint64_t bytes, uint32_t iters, double* units_per_s, void* stream);
 
 #ifdef __cplusplus
 }

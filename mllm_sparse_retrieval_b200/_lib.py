@@ -34,6 +34,8 @@ def _declare(lib):
         "msr_sparse_search": (I, [P, U32, P, P, P, U32, P, P, P, I, P]),
         "msr_sparse_index_status": (I, [P, P]),
         "msr_sparse_query_work": (I, [P, U32, P, P, P, ctypes.POINTER(U64), ctypes.POINTER(U64), I, P]),
+        "msr_sparse_query_traffic": (I, [P, U32, P, P, P, ctypes.POINTER(U64), P]),
+        "msr_microbench": (I, [I, I, U64, U32, ctypes.POINTER(D), P]),
         "msr_sparse_profile": (I, [P, I, ctypes.POINTER(D), ctypes.POINTER(D), ctypes.POINTER(U64), P]),
         "msr_topk_merge": (I, [I, U32, U32, U32, P, P, P, U32, P, P, P, P]),
         "msr_topk_rows": (I, [I, U32, U32, P, ctypes.c_size_t, U32, ctypes.c_int32, P, P, P, P]),

@@ -10,7 +10,7 @@ from concurrent.futures import ThreadPoolExecutor
 PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libmsr.so")
-SOURCES = ["api.cu", "sparse.cu", "topk.cu", "fuse.cu", "dense.cu", "quantise.cu", "metrics.cu", "invert.cu", "jsonl.cu"]
+SOURCES = ["api.cu", "sparse.cu", "topk.cu", "fuse.cu", "dense.cu", "quantise.cu", "metrics.cu", "invert.cu", "jsonl.cu", "microbench.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC", "-Xcompiler", "-Wall", "--expt-relaxed-constexpr"]
 

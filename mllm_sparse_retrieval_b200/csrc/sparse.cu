@@ -280,6 +280,35 @@ __global__ void query_work_kernel(const uint8_t* __restrict__ keep, const uint32
     if ((threadIdx.x & 31) == 0 && c) { atomicAdd(&out[0], p); atomicAdd(&out[1], c); }
 }
 
+// physical traffic of a batch: mark the distinct kept terms (flag 1 = used, 2 = used with a weight the u8 rows cannot take)
+__global__ void traffic_mark_kernel(const uint8_t* __restrict__ keep, const uint32_t* __restrict__ maximp, uint32_t n_terms,
+                                    uint64_t nnz_q, const uint32_t* __restrict__ q_terms, const uint32_t* __restrict__ q_weights,
+                                    uint32_t* __restrict__ flags) {
+    for (uint64_t j = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; j < nnz_q; j += (uint64_t)gridDim.x * blockDim.x) {
+        const uint32_t t = q_terms[j], w = q_weights[j];
+        if (t < n_terms && w && keep[t]) atomicOr(&flags[t], (w >= 256u || (uint64_t)w * maximp[t] >= (1u << 24)) ? 3u : 1u);
+    }
+}
+__global__ void traffic_sum_kernel(const uint32_t* __restrict__ flags, uint32_t n_terms, uint32_t n_tiles, uint32_t n_docs,
+                                   const uint32_t* __restrict__ seg_ptr, const uint32_t* __restrict__ dense_id,
+                                   unsigned long long* __restrict__ out) {
+    unsigned long long b = 0;
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n_terms; t += gridDim.x * blockDim.x) {
+        const uint32_t f = flags[t];
+        if (!f) continue;
+        const bool dense = dense_id[t] != kNotDense;
+        if (dense) b += (f & 2u) ? 3ull * n_docs : (unsigned long long)n_docs;   // u8 row (+ the u16 row for wide weights)
+        {                                                        // bucket postings (a dense term's: the remainder above 255)
+            for (uint32_t tile = 0; tile < n_tiles; ++tile) {
+                const size_t i = (size_t)tile * n_terms + t;
+                b += 4ull * (seg_ptr[i + 1] - seg_ptr[i]) + 8ull;   // slots + the two seg_ptr words
+            }
+        }
+    }
+    for (int o = 16; o > 0; o >>= 1) b += __shfl_xor_sync(0xffffffffu, b, o);
+    if ((threadIdx.x & 31) == 0 && b) atomicAdd(out, b);
+}
+
 static size_t search_smem_bytes(uint32_t tile_docs) {
     return sizeof(StageUnion) + sizeof(SmallState) + (size_t)((tile_docs + 7) & ~7u) * 4;
 }
@@ -693,6 +722,36 @@ extern "C" int msr_sparse_query_work(msr_sparse_index* h, uint32_t nq, const uin
     MSR_CUDA_CHECK(cudaMemcpyAsync(res, h->work, 16, cudaMemcpyDeviceToHost, s));
     MSR_CUDA_CHECK(cudaStreamSynchronize(s));
     *postings = res[0]; *kept_terms = res[1];
+    return MSR_OK;
+}
+
+extern "C" int msr_sparse_query_traffic(msr_sparse_index* h, uint32_t nq, const uint64_t* q_indptr, const uint32_t* q_terms,
+                                        const uint32_t* q_weights, uint64_t* bytes, void* stream) {
+    MSR_REQUIRE(h && bytes, "msr_sparse_query_traffic: NULL argument");
+    *bytes = 0;
+    if (nq == 0) return MSR_OK;
+    MSR_REQUIRE(q_indptr && q_terms && q_weights, "msr_sparse_query_traffic: NULL query arrays");
+    int rc = use_device(h->device);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    uint64_t nnz_q = 0;
+    MSR_CUDA_CHECK(cudaMemcpyAsync(&nnz_q, q_indptr + nq, 8, cudaMemcpyDeviceToHost, s));
+    MSR_CUDA_CHECK(cudaStreamSynchronize(s));
+    if (nnz_q == 0) return MSR_OK;
+    DevBuf flags;
+    MSR_CUDA_CHECK(flags.alloc((size_t)h->n_terms * 4));
+    MSR_CUDA_CHECK(cudaMemsetAsync(flags.p, 0, (size_t)h->n_terms * 4, s));
+    MSR_CUDA_CHECK(cudaMemsetAsync(h->work, 0, 16, s));
+    traffic_mark_kernel<<<(int)std::min<uint64_t>((nnz_q + 255) / 256, 148ull * 8), 256, 0, s>>>(
+        h->term_keep, h->term_maximp, h->n_terms, nnz_q, q_terms, q_weights, flags.as<uint32_t>());
+    traffic_sum_kernel<<<(h->n_terms + 255) / 256, 256, 0, s>>>(flags.as<uint32_t>(), h->n_terms, h->n_tiles, h->n_docs,
+                                                                h->seg_ptr, h->dense_id, (unsigned long long*)h->work);
+    count_launch(2);
+    uint64_t res = 0;
+    MSR_CUDA_CHECK(cudaMemcpyAsync(&res, h->work, 8, cudaMemcpyDeviceToHost, s));
+    MSR_CUDA_CHECK(cudaStreamSynchronize(s));
+    MSR_CUDA_CHECK(cudaGetLastError());
+    *bytes = res + (uint64_t)nnz_q * 8 + (uint64_t)(nq + 1) * 8;   // + the query CSR itself
     return MSR_OK;
 }
 

@@ -133,6 +133,29 @@ class SparseIndex:
                                                     current_stream_ptr(self.device)))
         return int(p.value), int(c.value)
 
+    def query_traffic(self, q_indptr, q_terms, q_weights):
+        """Physical index bytes the batch touches, every distinct kept term counted once (msr_sparse_query_traffic):
+        the DRAM floor of a cold-L2 search, used by bench.py's small-batch lines."""
+        nq = q_indptr.numel() - 1
+        b = ctypes.c_uint64()
+        with torch.cuda.device(self.device):
+            check(_lib.load().msr_sparse_query_traffic(self._h, nq, ptr(q_indptr), ptr(q_terms), ptr(q_weights),
+                                                       ctypes.byref(b), current_stream_ptr(self.device)))
+        return int(b.value)
+
+
+MB_L2_READ, MB_HBM_READ, MB_RED_SHARED, MB_ISSUE = 0, 1, 2, 3
+
+
+def microbench(what, nbytes=0, iters=5, device=0):
+    """Measured ceiling of one resource the sparse scorer uses (msr_microbench): bytes/s or warp instructions/s."""
+    v = ctypes.c_double()
+    dev = torch.device(device)
+    idx = dev.index if dev.index is not None else torch.cuda.current_device()
+    with torch.cuda.device(idx):
+        check(_lib.load().msr_microbench(idx, int(what), int(nbytes), int(iters), ctypes.byref(v), current_stream_ptr(dev)))
+    return float(v.value)
+
 
 def topk_merge(scores, docs, counts, k, out=None):
     """[n_lists,nq,k_in] lists (e.g. an all-gather of per-GPU results) -> merged [nq,k] (into ``out`` when given)."""

@@ -143,3 +143,99 @@ def test_c_matches_scipy_property(oracle):
             np.testing.assert_array_equal(x, y)
 
     prop()
+
+
+# ---- the timed CPU baselines (oracle/impact_tuned.c) must be the oracle, bit for bit ----
+@pytest.mark.parametrize("kind", ["exhaustive", "pruned"])
+@pytest.mark.parametrize("seed,n_docs,n_terms,nnz,nq,qlen,k", [
+    (1, 200, 64, 16, 20, 8, 10),
+    (2, 1000, 512, 32, 30, (1, 40), 100),
+    (3, 50, 16, (0, 10), 10, 6, 1000),
+    (4, 3000, 2000, 24, 16, 12, 100),
+    (5, 70000, 300, 12, 12, 10, 50),             # several 32 K-doc blocks: cursors and thresholds carry over
+    (6, 70000, 300, 12, 12, (1, 30), 1),
+])
+def test_tuned_baselines_match_oracle(oracle, kind, seed, n_docs, n_terms, nnz, nq, qlen, k):
+    rng = np.random.default_rng(seed)
+    if n_docs > 10000:                           # vectorised generator for the multi-block cases
+        t = rng.integers(0, n_terms, size=(n_docs, nnz))
+        t.sort(axis=1)
+        keep = np.ones_like(t, dtype=bool); keep[:, 1:] = t[:, 1:] != t[:, :-1]
+        d = np.repeat(np.arange(n_docs), nnz).reshape(n_docs, nnz)[keep]; t = t[keep]
+        w = rng.integers(1, 401, size=len(t))
+        order = np.lexsort((d, t))
+        indptr = np.zeros(n_terms + 1, dtype=np.uint64)
+        np.cumsum(np.bincount(t, minlength=n_terms), out=indptr[1:])
+        docids, impacts = d[order].astype(np.uint32), w[order].astype(np.uint16)
+    else:
+        indptr, docids, impacts = random_csr(rng, n_docs, n_terms, nnz)
+    qi, qt, qw = random_queries(rng, nq, n_terms, qlen, dup=(seed % 2 == 0))
+    a = oracle.impact_search_c(indptr, docids, impacts, n_docs, qi, qt, qw, k, threads=2)
+    b = oracle.impact_search_tuned(indptr, docids, impacts, n_docs, qi, qt, qw, k, kind=kind, threads=2)
+    for x, y in zip(a, b[:3]):
+        np.testing.assert_array_equal(x, y)
+    if kind == "exhaustive":
+        df = np.diff(indptr.astype(np.int64))
+        kept = (df > 0) & (df + 1 < n_docs)
+        valid = (qt < n_terms) & (qw > 0)
+        expect = int(df[qt[valid]][kept[qt[valid]]].sum())
+        assert b[3] == expect                    # every posting of every kept term was applied
+
+
+def test_tuned_baselines_wide_path_and_shards(oracle):
+    # S6: a per-term product >= 2^24 sends the query down the wide (double) path
+    indptr = np.array([0, 2, 4], dtype=np.uint64)
+    docids = np.array([0, 1, 0, 1], dtype=np.uint32)
+    impacts = np.array([65535, 65535, 1, 3], dtype=np.uint16)
+    qi = np.array([0, 2], dtype=np.uint64)
+    qt = np.array([0, 1], dtype=np.uint32)
+    qw = np.array([65535, 1], dtype=np.uint32)
+    a = oracle.impact_search_c(indptr, docids, impacts, 8, qi, qt, qw, 2)
+    for kind in ("exhaustive", "pruned"):
+        b = oracle.impact_search_tuned(indptr, docids, impacts, 8, qi, qt, qw, 2, kind=kind)
+        for x, y in zip(a, b[:3]):
+            np.testing.assert_array_equal(x, y)
+    # doc shard with collection-wide df / N and a doc base
+    rng = np.random.default_rng(21)
+    n_docs, n_terms, k = 900, 300, 50
+    indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 20)
+    qi, qt, qw = random_queries(rng, 12, n_terms, 10)
+    df = np.diff(indptr.astype(np.int64)).astype(np.uint32)
+    term_of = np.repeat(np.arange(n_terms), df)
+    lo, hi = 300, 650
+    m = (docids >= lo) & (docids < hi)
+    ip = np.zeros(n_terms + 1, dtype=np.uint64)
+    np.cumsum(np.bincount(term_of[m], minlength=n_terms), out=ip[1:])
+    kw = dict(n_docs_global=n_docs, df_global=df, doc_base=lo)
+    a = oracle.impact_search_c(ip, docids[m] - lo, impacts[m], hi - lo, qi, qt, qw, k, **kw)
+    for kind in ("exhaustive", "pruned"):
+        b = oracle.impact_search_tuned(ip, docids[m] - lo, impacts[m], hi - lo, qi, qt, qw, k, kind=kind, **kw)
+        for x, y in zip(a, b[:3]):
+            np.testing.assert_array_equal(x, y)
+
+
+def test_tuned_pruned_property(oracle):
+    """MaxScore pruning against the exhaustive oracle on hypothesis-drawn ragged collections with heavy score ties
+    (tiny impact range): the tie rule (a later doc never displaces an equal score) is what the pruning leans on."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=60, deadline=None)
+    @given(st.integers(0, 2 ** 32 - 1), st.integers(3, 400), st.integers(1, 40), st.integers(0, 12),
+           st.integers(0, 9), st.integers(1, 4), st.sampled_from([1, 3, 7, 130]))
+    def prop(seed, n_docs, n_terms, nnz, nq, max_imp, k):
+        rng = np.random.default_rng(seed)
+        indptr, docids, impacts = random_csr(rng, n_docs, n_terms, (0, min(nnz, n_terms) + 1), max_impact=max_imp, zipf=False)
+        qi, qt, qw = random_queries(rng, nq, n_terms, (0, 8), max_w=3, dup=True, zipf=False)
+        if len(qt):
+            qt = qt.copy(); qw = qw.copy()
+            qt[rng.random(len(qt)) < 0.1] = n_terms + 5
+            qw[rng.random(len(qw)) < 0.1] = 0
+        a = oracle.impact_search_c(indptr, docids, impacts, n_docs, qi, qt, qw, k, threads=2)
+        for kind in ("exhaustive", "pruned"):
+            for block in (0, 8, 37):                     # tiny accumulator tiles: the threshold is live from doc 8 on
+                b = oracle.impact_search_tuned(indptr, docids, impacts, n_docs, qi, qt, qw, k, kind=kind, threads=2,
+                                               block_docs=block)
+                for x, y in zip(a, b[:3]):
+                    np.testing.assert_array_equal(x, y)
+
+    prop()
