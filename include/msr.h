@@ -319,13 +319,17 @@ int msr_provenance_hist(int device, uint32_t nq, const double* scores, const uin
  * Measured ceilings for `roofline.binding` (csrc/microbench.cu; replaces no reference call).  The sparse scorer shares
  * postings across the query batch through L2, so HBM does not bound it; bench.py reports it against these numbers,
  * measured on the same GPU in the same run.  *units_per_s: bytes/s for the two read benchmarks (`bytes` = buffer size;
- * L2: choose <= 64 MiB so it stays L2-resident, HBM: >= 1 GiB), warp instructions/s for the other two (`bytes` unused).
+ * L2: choose <= 64 MiB so it stays L2-resident, HBM: >= 1 GiB), instructions (wavefronts for MSR_MB_LDS) per second for the others (`bytes` unused).
  * Synchronous.
  */
 #define MSR_MB_L2_READ 0      /* ld.global.nc.L1::no_allocate.v2.u32, 8 in flight per thread, L2-resident buffer */
 #define MSR_MB_HBM_READ 1     /* the same loop over a buffer far larger than L2 */
 #define MSR_MB_RED_SHARED 2   /* red.shared.add.u32, one bank per lane */
-#define MSR_MB_ISSUE 3        /* independent dp4a chains: issue-slot ceiling */
+#define MSR_MB_ISSUE 3        /* independent dp4a chains (fma pipe) */
+#define MSR_MB_ALU 4          /* independent PRMT chains (alu pipe) */
+#define MSR_MB_LDS 5          /* conflict-free 16-byte ld.shared: wavefronts/s of the l1tex data pipe */
+#define MSR_MB_IMMA 6         /* mma.sync.m16n8k32 u8 x u8 -> s32 instructions/s */
+#define MSR_MB_IMMA_PRMT 7    /* the same with 8 PRMT per mma (the dense phase's 4x4 byte transposes) */
 int msr_microbench(int device, int what, uint64_t bytes, uint32_t iters, double* units_per_s, void* stream);
 
 #ifdef __cplusplus

@@ -38,20 +38,33 @@ __device__ __forceinline__ uint32_t pow2_ceil(uint32_t x) {
     return n;
 }
 
-__global__ void __launch_bounds__(kMergeThreads)
+// key number idx (0 <= idx < n_lists * stride) of query q, 0 when the slot is beyond its list's count
+__device__ __forceinline__ uint64_t merge_key_at(const MergeParams& P, uint32_t q, uint32_t idx) {
+    const uint32_t j = idx / P.stride, i = idx - j * P.stride;
+    const size_t li = P.mode == 0 ? (size_t)q * P.n_lists + j : (size_t)j * P.nq + q;
+    const size_t ci = (P.mode == 1 && P.cnt_list_stride) ? (size_t)j * P.cnt_list_stride + q : li;
+    if (i >= min(P.cnts[ci], P.stride)) return 0ull;
+    if (P.mode == 0) return P.keys[li * P.stride + i];
+    const size_t ro = (P.mode == 1 && P.list_stride) ? (size_t)j * P.list_stride + (size_t)q * P.stride : li * P.stride;
+    return make_key(P.scores[ro + i], (uint32_t)P.docs[ro + i]);
+}
+
+// One CTA per query.  Common case (large batches: the shared threshold keeps the per-tile lists short): all candidates fit
+// the shared buffer, one bitonic sort.  Otherwise (small batches, deep k: every tile delivers a full list) the k-th largest
+// key is located by an MSB-first radix select over the lists where they lie (8-bit digits; the lists stay in L2), and only
+// the keys at or above it are gathered and sorted -- 41 lists x 1000 keys took 600 us by repeated sorting, ~30 us this way.
+__global__ void __launch_bounds__(1024)
 topk_merge_kernel(const MergeParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
-    const uint32_t q = blockIdx.x, tid = threadIdx.x;
+    const uint32_t q = blockIdx.x, tid = threadIdx.x, nthr = blockDim.x;
     uint32_t fill = 0;
-    // Common case: all candidates of the query fit the buffer at once.  Every warp then reserves room for its lists
-    // with one shared atomic and copies them in parallel (the order inside the buffer is irrelevant, it is sorted next).
-    __shared__ uint32_t s_total, s_fill;
+    __shared__ uint32_t s_total, s_fill, s_hist[256], s_sel[3];
     if (tid == 0) { s_total = 0; s_fill = 0; }
     __syncthreads();
     {
         uint32_t mine = 0;
-        for (uint32_t j = tid; j < P.n_lists; j += kMergeThreads) {
+        for (uint32_t j = tid; j < P.n_lists; j += nthr) {
             const size_t li = P.mode == 0 ? (size_t)q * P.n_lists + j : (size_t)j * P.nq + q;
             const size_t ci = (P.mode == 1 && P.cnt_list_stride) ? (size_t)j * P.cnt_list_stride + q : li;
             mine += min(P.cnts[ci], P.stride);
@@ -60,10 +73,11 @@ topk_merge_kernel(const MergeParams P) {
         if ((tid & 31) == 0 && mine) atomicAdd(&s_total, mine);
     }
     __syncthreads();
-    const bool all_fit = s_total <= P.cap;
-    if (all_fit) {
+    const uint32_t total = s_total;
+    if (total <= P.cap) {
+        // every warp reserves room for its lists with one shared atomic and copies them (the order is irrelevant, it is sorted next)
         const uint32_t lane = tid & 31, warp = tid >> 5;
-        for (uint32_t j = warp; j < P.n_lists; j += kMergeThreads / 32) {
+        for (uint32_t j = warp; j < P.n_lists; j += nthr / 32) {
             const size_t li = P.mode == 0 ? (size_t)q * P.n_lists + j : (size_t)j * P.nq + q;
             const size_t ci = (P.mode == 1 && P.cnt_list_stride) ? (size_t)j * P.cnt_list_stride + q : li;
             const size_t ro = (P.mode == 1 && P.list_stride) ? (size_t)j * P.list_stride + (size_t)q * P.stride : li * P.stride;
@@ -82,40 +96,63 @@ topk_merge_kernel(const MergeParams P) {
             }
         }
         __syncthreads();
-        fill = s_total;
-    }
-    for (uint32_t j = 0; j < P.n_lists && !all_fit; ++j) {
-        const size_t li = P.mode == 0 ? (size_t)q * P.n_lists + j : (size_t)j * P.nq + q;
-        const size_t ci = (P.mode == 1 && P.cnt_list_stride) ? (size_t)j * P.cnt_list_stride + q : li;
-        const size_t ro = (P.mode == 1 && P.list_stride) ? (size_t)j * P.list_stride + (size_t)q * P.stride : li * P.stride;
-        const uint32_t c = min(P.cnts[ci], P.stride);
-        if (c == 0) continue;
-        if (fill + c > P.cap) {
-            const uint32_t n2 = pow2_ceil(fill);
-            for (uint32_t i = fill + tid; i < n2; i += kMergeThreads) buf[i] = 0;
-            bitonic_sort_desc(buf, n2);
-            fill = min(fill, P.k);
+        fill = total;
+    } else {
+        // radix select of the k-th largest key (keys of real hits are distinct and non-zero)
+        const uint32_t n_slots = P.n_lists * P.stride;
+        uint32_t need = P.k;                                    // total > cap >= 2k, so k keys exist
+        uint64_t prefix = 0;                                    // the digits fixed so far (top 8 * pass bits)
+        uint32_t pass = 0;
+        for (;; ++pass) {
+            for (uint32_t i = tid; i < 256; i += nthr) s_hist[i] = 0;
+            __syncthreads();
+            const uint32_t shift = 56 - 8 * pass;
+            for (uint32_t idx = tid; idx < n_slots; idx += nthr) {
+                const uint64_t key = merge_key_at(P, q, idx);
+                if (key && (pass == 0 || (key >> (shift + 8)) == prefix)) atomicAdd(&s_hist[(key >> shift) & 255u], 1u);
+            }
+            __syncthreads();
+            if (tid < 32) {                                     // lane l owns bins 255-8l .. 248-8l (descending)
+                uint32_t h[8], sum = 0;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) { h[i] = s_hist[255 - 8 * tid - i]; sum += h[i]; }
+                uint32_t before = warp_incl_scan(sum, tid) - sum;        // keys in higher bins
+                if (before < need && before + sum >= need) {
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        if (before < need && before + h[i] >= need) { s_sel[0] = 255 - 8 * tid - i; s_sel[1] = before; s_sel[2] = h[i]; }
+                        before += h[i];
+                    }
+                }
+            }
+            __syncthreads();
+            const uint32_t bin = s_sel[0], greater = s_sel[1], cnt = s_sel[2];
+            prefix = (prefix << 8) | bin;
+            // keys above the bin are certain; stop as soon as they and the bin's keys fit the buffer together
+            if ((P.k - need) + greater + cnt <= P.cap || pass == 7) break;
+            need -= greater;
+            __syncthreads();
         }
-        if (P.mode == 0) {
-            const uint64_t* src = P.keys + li * P.stride;
-            for (uint32_t i = tid; i < c; i += kMergeThreads) buf[fill + i] = src[i];
-        } else {
-            const float* ss = P.scores + ro;
-            const int32_t* dd = P.docs + ro;
-            for (uint32_t i = tid; i < c; i += kMergeThreads) buf[fill + i] = make_key(ss[i], (uint32_t)dd[i]);
+        const uint32_t shift = 56 - 8 * pass;
+        for (uint32_t idx = tid; idx < n_slots; idx += nthr) {
+            const uint64_t key = merge_key_at(P, q, idx);
+            if (key && (key >> shift) >= prefix) {
+                const uint32_t pos = atomicAdd(&s_fill, 1u);
+                if (pos < P.cap) buf[pos] = key;
+            }
         }
-        fill += c;
         __syncthreads();
+        fill = min(s_fill, P.cap);
     }
     if (fill > 1) {
         const uint32_t n2 = pow2_ceil(fill);
-        for (uint32_t i = fill + tid; i < n2; i += kMergeThreads) buf[i] = 0;
+        for (uint32_t i = fill + tid; i < n2; i += nthr) buf[i] = 0;
         bitonic_sort_desc(buf, n2);
     } else {
         __syncthreads();
     }
     const uint32_t n = min(fill, P.k);
-    for (uint32_t r = tid; r < P.k; r += kMergeThreads) {
+    for (uint32_t r = tid; r < P.k; r += nthr) {
         const bool ok = r < n;
         const uint64_t key = ok ? buf[r] : 0;
         const float sc = ok ? key_score(key) : 0.0f;
@@ -134,12 +171,10 @@ topk_merge_kernel(const MergeParams P) {
 }
 
 static int merge_launch(MergeParams P, cudaStream_t s) {
-    uint32_t need = P.k + P.stride;
-    uint64_t total = (uint64_t)P.n_lists * P.stride;
-    uint32_t cap = 2;
-    while (cap < need) cap <<= 1;
-    while (cap < total && cap < 8192) cap <<= 1;
-    if (cap > 8192) { set_error("topk merge: k + k_in = %u exceeds 8192", need); return MSR_ERR_INVALID; }
+    // buffer: at least 2k keys (the select path gathers k + the k-th key's bin), 2048 at least, a power of two
+    uint32_t cap = 2048;
+    while (cap < 2 * P.k) cap <<= 1;
+    if (cap > 8192) { set_error("topk merge: k = %u exceeds %u", P.k, MSR_MAX_K); return MSR_ERR_INVALID; }
     P.cap = cap;
     const size_t smem = (size_t)cap * 8;
     static std::atomic<uint64_t> attr_set{0};
@@ -147,7 +182,9 @@ static int merge_launch(MergeParams P, cudaStream_t s) {
         MSR_CUDA_CHECK(cudaFuncSetAttribute(topk_merge_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 8192 * 8));
         attr_mark(attr_set);
     }
-    topk_merge_kernel<<<P.nq, kMergeThreads, smem, s>>>(P);
+    // few queries cannot fill the GPU with CTAs: give each one more threads (the sort and the select scale with them)
+    const int threads = P.nq <= 148 ? 1024 : (P.nq <= 2048 ? 512 : kMergeThreads);
+    topk_merge_kernel<<<P.nq, threads, smem, s>>>(P);
     count_launch();
     MSR_CUDA_CHECK(cudaGetLastError());
     return MSR_OK;

@@ -144,7 +144,7 @@ class SparseIndex:
         return int(b.value)
 
 
-MB_L2_READ, MB_HBM_READ, MB_RED_SHARED, MB_ISSUE = 0, 1, 2, 3
+MB_L2_READ, MB_HBM_READ, MB_RED_SHARED, MB_ISSUE, MB_ALU, MB_LDS, MB_IMMA, MB_IMMA_PRMT = range(8)
 
 
 def microbench(what, nbytes=0, iters=5, device=0):

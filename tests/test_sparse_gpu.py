@@ -348,3 +348,43 @@ def test_bounded_select_edges(oracle, lib_built, tile):
     sc[perm[-2:]] = 0
     for k in (1, 512, 513):
         _check(oracle, *_one_term_index(sc), n, qi, qt, qw, k, tile_docs=tile)
+
+
+@pytest.mark.parametrize("n_lists,k_in,k,nq,fill", [
+    (41, 100, 100, 3, "full"),          # 4100 keys > the 2048-key buffer: radix-select path (small batch at 1 M docs)
+    (41, 1000, 1000, 2, "full"),        # the reference's depth (scripts/search.sh:25): 41 000 keys per query
+    (8, 1000, 1000, 5, "ragged"),       # cross-GPU merge shape, ragged counts
+    (300, 100, 37, 4, "ragged"),        # many lists, k below k_in
+    (64, 64, 4096, 2, "full"),          # k above the number of keys: everything, sorted
+    (5, 100, 100, 300, "ragged"),       # buffer path (<= 2048 keys), many queries
+])
+def test_topk_merge_select_path_vs_numpy(lib_built, n_lists, k_in, k, nq, fill):
+    """msr_topk_merge on lists too long for one shared-memory sort (the MSB-first radix select over the lists in place)
+    and on short ones, against a NumPy lexsort with the same (score desc, id asc) key.  Heavy score ties."""
+    from mllm_sparse_retrieval_b200.ops import topk_merge
+    rng = np.random.default_rng(n_lists * 1000 + k)
+    dev = torch.device("cuda")
+    scores = rng.integers(1, 400, size=(n_lists, nq, k_in)).astype(np.float32) * 64.0       # many equal scores
+    docs = np.stack([rng.permutation(n_lists * k_in * 4)[:n_lists * k_in].reshape(n_lists, k_in) for _ in range(nq)], 1).astype(np.int32)
+    counts = np.full((n_lists, nq), k_in, dtype=np.int32) if fill == "full" else rng.integers(0, k_in + 1, size=(n_lists, nq)).astype(np.int32)
+    ms, md, mc = topk_merge(torch.from_numpy(scores).to(dev), torch.from_numpy(docs).to(dev), torch.from_numpy(counts).to(dev), k)
+    ms, md, mc = ms.cpu().numpy(), md.cpu().numpy(), mc.cpu().numpy()
+    for q in range(nq):
+        s = np.concatenate([scores[j, q, :counts[j, q]] for j in range(n_lists)])
+        d = np.concatenate([docs[j, q, :counts[j, q]] for j in range(n_lists)])
+        order = np.lexsort((d, -s.astype(np.float64)))[:k]
+        n = len(order)
+        assert mc[q] == n
+        np.testing.assert_array_equal(md[q, :n], d[order])
+        np.testing.assert_array_equal(ms[q, :n], s[order])
+        assert (md[q, n:] == -1).all() and (ms[q, n:] == 0).all()
+
+
+@pytest.mark.parametrize("nq,k", [(1, 100), (4, 1000), (2, 10), (3, 4096)])
+def test_small_batch_deep_k_matches_oracle(oracle, lib_built, nq, k):
+    """The reference's operating point (scripts/search.sh: batch 2, depth 1000; search_sparse.sh: batch 4, depth 10): few
+    queries, many tiles, every tile delivers a full list -> the merge's select path.  Bit-exact against the oracle."""
+    from mllm_sparse_retrieval_b200 import synth
+    coll = synth.make_collection(60000, 48, V=8192, seed=77, device="cuda")
+    qs = synth.make_queries(nq, 24, V=8192, seed=78, device="cuda")
+    _check(oracle, *coll.numpy(), coll.n_docs, *qs.numpy(), k, tile_docs=2048)          # 30 tiles
