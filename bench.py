@@ -579,13 +579,13 @@ def run_ours(a, rank, world, local_rank):
            "e2e": {"value": nq * a.steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                    "api": "msr_sparse_search(MSR_HOST) with pinned host buffers" if world == 1 else
                           ("pinned query CSR -> msr_sparse_search(MSR_DEVICE) per shard with the exchange fused into the tile-merge "
-                           "epilogue (peer stores over NVLink, symmetric memory) -> barrier -> msr_topk_merge_strided -> pinned host "
+                           "epilogue (peer stores over NVLink, symmetric memory) -> msr_topk_merge_exchange (signal + wait + merge) -> pinned host "
                            "lists on rank 0" if px is not None else
                            "pinned query CSR -> msr_sparse_search(MSR_DEVICE) per shard -> NCCL all-gather -> msr_topk_merge -> "
                            "pinned host lists on rank 0")},
            "gpu_launches": int(launches), "roofline": roof, "clocks": clocks, "parity_check": check,
            "query_rotation": f"{n_var} rotations of the query order, one per step in turn",
-           "exchange": "single GPU" if world == 1 else ("p2p: fused peer stores + signal-pad barrier" if px is not None else "nccl all-gather"),
+           "exchange": "single GPU" if world == 1 else ("p2p: 16-byte peer stores fused into the tile merge, barrier fused into the final merge kernel, pruning threshold shared across GPUs" if px is not None else "nccl all-gather"),
            "index": {"n_tiles": idx.n_tiles, "tile_docs": idx.tile_docs, "nnz_shard": idx.nnz, "resident_bytes": idx.resident_bytes}}
     if idx.resident_bytes < (126 << 20):                       # PER-GPU bytes against this GPU's L2
         if idx.resident_bytes * world < (126 << 20):

@@ -150,6 +150,33 @@ int msr_sparse_set_peer_outputs(msr_sparse_index* h, uint32_t n_peers, float* co
                                 int32_t* const* peer_docs, uint32_t* const* peer_counts);
 
 /*
+ * Cross-GPU threshold sharing for the doc-sharded search (no reference counterpart -- FAISS IndexShards and
+ * Lucene share nothing between shards).  `local_theta` u64[capacity] lives in symmetric memory of this GPU, `peer_theta[p]`
+ * is the same array on peer p.  Device-path searches of at most `capacity` queries then keep the per-query pruning
+ * threshold there and push every raise to the peers (red.max at system scope over NVLink): each shard prunes with the
+ * k-th best key of the whole collection.  A shard's own list may then hold FEWER than k docs (never a wrong one); the merge
+ * of the shards' lists is exact.  The caller clears `local_theta` before each search and must not reuse an array before
+ * every GPU has finished the search that wrote into it (sharded.PeerExchange rotates three).  rot_num / rot_den: fraction
+ * of the batch at which this GPU starts its walk over the queries (rank / world), so the GPUs publish different queries
+ * first.  local_theta = NULL switches the sharing off.
+ */
+int msr_sparse_set_peer_theta(msr_sparse_index* h, uint32_t n_peers, uint64_t* local_theta, uint64_t* const* peer_theta,
+                              uint32_t capacity, uint32_t rot_num, uint32_t rot_den);
+
+/*
+ * msr_topk_merge_strided with the exchange barrier fused into the kernel (replaces a separate signal-pad barrier launch):
+ * the kernel first stores `flag_value` into flag_peers[p][my_rank] on every peer (release, system scope; the kernel that
+ * produced this GPU's rows precedes it on `stream`), waits until flag_local[peer_ranks[p]] >= flag_value for every peer
+ * (wrap-safe compare), then merges.  flag_value must grow by one per exchange step; flags are u32 in symmetric memory,
+ * zero-initialised.
+ */
+int msr_topk_merge_exchange(int device, uint32_t n_lists, uint32_t nq, uint32_t k_in, const float* scores,
+                            const int32_t* docs, const uint32_t* counts, size_t list_stride, size_t count_list_stride,
+                            uint32_t k, float* out_scores, int32_t* out_docs, uint32_t* out_counts, uint32_t n_peers,
+                            uint32_t my_rank, uint32_t* flag_local, uint32_t* const* flag_peers, const uint32_t* peer_ranks,
+                            uint32_t flag_value, void* stream);
+
+/*
  * Stand-alone radix-select top-k over dense score rows (kernel (b) on its own): scores [nq, n] row-major
  * fp32 on the device; output k best per row by (score desc, column asc), columns offset by col_base.
  * Entries equal to -inf are never returned (counts < k possible).

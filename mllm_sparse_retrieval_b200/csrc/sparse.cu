@@ -83,6 +83,10 @@ struct msr_sparse_index {
     float* peer_scores[16] = {};
     int32_t* peer_docs[16] = {};
     uint32_t* peer_counts[16] = {};
+    // cross-GPU threshold sharing (msr_sparse_set_peer_theta)
+    unsigned long long* ext_theta = nullptr;      // this GPU's theta[] in symmetric memory (capacity ext_theta_cap queries)
+    unsigned long long* peer_theta[15] = {};
+    uint32_t n_peer_theta = 0, ext_theta_cap = 0, q_rot_num = 0, q_rot_den = 1;
 };
 
 namespace msr {
@@ -646,7 +650,10 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     P.k = k; P.k_stride = k_stride;
     P.cand_keys = (uint64_t*)(base + off_keys); P.cand_cnt = (uint32_t*)(base + off_cnt);
     P.theta = (unsigned long long*)(base + off_theta); P.tlist = (uint64_t*)(base + off_tlist);
-    P.use_theta = (h->n_tiles > 1 && h->use_theta) ? 1u : 0u;
+    const bool shared_theta = where == MSR_DEVICE && h->ext_theta && h->use_theta && nq <= h->ext_theta_cap;
+    P.use_theta = ((h->n_tiles > 1 || shared_theta) && h->use_theta) ? 1u : 0u;
+    P.n_peer_theta = shared_theta ? h->n_peer_theta : 0u;
+    for (uint32_t p = 0; p < P.n_peer_theta; ++p) P.peer_theta[p] = h->peer_theta[p];
     // Re-publishing costs a rank count over c + k keys; it pays while the list is still loose.  Measured (k = 100):
     // 6 tiles k/2 3.47 ms, k/4 3.63, k/8 3.68; 21 tiles 10.36 / 10.45 / 10.70; 41 tiles 19.84 (+0.5 ms final merge) / 19.78 / 19.96.
     P.merge_min = std::max(1u, k >> (h->n_tiles <= 24 ? 1 : 2));
@@ -656,6 +663,8 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     for (uint32_t q0 = 0; q0 < nq; q0 += qc) {
         const uint32_t n = std::min(qc, nq - q0);
         P.q_lo = q0; P.nq = n;
+        P.q_rot = shared_theta ? (uint32_t)((uint64_t)n * h->q_rot_num / h->q_rot_den) : 0u;
+        if (shared_theta) P.theta = h->ext_theta + q0;           // cleared by the caller (it rotates three buffers)
         cudaEvent_t* evs = nullptr;
         if (h->profiling) {
             if (h->ev_used + 3 > h->ev.size()) {
@@ -667,6 +676,7 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
         }
         if (P.use_theta)      // theta[] and tlist[] are contiguous up to alignment: one clear
             MSR_CUDA_CHECK(cudaMemsetAsync(base + off_theta, 0, off_tlist - off_theta + (size_t)n * k * 8, s));
+        static_assert(sizeof(SearchParams) <= 4000, "kernel parameter space");
         sparse_score_topk_kernel<<<n * h->n_tiles, kThreads, smem, s>>>(P);
         count_launch();
         MSR_CUDA_CHECK(cudaGetLastError());
@@ -752,6 +762,25 @@ extern "C" int msr_sparse_query_traffic(msr_sparse_index* h, uint32_t nq, const 
     MSR_CUDA_CHECK(cudaStreamSynchronize(s));
     MSR_CUDA_CHECK(cudaGetLastError());
     *bytes = res + (uint64_t)nnz_q * 8 + (uint64_t)(nq + 1) * 8;   // + the query CSR itself
+    return MSR_OK;
+}
+
+extern "C" int msr_sparse_set_peer_theta(msr_sparse_index* h, uint32_t n_peers, uint64_t* local_theta,
+                                         uint64_t* const* peer_theta, uint32_t capacity, uint32_t rot_num, uint32_t rot_den) {
+    MSR_REQUIRE(h, "msr_sparse_set_peer_theta: NULL handle");
+    MSR_REQUIRE(n_peers <= 15, "msr_sparse_set_peer_theta: at most 15 peers");
+    if (!local_theta) {                                          // switch the sharing off
+        h->ext_theta = nullptr; h->n_peer_theta = 0; h->ext_theta_cap = 0; h->q_rot_num = 0; h->q_rot_den = 1;
+        return MSR_OK;
+    }
+    MSR_REQUIRE(capacity > 0 && rot_den > 0 && rot_num < rot_den, "msr_sparse_set_peer_theta: bad capacity / rotation");
+    MSR_REQUIRE(n_peers == 0 || peer_theta, "msr_sparse_set_peer_theta: NULL pointer table");
+    for (uint32_t p = 0; p < n_peers; ++p) {
+        MSR_REQUIRE(peer_theta[p], "msr_sparse_set_peer_theta: NULL peer pointer %u", p);
+        h->peer_theta[p] = (unsigned long long*)peer_theta[p];
+    }
+    h->ext_theta = (unsigned long long*)local_theta; h->n_peer_theta = n_peers; h->ext_theta_cap = capacity;
+    h->q_rot_num = rot_num; h->q_rot_den = rot_den;
     return MSR_OK;
 }
 

@@ -61,7 +61,22 @@ struct SearchParams {
     uint32_t use_theta;
     uint32_t merge_min;           // a tile re-publishes the query's threshold list when it adds >= this many candidates
     uint32_t fast_select;         // exact select through the per-thread-maxima bound first (MSR_SPARSE_FAST_SELECT, default 1)
+    // Doc-sharded search over several GPUs (msr_sparse_set_peer_theta): theta[] then lives in symmetric memory and every
+    // raise is ALSO pushed into the same slot of the other GPUs' arrays (fire-and-forget red.max over NVLink).  A key is
+    // (float32 score, GLOBAL doc id), so "at least k docs of the COLLECTION reach theta" holds on every GPU and each shard
+    // prunes as if it had all the tiles.  A shard's own list may then hold fewer than k docs; the merged list is exact.
+    uint32_t n_peer_theta;
+    uint32_t q_rot;               // the grid walks the queries from this offset (a different one per GPU), so the GPUs
+                                  // publish different queries first and find each other's thresholds already there
+    unsigned long long* peer_theta[15];
 };
+
+// raise the query's threshold here and on every peer GPU
+__device__ __forceinline__ void theta_raise(const SearchParams& P, unsigned long long* theta_p, uint32_t q, unsigned long long key) {
+    atomicMax(theta_p, key);
+    for (uint32_t p = 0; p < P.n_peer_theta; ++p)
+        asm volatile("red.relaxed.sys.global.max.u64 [%0], %1;" ::"l"(P.peer_theta[p] + P.q_lo + q), "l"(key) : "memory");
+}
 
 // One warp per query: exact-arithmetic range check over the kept terms (see msr.h), done once instead of per tile.
 __global__ void query_prep_kernel(const uint8_t* __restrict__ keep, const uint32_t* __restrict__ maximp, uint32_t n_terms,
@@ -245,7 +260,8 @@ sparse_score_topk_kernel(const SearchParams P) {
     const uint32_t acc_s = (uint32_t)__cvta_generic_to_shared(acc);
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t q = blockIdx.x % P.nq;
+    uint32_t q = blockIdx.x % P.nq + P.q_rot;
+    if (q >= P.nq) q -= P.nq;
     const uint32_t tile = blockIdx.x / P.nq;
     const uint32_t tile_lo = tile * P.tile_docs;
     const uint32_t tl = min(P.tile_docs, P.n_docs - tile_lo);
@@ -521,7 +537,7 @@ sparse_score_topk_kernel(const SearchParams P) {
                 if (!__syncthreads_or((int)dup)) {
                     if (mine && gt < P.k) {
                         tlist[gt] = mine;
-                        if (gt == P.k - 1) atomicMax(theta_p, (unsigned long long)mine);
+                        if (gt == P.k - 1) theta_raise(P, theta_p, q, (unsigned long long)mine);
                     }
                     return;
                 }
@@ -548,7 +564,7 @@ sparse_score_topk_kernel(const SearchParams P) {
                 if (f[j]) {
                     if (ex < P.k) {
                         tlist[ex] = e[j];
-                        if (ex == P.k - 1) atomicMax(theta_p, (unsigned long long)e[j]);
+                        if (ex == P.k - 1) theta_raise(P, theta_p, q, (unsigned long long)e[j]);
                     }
                     ++ex;
                 }
@@ -630,7 +646,7 @@ sparse_score_topk_kernel(const SearchParams P) {
                         keys_out[gt] = mine;
                         if (P.use_theta) {
                             tlist[gt] = mine;
-                            if (gt == P.k - 1) atomicMax(theta_p, (unsigned long long)mine);
+                            if (gt == P.k - 1) theta_raise(P, theta_p, q, (unsigned long long)mine);
                         }
                     }
                 }
@@ -748,7 +764,7 @@ sparse_score_topk_kernel(const SearchParams P) {
     if (P.use_theta && kq == P.k) {
         __syncthreads();
         for (uint32_t r = tid; r < P.k; r += kThreads) tlist[r] = keys_out[r];
-        if (tid == 0) atomicMax(theta_p, (unsigned long long)keys_out[P.k - 1]);
+        if (tid == 0) theta_raise(P, theta_p, q, (unsigned long long)keys_out[P.k - 1]);
     }
 }
 

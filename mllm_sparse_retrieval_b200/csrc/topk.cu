@@ -30,6 +30,14 @@ struct MergeParams {
     float* peer_scores[kMaxPeers];
     int32_t* peer_docs[kMaxPeers];
     uint32_t* peer_counts[kMaxPeers];
+    // Fused barrier (msr_topk_merge_exchange): before it reads the lists, the kernel tells every peer GPU that THIS GPU's
+    // rows of step `flag_value` have been stored (flag_peers[p][my_rank] = flag_value, release at system scope, after the
+    // producing kernel of the same stream has completed) and waits until every peer has said the same (flag_local[rank]).
+    uint32_t n_flag_peers, my_rank, flag_value;
+    uint32_t vec_ok;                         // set by merge_launch: k % 4 == 0 and every output row base is 16-byte aligned
+    uint32_t* flag_local;                    // [world] written by the peers
+    uint32_t* flag_peers[kMaxPeers];         // the peers' flag arrays
+    uint32_t flag_peer_rank[kMaxPeers];      // rank of peer p (index into flag_local)
 };
 
 __device__ __forceinline__ uint32_t pow2_ceil(uint32_t x) {
@@ -61,6 +69,20 @@ topk_merge_kernel(const MergeParams P) {
     uint32_t fill = 0;
     __shared__ uint32_t s_total, s_fill, s_hist[256], s_sel[3];
     if (tid == 0) { s_total = 0; s_fill = 0; }
+    if (P.n_flag_peers) {
+        // signal (CTA 0 only) then wait; no CTA waits on another CTA of this grid, only on the other GPUs
+        if (tid < P.n_flag_peers) {
+            if (blockIdx.x == 0) {
+                __threadfence_system();
+                asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.flag_peers[tid] + P.my_rank), "r"(P.flag_value) : "memory");
+            }
+            const uint32_t* f = P.flag_local + P.flag_peer_rank[tid];
+            uint32_t v;
+            do {
+                asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+            } while ((int32_t)(v - P.flag_value) < 0);
+        }
+    }
     __syncthreads();
     {
         uint32_t mine = 0;
@@ -152,16 +174,38 @@ topk_merge_kernel(const MergeParams P) {
         __syncthreads();
     }
     const uint32_t n = min(fill, P.k);
-    for (uint32_t r = tid; r < P.k; r += nthr) {
-        const bool ok = r < n;
-        const uint64_t key = ok ? buf[r] : 0;
-        const float sc = ok ? key_score(key) : 0.0f;
-        const int32_t dc = ok ? (int32_t)key_doc(key) : -1;
-        P.out_scores[(size_t)q * P.k + r] = sc;
-        P.out_docs[(size_t)q * P.k + r] = dc;
-        for (uint32_t p = 0; p < P.n_peers; ++p) {               // the exchange: same row into every peer's slot
-            P.peer_scores[p][(size_t)q * P.k + r] = sc;
-            P.peer_docs[p][(size_t)q * P.k + r] = dc;
+    if (P.n_peers && P.vec_ok) {
+        // rows leave as 16-byte stores: keys -> (score, doc) in place, then one uint4 per 4 ranks and destination
+        __syncthreads();
+        uint32_t* pair = reinterpret_cast<uint32_t*>(buf);
+        for (uint32_t r = tid; r < P.k; r += nthr) {
+            const bool ok = r < n;
+            const uint64_t key = ok ? buf[r] : 0;
+            pair[2 * r] = ok ? __float_as_uint(key_score(key)) : 0u;
+            pair[2 * r + 1] = ok ? key_doc(key) : 0xFFFFFFFFu;
+        }
+        __syncthreads();
+        const uint32_t nv = P.k >> 2, n_dst = P.n_peers + 1;
+        for (uint32_t i = tid; i < 2 * nv * n_dst; i += nthr) {
+            const uint32_t v = i % nv, what = (i / nv) & 1u, dst = i / (2 * nv);
+            const uint32_t* src = pair + 8 * v + what;
+            const uint4 x = make_uint4(src[0], src[2], src[4], src[6]);
+            void* base = what ? (dst ? (void*)P.peer_docs[dst - 1] : (void*)P.out_docs)
+                              : (dst ? (void*)P.peer_scores[dst - 1] : (void*)P.out_scores);
+            reinterpret_cast<uint4*>(reinterpret_cast<uint32_t*>(base) + (size_t)q * P.k)[v] = x;
+        }
+    } else {
+        for (uint32_t r = tid; r < P.k; r += nthr) {
+            const bool ok = r < n;
+            const uint64_t key = ok ? buf[r] : 0;
+            const float sc = ok ? key_score(key) : 0.0f;
+            const int32_t dc = ok ? (int32_t)key_doc(key) : -1;
+            P.out_scores[(size_t)q * P.k + r] = sc;
+            P.out_docs[(size_t)q * P.k + r] = dc;
+            for (uint32_t p = 0; p < P.n_peers; ++p) {           // the exchange: same row into every peer's slot
+                P.peer_scores[p][(size_t)q * P.k + r] = sc;
+                P.peer_docs[p][(size_t)q * P.k + r] = dc;
+            }
         }
     }
     if (tid == 0) {
@@ -176,6 +220,9 @@ static int merge_launch(MergeParams P, cudaStream_t s) {
     while (cap < 2 * P.k) cap <<= 1;
     if (cap > 8192) { set_error("topk merge: k = %u exceeds %u", P.k, MSR_MAX_K); return MSR_ERR_INVALID; }
     P.cap = cap;
+    auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+    P.vec_ok = (P.k & 3u) == 0 && al16(P.out_scores) && al16(P.out_docs);
+    for (uint32_t p = 0; p < P.n_peers; ++p) P.vec_ok = P.vec_ok && al16(P.peer_scores[p]) && al16(P.peer_docs[p]);
     const size_t smem = (size_t)cap * 8;
     static std::atomic<uint64_t> attr_set{0};
     if (attr_needed(attr_set)) {
@@ -439,6 +486,33 @@ extern "C" int msr_topk_merge_strided(int device, uint32_t n_lists, uint32_t nq,
     P.nq = nq; P.n_lists = n_lists; P.stride = k_in; P.k = k; P.mode = 1;
     P.scores = scores; P.docs = docs; P.cnts = counts; P.list_stride = list_stride; P.cnt_list_stride = count_list_stride;
     P.out_scores = out_scores; P.out_docs = out_docs; P.out_counts = out_counts;
+    return merge_launch(P, (cudaStream_t)stream);
+}
+
+extern "C" int msr_topk_merge_exchange(int device, uint32_t n_lists, uint32_t nq, uint32_t k_in, const float* scores,
+                                       const int32_t* docs, const uint32_t* counts, size_t list_stride,
+                                       size_t count_list_stride, uint32_t k, float* out_scores, int32_t* out_docs,
+                                       uint32_t* out_counts, uint32_t n_peers, uint32_t my_rank, uint32_t* flag_local,
+                                       uint32_t* const* flag_peers, const uint32_t* peer_ranks, uint32_t flag_value,
+                                       void* stream) {
+    MSR_REQUIRE(n_lists >= 1 && k >= 1 && k_in >= 1, "msr_topk_merge_exchange: n_lists, k, k_in must be >= 1");
+    MSR_REQUIRE(k <= MSR_MAX_K && k_in <= MSR_MAX_K, "msr_topk_merge_exchange: k/k_in above %u", MSR_MAX_K);
+    MSR_REQUIRE(list_stride >= (size_t)nq * k_in && count_list_stride >= nq, "msr_topk_merge_exchange: list strides too small");
+    MSR_REQUIRE(n_peers >= 1 && n_peers <= (uint32_t)kMaxPeers - 1 && flag_local && flag_peers && peer_ranks,
+                "msr_topk_merge_exchange: bad peer arguments");
+    MSR_REQUIRE(nq >= 1, "msr_topk_merge_exchange: nq = 0 (the flags must still be exchanged: pass at least one row)");
+    MSR_REQUIRE(scores && docs && counts && out_scores && out_docs && out_counts, "msr_topk_merge_exchange: NULL buffer");
+    int rc = use_device(device);
+    if (rc) return rc;
+    MergeParams P{};
+    P.nq = nq; P.n_lists = n_lists; P.stride = k_in; P.k = k; P.mode = 1;
+    P.scores = scores; P.docs = docs; P.cnts = counts; P.list_stride = list_stride; P.cnt_list_stride = count_list_stride;
+    P.out_scores = out_scores; P.out_docs = out_docs; P.out_counts = out_counts;
+    P.n_flag_peers = n_peers; P.my_rank = my_rank; P.flag_value = flag_value; P.flag_local = flag_local;
+    for (uint32_t p = 0; p < n_peers; ++p) {
+        MSR_REQUIRE(flag_peers[p], "msr_topk_merge_exchange: NULL flag pointer %u", p);
+        P.flag_peers[p] = flag_peers[p]; P.flag_peer_rank[p] = peer_ranks[p];
+    }
     return merge_launch(P, (cudaStream_t)stream);
 }
 

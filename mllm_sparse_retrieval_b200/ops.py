@@ -90,6 +90,14 @@ class SparseIndex:
         arr = lambda xs: (ctypes.c_void_p * max(1, n))(*[ctypes.c_void_p(int(x)) for x in xs])
         check(_lib.load().msr_sparse_set_peer_outputs(self._h, n, arr(peer_scores), arr(peer_docs), arr(peer_counts)))
 
+    def set_peer_theta(self, local_theta=0, peer_theta=(), capacity=0, rank=0, world=1):
+        """Cross-GPU threshold sharing (msr_sparse_set_peer_theta): raw device addresses of this GPU's u64[capacity]
+        threshold array in symmetric memory and of the peers' copies; ``local_theta=0`` switches it off."""
+        n = len(peer_theta)
+        arr = (ctypes.c_void_p * max(1, n))(*[ctypes.c_void_p(int(x)) for x in peer_theta])
+        check(_lib.load().msr_sparse_set_peer_theta(self._h, n, ctypes.c_void_p(int(local_theta)) if local_theta else None, arr,
+                                                    int(capacity), int(rank), int(max(1, world))))
+
     def status(self):
         """Synchronise and raise MsrError(MSR_ERR_RANGE) if an earlier device-path search left the exact range."""
         with torch.cuda.device(self.device):
@@ -180,6 +188,23 @@ def topk_merge_strided(scores_ptr, docs_ptr, counts_ptr, n_lists, nq, k_in, list
         check(_lib.load().msr_topk_merge_strided(di, n_lists, nq, k_in, ctypes.c_void_p(scores_ptr), ctypes.c_void_p(docs_ptr),
                                                  ctypes.c_void_p(counts_ptr), list_stride, count_list_stride, int(k),
                                                  ptr(out[0]), ptr(out[1]), ptr(out[2]), current_stream_ptr(di)))
+    return out
+
+
+def topk_merge_exchange(scores_ptr, docs_ptr, counts_ptr, n_lists, nq, k_in, list_stride, count_list_stride, k, out, device,
+                        rank, flag_local, flag_peers, peer_ranks, flag_value):
+    """msr_topk_merge_exchange: ``topk_merge_strided`` with the exchange barrier fused in (signal the peers, wait for
+    them, merge -- one kernel).  flag_local / flag_peers are raw device addresses of u32 flag arrays in symmetric memory."""
+    di = _dev_index(device)
+    n = len(flag_peers)
+    fp = (ctypes.c_void_p * max(1, n))(*[ctypes.c_void_p(int(x)) for x in flag_peers])
+    pr = (ctypes.c_uint32 * max(1, n))(*[int(x) for x in peer_ranks])
+    with torch.cuda.device(di):
+        check(_lib.load().msr_topk_merge_exchange(di, n_lists, nq, k_in, ctypes.c_void_p(scores_ptr), ctypes.c_void_p(docs_ptr),
+                                                  ctypes.c_void_p(counts_ptr), list_stride, count_list_stride, int(k),
+                                                  ptr(out[0]), ptr(out[1]), ptr(out[2]), n, int(rank),
+                                                  ctypes.c_void_p(int(flag_local)), fp, pr, int(flag_value) & 0xFFFFFFFF,
+                                                  current_stream_ptr(di)))
     return out
 
 

@@ -78,78 +78,96 @@ class PipelinedExchange:
         return self.final
 
 
+def peer_layout(nq, k, world):
+    """Symmetric buffer of ``PeerExchange`` in 4-byte units (every section starts on a 16-byte boundary):
+    2 step buffers x world slots of [scores nq*k | docs nq*k | counts nq(+pad)], then 3 threshold arrays of nq u64, then
+    world flags.  Returns (slot, theta_off, flag_off, total)."""
+    al = lambda x: (x + 3) // 4 * 4
+    slot = 2 * al(nq * k) + al(nq)
+    theta_off = 2 * world * slot
+    flag_off = theta_off + 3 * al(2 * nq)
+    return slot, theta_off, flag_off, flag_off + al(world)
+
+
 class PeerExchange:
     """The same exchange with the transfer FUSED into the scorer's last kernel: the tile-merge epilogue of every rank
-    stores its [nq,k] result rows straight into that rank's slot of a symmetric-memory buffer on every other GPU (NVLink
-    peer stores, ``msr_sparse_set_peer_outputs``), a signal-pad barrier follows, and ``msr_topk_merge_strided`` merges
-    the slots in place.  No NCCL call is on the path.  Two buffers alternate, so a rank that runs ahead writes the slots of
-    step n+1 while a slower peer still merges step n; the barrier of step n+1 orders the reuse two steps later.
+    stores its [nq,k] result rows straight into that rank's slot of a symmetric-memory buffer on every other GPU (16-byte
+    NVLink peer stores, ``msr_sparse_set_peer_outputs``); ONE more kernel (``msr_topk_merge_exchange``) then signals the
+    peers, waits for their signals and merges the slots in place.  No NCCL call and no separate barrier launch is on the
+    path.  Two step buffers alternate, so a rank that runs ahead writes the slots of step n+1 while a slower peer still
+    merges step n; a rank can only reach step n+2 after every peer has signalled step n+1, i.e. finished merging step n.
 
-    Buffer of one step, in 4-byte units: [world][ scores nq*k | docs nq*k | counts nq ].  Raises (RuntimeError / ImportError)
-    when symmetric memory cannot be set up; callers fall back to ``PipelinedExchange`` (NCCL)."""
+    The scorer's pruning threshold is shared the same way (``msr_sparse_set_peer_theta``): theta[q] lives in the symmetric
+    buffer and every raise is pushed to all peers, so a shard with 6 tiles prunes like one with 41.  Three threshold
+    arrays rotate (step n uses n % 3 and clears (n + 2) % 3), so a peer that is one step ahead never has its pushes
+    wiped, and no array is reused before every rank has finished with it.
 
-    def __init__(self, nq, k, device, world, rank, group=None):
+    Raises (RuntimeError / ImportError) when symmetric memory cannot be set up; callers fall back to
+    ``PipelinedExchange`` (NCCL)."""
+
+    def __init__(self, nq, k, device, world, rank, group=None, share_theta=True):
         import torch.distributed._symmetric_memory as symm_mem
         self.nq, self.k, self.device, self.world, self.rank = nq, k, torch.device(device), world, rank
         group = group if group is not None else dist.group.WORLD
-        self.slot = 2 * nq * k + nq                                   # 4-byte units per (step buffer, rank)
-        self.buf = symm_mem.empty((2 * world * self.slot,), dtype=torch.int32, device=self.device)
+        self.slot, self.theta_off, self.flag_off, total = peer_layout(nq, k, world)
+        self.buf = symm_mem.empty((total,), dtype=torch.int32, device=self.device)
+        self.buf.zero_()
         self.hdl = symm_mem.rendezvous(self.buf, group)
         self.ptrs = [int(p) for p in self.hdl.buffer_ptrs]
         self.final = (torch.empty((nq, k), dtype=torch.float32, device=self.device),
                       torch.empty((nq, k), dtype=torch.int32, device=self.device),
                       torch.empty((nq,), dtype=torch.int32, device=self.device))
         self.step = 0
-        self.hdl.barrier(channel=0)
+        self.share_theta = share_theta
+        self.peers = [r for r in range(world) if r != rank]
+        torch.cuda.synchronize(self.device)
+        self.hdl.barrier(channel=0)                                     # every rank's buffer is zeroed before anyone writes
 
     def _slot_ptrs(self, base, parity, who):
+        al = lambda x: (x + 3) // 4 * 4
         b = base + 4 * ((parity * self.world + who) * self.slot)
-        return b, b + 4 * self.nq * self.k, b + 8 * self.nq * self.k
+        return b, b + 4 * al(self.nq * self.k), b + 8 * al(self.nq * self.k)
+
+    def _theta_ptr(self, base, which):
+        return base + 4 * (self.theta_off + which * ((2 * self.nq + 3) // 4 * 4))
 
     def run(self, index, search, nq=None):
         """search(out_views) runs ONE device-path search of the whole batch on ``index`` (a ``SparseIndex``) writing
         (scores, ids, counts) into out_views; returns the merged result of all shards on the current stream.
         ``nq`` <= the capacity given at construction (default: the capacity) is the batch size of THIS call and must be
         the same on every rank; the slots keep their capacity-sized layout and only the first ``nq`` rows are used."""
-        if nq is not None and nq != self.nq:
-            return self._run_partial(index, search, int(nq))
+        nq = self.nq if nq is None else int(nq)
+        assert 0 < nq <= self.nq
         par = self.step & 1
+        t_now, t_clear = self.step % 3, (self.step + 2) % 3
         self.step += 1
-        peers = [self._slot_ptrs(self.ptrs[r], par, self.rank) for r in range(self.world) if r != self.rank]
+        al = lambda x: (x + 3) // 4 * 4
+        peers = [self._slot_ptrs(self.ptrs[r], par, self.rank) for r in self.peers]
         index.set_peer_outputs([p[0] for p in peers], [p[1] for p in peers], [p[2] for p in peers])
+        if self.share_theta:
+            # the array two steps ahead is cleared now: nobody can be writing it yet, and nobody will read it before
+            tw = al(2 * self.nq)
+            o = self.theta_off + t_clear * tw
+            self.buf[o:o + tw].zero_()
+            index.set_peer_theta(self._theta_ptr(self.ptrs[self.rank], t_now), [self._theta_ptr(self.ptrs[r], t_now) for r in self.peers],
+                                 self.nq, self.rank, self.world)
         try:
             # the local slot is the search's own output: views into the symmetric buffer
             o = self.slot * (par * self.world + self.rank)
-            nk = self.nq * self.k
-            out = (self.buf[o:o + nk].view(torch.float32).view(self.nq, self.k), self.buf[o + nk:o + 2 * nk].view(self.nq, self.k),
-                   self.buf[o + 2 * nk:o + 2 * nk + self.nq])
-            search(out)
-        finally:
-            index.set_peer_outputs()
-        self.hdl.barrier(channel=0)                                     # every rank's rows have landed everywhere
-        s0, d0, c0 = self._slot_ptrs(self.ptrs[self.rank], par, 0)
-        ops.topk_merge_strided(s0, d0, c0, self.world, self.nq, self.k, self.slot, self.slot, self.k, self.final, self.device)
-        return self.final
-
-    def _run_partial(self, index, search, nq):
-        assert 0 < nq < self.nq
-        par = self.step & 1
-        self.step += 1
-        peers = [self._slot_ptrs(self.ptrs[r], par, self.rank) for r in range(self.world) if r != self.rank]
-        index.set_peer_outputs([p[0] for p in peers], [p[1] for p in peers], [p[2] for p in peers])
-        try:
-            o = self.slot * (par * self.world + self.rank)
-            cap_nk = self.nq * self.k
+            cap_nk = al(self.nq * self.k)
             out = (self.buf[o:o + nq * self.k].view(torch.float32).view(nq, self.k),
                    self.buf[o + cap_nk:o + cap_nk + nq * self.k].view(nq, self.k),
                    self.buf[o + 2 * cap_nk:o + 2 * cap_nk + nq])
             search(out)
         finally:
             index.set_peer_outputs()
-        self.hdl.barrier(channel=0)
+            if self.share_theta:
+                index.set_peer_theta()
         s0, d0, c0 = self._slot_ptrs(self.ptrs[self.rank], par, 0)
-        final = tuple(t[:nq] for t in self.final)
-        ops.topk_merge_strided(s0, d0, c0, self.world, nq, self.k, self.slot, self.slot, self.k, final, self.device)
+        final = self.final if nq == self.nq else tuple(t[:nq] for t in self.final)
+        ops.topk_merge_exchange(s0, d0, c0, self.world, nq, self.k, self.slot, self.slot, self.k, final, self.device,
+                                self.rank, self.ptrs[self.rank] + 4 * self.flag_off,
+                                [self.ptrs[r] + 4 * self.flag_off for r in self.peers], self.peers, self.step)
         return final
 
 

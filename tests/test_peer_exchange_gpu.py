@@ -27,7 +27,8 @@ def _problem():
     rng = np.random.default_rng(77)
     n_docs, n_terms = 9000, 1500
     indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 48)
-    qs = [random_queries(rng, 64, n_terms, 16) for _ in range(3)]         # a different batch per step
+    qs = [random_queries(rng, 64 if i % 3 else 40, n_terms, 16) for i in range(8)]   # a different batch per step (some
+    # smaller than the exchange's capacity): 8 steps walk the 2 step buffers and the 3 threshold arrays several times
     return n_docs, n_terms, indptr, docids, impacts, qs
 
 
@@ -56,8 +57,9 @@ def _worker(rank, world, port, k, out_path):
         for step, (qi, qt, qw) in enumerate(qs):
             dq = (torch.from_numpy(qi.astype(np.int64)).to(dev), torch.from_numpy(qt.astype(np.int32)).to(dev),
                   torch.from_numpy(qw.astype(np.int32)).to(dev))
-            a = [t.clone() for t in px.run(idx, lambda o: idx.search(*dq, k, out=o))]
-            b = [t.clone() for t in ex.run(lambda i, l, h, o: idx.search(*dq, k, out=o))]
+            n_step = dq[0].numel() - 1
+            a = [t.clone() for t in px.run(idx, lambda o: idx.search(*dq, k, out=o), nq=n_step)]
+            b = [t[:n_step].clone() for t in ex.run(lambda i, l, h, o: idx.search(*dq, k, out=tuple(x[:n_step] for x in o)))]
             torch.cuda.synchronize()
             for x, y in zip(a, b):
                 assert torch.equal(x, y), f"rank {rank} step {step}: p2p exchange != NCCL exchange"
@@ -68,7 +70,7 @@ def _worker(rank, world, port, k, out_path):
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs with peer access")
-@pytest.mark.parametrize("k", [100])
+@pytest.mark.parametrize("k", [100, 10])
 def test_peer_exchange_two_gpus(oracle, lib_built, tmp_path, k):
     out = str(tmp_path / "px")
     mp.spawn(_worker, args=(2, _free_port(), k, out), nprocs=2, join=True)

@@ -104,23 +104,30 @@ def test_shard_keeps_global_term_filter():
 
 
 def test_peer_exchange_slot_layout_tiles_the_buffer():
-    """Host arithmetic of the fused exchange (no GPU): the (step buffer, rank) slots and their scores / docs / counts
-    sections are disjoint and tile the symmetric buffer exactly; slot strides are what msr_topk_merge_strided is given."""
-    from mllm_sparse_retrieval_b200.sharded import PeerExchange
-    for nq, k, world in ((50, 7, 4), (1, 1, 2), (64, 100, 8)):
+    """Host arithmetic of the fused exchange (no GPU): the (step buffer, rank) slots with their scores / docs / counts
+    sections, the three rotating threshold arrays and the flag words are disjoint, 16-byte aligned (the kernels store rows
+    as uint4) and inside the symmetric buffer; slot strides are what msr_topk_merge_exchange is given."""
+    from mllm_sparse_retrieval_b200.sharded import PeerExchange, peer_layout
+    for nq, k, world in ((50, 7, 4), (1, 1, 2), (64, 100, 8), (10000, 100, 8), (33, 12, 3)):
         px = object.__new__(PeerExchange)                               # layout only: no symmetric memory on this box
         px.nq, px.k, px.world = nq, k, world
-        px.slot = 2 * nq * k + nq
+        px.slot, px.theta_off, px.flag_off, total = peer_layout(nq, k, world)
         base = 4096
         regions = []
         for par in (0, 1):
             for who in range(world):
                 s, d, c = px._slot_ptrs(base, par, who)
-                assert d - s == 4 * nq * k and c - d == 4 * nq * k
+                assert s % 16 == 0 and d % 16 == 0 and c % 16 == 0
+                assert d - s >= 4 * nq * k and c - d >= 4 * nq * k
                 regions += [(s, s + 4 * nq * k), (d, d + 4 * nq * k), (c, c + 4 * nq)]
                 if who:
                     assert s - px._slot_ptrs(base, par, who - 1)[0] == 4 * px.slot      # the list stride of the merge
+        for t in range(3):
+            th = px._theta_ptr(base, t)
+            assert th % 16 == 0
+            regions.append((th, th + 8 * nq))
+        regions.append((base + 4 * px.flag_off, base + 4 * px.flag_off + 4 * world))
         regions.sort()
-        assert regions[0][0] == base and regions[-1][1] == base + 4 * 2 * world * px.slot
+        assert regions[0][0] == base and regions[-1][1] <= base + 4 * total
         for (a0, a1), (b0, b1) in zip(regions[:-1], regions[1:]):
-            assert a1 == b0                                             # no gap, no overlap
+            assert a1 <= b0                                             # no overlap
