@@ -480,6 +480,12 @@ def run_ours(a, rank, world, local_rank):
     launches = kernel_launches() - launches0
     score_ms, merge_ms, n_launch = idx.profile(False)
     clocks = sampler.stop(t_wall0, t_wall1) if rank == 0 else None
+    phases = None
+    if px is not None and px.profile:                         # MSR_PX_PROFILE=1: per-rank (search, exchange+merge) ms of the timed steps
+        ph = torch.tensor(list(px.phase_ms(a.steps)) + [score_ms / max(1, n_launch), merge_ms / max(1, n_launch)], dtype=torch.float64, device=dev)
+        allp = [torch.zeros_like(ph) for _ in range(world)]
+        dist.all_gather(allp, ph)
+        phases = [[round(float(x), 4) for x in t] for t in allp]
     v_dev, r_dev = state["last_dev"]
     last_dev = tuple(t.clone() for t in r_dev)                # the LAST timed step's rows, before anything reuses the buffers
     ms_e2e = timed(step_host, a.steps, max(1, a.warmup))
@@ -584,6 +590,7 @@ def run_ours(a, rank, world, local_rank):
                            "pinned query CSR -> msr_sparse_search(MSR_DEVICE) per shard -> NCCL all-gather -> msr_topk_merge -> "
                            "pinned host lists on rank 0")},
            "gpu_launches": int(launches), "roofline": roof, "clocks": clocks, "parity_check": check,
+           "exchange_phases_ms": {"per_rank": phases, "columns": ["search call (prep + scorer + tile merge)", "msr_topk_merge_exchange incl. wait", "scorer kernel", "tile-merge kernel"]} if phases else None,
            "query_rotation": f"{n_var} rotations of the query order, one per step in turn",
            "exchange": "single GPU" if world == 1 else ("p2p: 16-byte peer stores fused into the tile merge, barrier fused into the final merge kernel, pruning threshold shared across GPUs" if px is not None else "nccl all-gather"),
            "index": {"n_tiles": idx.n_tiles, "tile_docs": idx.tile_docs, "nnz_shard": idx.nnz, "resident_bytes": idx.resident_bytes}}

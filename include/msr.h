@@ -133,6 +133,8 @@ int msr_topk_merge(int device, uint32_t n_lists, uint32_t nq, uint32_t k_in,
  * msr_topk_merge over lists that are not packed back to back: list j starts list_stride elements after list j-1
  * (scores and docs) and count_list_stride elements (counts).  This is the layout of a symmetric-memory result buffer
  * [world][scores nq*k | docs nq*k | counts nq] that the fused exchange below fills.
+ * The lists must be sorted best-first, as every libmsr search returns its rows (the kernel drops whatever lies below the
+ * smallest of the lists' ceil(k / n_lists)-th keys before it sorts); msr_topk_merge accepts unsorted lists.
  */
 int msr_topk_merge_strided(int device, uint32_t n_lists, uint32_t nq, uint32_t k_in, const float* scores,
                            const int32_t* docs, const uint32_t* counts, size_t list_stride, size_t count_list_stride,
@@ -159,15 +161,21 @@ int msr_sparse_set_peer_outputs(msr_sparse_index* h, uint32_t n_peers, float* co
  * every GPU has finished the search that wrote into it (sharded.PeerExchange rotates three).  rot_num / rot_den: fraction
  * of the batch at which this GPU starts its walk over the queries (rank / world), so the GPUs publish different queries
  * first.  local_theta = NULL switches the sharing off.
+ * Quantile sharing (local_quant != NULL; needs n_peers + 1 == rot_den, i.e. every GPU of the group): local_quant
+ * u64[rot_den][capacity] holds, per GPU g and query, g's local r-th best key with r = ceil(k / rot_den); peer_quant[p] is
+ * the same array on peer p.  Every GPU pushes its own row to all copies.  If every GPU holds r docs at or above t the
+ * collection holds >= k, so min over g is a valid threshold -- for balanced shards close to the collection's true k-th key,
+ * which a single shard's own k-th key is not.  The tile merge drops keys below max(theta, that minimum) as well.
  */
 int msr_sparse_set_peer_theta(msr_sparse_index* h, uint32_t n_peers, uint64_t* local_theta, uint64_t* const* peer_theta,
-                              uint32_t capacity, uint32_t rot_num, uint32_t rot_den);
+                              uint32_t capacity, uint32_t rot_num, uint32_t rot_den, uint64_t* local_quant,
+                              uint64_t* const* peer_quant);
 
 /*
- * msr_topk_merge_strided with the exchange barrier fused into the kernel (replaces a separate signal-pad barrier launch):
- * the kernel first stores `flag_value` into flag_peers[p][my_rank] on every peer (release, system scope; the kernel that
- * produced this GPU's rows precedes it on `stream`), waits until flag_local[peer_ranks[p]] >= flag_value for every peer
- * (wrap-safe compare), then merges.  flag_value must grow by one per exchange step; flags are u32 in symmetric memory,
+ * msr_topk_merge_strided behind the exchange's own one-way barrier (replaces a generic two-phase signal-pad barrier):
+ * a one-warp kernel first stores `flag_value` into flag_peers[p][my_rank] on every peer (release, system scope; the kernel
+ * that produced this GPU's rows precedes it on `stream`) and waits until flag_local[peer_ranks[p]] >= flag_value for every
+ * peer (wrap-safe compare); the merge kernel follows on the stream.  flag_value must grow by one per exchange step; flags are u32 in symmetric memory,
  * zero-initialised.
  */
 int msr_topk_merge_exchange(int device, uint32_t n_lists, uint32_t nq, uint32_t k_in, const float* scores,

@@ -47,7 +47,9 @@ constexpr int kBuildWarps = 8;                 // warps per CTA of the bucket la
 int topk_merge_keys_launch(uint32_t nq, uint32_t n_lists, uint32_t stride, const uint64_t* keys,
                            const uint32_t* cnts, uint32_t k, float* out_scores, int32_t* out_docs,
                            uint32_t* out_counts, cudaStream_t s, uint32_t n_peers, float* const* peer_scores,
-                           int32_t* const* peer_docs, uint32_t* const* peer_counts, size_t peer_row0);
+                           int32_t* const* peer_docs, uint32_t* const* peer_counts, size_t peer_row0,
+                           const unsigned long long* theta, const unsigned long long* quant, uint32_t quant_world,
+                           uint32_t quant_cap);
 
 }  // namespace msr
 
@@ -86,6 +88,8 @@ struct msr_sparse_index {
     // cross-GPU threshold sharing (msr_sparse_set_peer_theta)
     unsigned long long* ext_theta = nullptr;      // this GPU's theta[] in symmetric memory (capacity ext_theta_cap queries)
     unsigned long long* peer_theta[15] = {};
+    unsigned long long* ext_quant = nullptr;      // [world][ext_theta_cap] r-th best keys of every GPU (see sparse_kernel.cuh)
+    unsigned long long* peer_quant[15] = {};
     uint32_t n_peer_theta = 0, ext_theta_cap = 0, q_rot_num = 0, q_rot_den = 1;
 };
 
@@ -653,7 +657,10 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     const bool shared_theta = where == MSR_DEVICE && h->ext_theta && h->use_theta && nq <= h->ext_theta_cap;
     P.use_theta = ((h->n_tiles > 1 || shared_theta) && h->use_theta) ? 1u : 0u;
     P.n_peer_theta = shared_theta ? h->n_peer_theta : 0u;
-    for (uint32_t p = 0; p < P.n_peer_theta; ++p) P.peer_theta[p] = h->peer_theta[p];
+    for (uint32_t p = 0; p < P.n_peer_theta; ++p) { P.peer_theta[p] = h->peer_theta[p]; P.peer_quant[p] = h->peer_quant[p]; }
+    P.quant = shared_theta ? h->ext_quant : nullptr;
+    P.quant_world = h->q_rot_den; P.quant_me = h->q_rot_num; P.quant_cap = h->ext_theta_cap;
+    P.quant_rank = P.quant ? (k + h->q_rot_den - 1) / h->q_rot_den : 0u;
     // Re-publishing costs a rank count over c + k keys; it pays while the list is still loose.  Measured (k = 100):
     // 6 tiles k/2 3.47 ms, k/4 3.63, k/8 3.68; 21 tiles 10.36 / 10.45 / 10.70; 41 tiles 19.84 (+0.5 ms final merge) / 19.78 / 19.96.
     P.merge_min = std::max(1u, k >> (h->n_tiles <= 24 ? 1 : 2));
@@ -683,7 +690,8 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
         if (evs) MSR_CUDA_CHECK(cudaEventRecord(evs[1], s));
         rc = topk_merge_keys_launch(n, h->n_tiles, k_stride, P.cand_keys, P.cand_cnt, k, d_os + (size_t)q0 * k,
                                     d_od + (size_t)q0 * k, d_oc + q0, s, where == MSR_DEVICE ? h->n_peers : 0u,
-                                    h->peer_scores, h->peer_docs, h->peer_counts, q0);
+                                    h->peer_scores, h->peer_docs, h->peer_counts, q0, P.use_theta ? P.theta : nullptr,
+                                    P.quant ? P.quant + q0 : nullptr, P.quant_world, P.quant_cap);
         if (rc) return rc;
         if (evs) MSR_CUDA_CHECK(cudaEventRecord(evs[2], s));
     }
@@ -766,11 +774,12 @@ extern "C" int msr_sparse_query_traffic(msr_sparse_index* h, uint32_t nq, const 
 }
 
 extern "C" int msr_sparse_set_peer_theta(msr_sparse_index* h, uint32_t n_peers, uint64_t* local_theta,
-                                         uint64_t* const* peer_theta, uint32_t capacity, uint32_t rot_num, uint32_t rot_den) {
+                                         uint64_t* const* peer_theta, uint32_t capacity, uint32_t rot_num, uint32_t rot_den,
+                                         uint64_t* local_quant, uint64_t* const* peer_quant) {
     MSR_REQUIRE(h, "msr_sparse_set_peer_theta: NULL handle");
     MSR_REQUIRE(n_peers <= 15, "msr_sparse_set_peer_theta: at most 15 peers");
     if (!local_theta) {                                          // switch the sharing off
-        h->ext_theta = nullptr; h->n_peer_theta = 0; h->ext_theta_cap = 0; h->q_rot_num = 0; h->q_rot_den = 1;
+        h->ext_theta = nullptr; h->ext_quant = nullptr; h->n_peer_theta = 0; h->ext_theta_cap = 0; h->q_rot_num = 0; h->q_rot_den = 1;
         return MSR_OK;
     }
     MSR_REQUIRE(capacity > 0 && rot_den > 0 && rot_num < rot_den, "msr_sparse_set_peer_theta: bad capacity / rotation");
@@ -778,7 +787,11 @@ extern "C" int msr_sparse_set_peer_theta(msr_sparse_index* h, uint32_t n_peers, 
     for (uint32_t p = 0; p < n_peers; ++p) {
         MSR_REQUIRE(peer_theta[p], "msr_sparse_set_peer_theta: NULL peer pointer %u", p);
         h->peer_theta[p] = (unsigned long long*)peer_theta[p];
+        MSR_REQUIRE(!local_quant || (peer_quant && peer_quant[p]), "msr_sparse_set_peer_theta: NULL peer quantile pointer %u", p);
+        h->peer_quant[p] = local_quant ? (unsigned long long*)peer_quant[p] : nullptr;
     }
+    MSR_REQUIRE(!local_quant || n_peers + 1 == rot_den, "msr_sparse_set_peer_theta: quantile sharing needs every GPU of the group as a peer");
+    h->ext_quant = (unsigned long long*)local_quant;
     h->ext_theta = (unsigned long long*)local_theta; h->n_peer_theta = n_peers; h->ext_theta_cap = capacity;
     h->q_rot_num = rot_num; h->q_rot_den = rot_den;
     return MSR_OK;

@@ -69,7 +69,34 @@ struct SearchParams {
     uint32_t q_rot;               // the grid walks the queries from this offset (a different one per GPU), so the GPUs
                                   // publish different queries first and find each other's thresholds already there
     unsigned long long* peer_theta[15];
+    // Quantile sharing: a GPU's local k-th key says little about the collection's k-th (the top k are spread over the
+    // shards).  Every GPU therefore also publishes, per query, its local r-th best key with r = ceil(k / world)
+    // (quant[g][q], pushed to all GPUs like theta).  If every GPU holds r docs at or above t, the collection holds
+    // world * r >= k: min over g of quant[g][q] is a valid -- and for balanced shards nearly exact -- threshold.
+    unsigned long long* quant;    // [quant_world][quant_cap] on this GPU (NULL = off)
+    unsigned long long* peer_quant[15];
+    uint32_t quant_world, quant_me, quant_cap, quant_rank;
 };
+
+// this GPU's r-th best key of query q went up: tell everyone (quant[me][q] on every GPU)
+__device__ __forceinline__ void quant_raise(const SearchParams& P, uint32_t q, unsigned long long key) {
+    if (!P.quant) return;
+    const size_t i = (size_t)P.quant_me * P.quant_cap + P.q_lo + q;
+    atomicMax(P.quant + i, key);
+    for (uint32_t p = 0; p < P.n_peer_theta; ++p)
+        asm volatile("red.relaxed.sys.global.max.u64 [%0], %1;" ::"l"(P.peer_quant[p] + i), "l"(key) : "memory");
+}
+// the threshold a CTA starts from: the shared theta, or the smallest of the GPUs' r-th keys when that is larger
+__device__ __forceinline__ unsigned long long theta_read(const SearchParams& P, uint32_t q) {
+    unsigned long long t = *(volatile unsigned long long*)(P.theta + q);
+    if (P.quant) {
+        unsigned long long m = ~0ull;
+        for (uint32_t g = 0; g < P.quant_world; ++g)
+            m = min(m, *(volatile unsigned long long*)(P.quant + (size_t)g * P.quant_cap + P.q_lo + q));
+        t = max(t, m);
+    }
+    return t;
+}
 
 // raise the query's threshold here and on every peer GPU
 __device__ __forceinline__ void theta_raise(const SearchParams& P, unsigned long long* theta_p, uint32_t q, unsigned long long key) {
@@ -477,7 +504,7 @@ sparse_score_topk_kernel(const SearchParams P) {
     // The threshold is read ONCE per CTA and broadcast: theta rises while other tiles of the query publish, and
     // threads reading it on their own could disagree -- some still seeing 0 (exact select, with its barriers)
     // while others already take the threshold path.
-    if (tid == 0) S->theta = P.use_theta ? *(volatile unsigned long long*)(P.theta + q) : 0ull;
+    if (tid == 0) S->theta = P.use_theta ? theta_read(P, q) : 0ull;
     __syncthreads();
 
     // ---- phase 2: candidates of the tile by (float32(score) desc, doc asc) ----
@@ -538,6 +565,7 @@ sparse_score_topk_kernel(const SearchParams P) {
                     if (mine && gt < P.k) {
                         tlist[gt] = mine;
                         if (gt == P.k - 1) theta_raise(P, theta_p, q, (unsigned long long)mine);
+                        if (gt == P.quant_rank - 1) quant_raise(P, q, (unsigned long long)mine);
                     }
                     return;
                 }
@@ -565,6 +593,7 @@ sparse_score_topk_kernel(const SearchParams P) {
                     if (ex < P.k) {
                         tlist[ex] = e[j];
                         if (ex == P.k - 1) theta_raise(P, theta_p, q, (unsigned long long)e[j]);
+                        if (ex == P.quant_rank - 1) quant_raise(P, q, (unsigned long long)e[j]);
                     }
                     ++ex;
                 }
@@ -647,6 +676,7 @@ sparse_score_topk_kernel(const SearchParams P) {
                         if (P.use_theta) {
                             tlist[gt] = mine;
                             if (gt == P.k - 1) theta_raise(P, theta_p, q, (unsigned long long)mine);
+                            if (gt == P.quant_rank - 1) quant_raise(P, q, (unsigned long long)mine);
                         }
                     }
                 }

@@ -90,13 +90,16 @@ class SparseIndex:
         arr = lambda xs: (ctypes.c_void_p * max(1, n))(*[ctypes.c_void_p(int(x)) for x in xs])
         check(_lib.load().msr_sparse_set_peer_outputs(self._h, n, arr(peer_scores), arr(peer_docs), arr(peer_counts)))
 
-    def set_peer_theta(self, local_theta=0, peer_theta=(), capacity=0, rank=0, world=1):
+    def set_peer_theta(self, local_theta=0, peer_theta=(), capacity=0, rank=0, world=1, local_quant=0, peer_quant=()):
         """Cross-GPU threshold sharing (msr_sparse_set_peer_theta): raw device addresses of this GPU's u64[capacity]
-        threshold array in symmetric memory and of the peers' copies; ``local_theta=0`` switches it off."""
+        threshold array in symmetric memory and of the peers' copies, optionally with the u64[world][capacity] quantile
+        arrays; ``local_theta=0`` switches it off."""
         n = len(peer_theta)
         arr = (ctypes.c_void_p * max(1, n))(*[ctypes.c_void_p(int(x)) for x in peer_theta])
+        qarr = (ctypes.c_void_p * max(1, n))(*[ctypes.c_void_p(int(x)) for x in peer_quant]) if local_quant else None
         check(_lib.load().msr_sparse_set_peer_theta(self._h, n, ctypes.c_void_p(int(local_theta)) if local_theta else None, arr,
-                                                    int(capacity), int(rank), int(max(1, world))))
+                                                    int(capacity), int(rank), int(max(1, world)),
+                                                    ctypes.c_void_p(int(local_quant)) if local_quant else None, qarr))
 
     def status(self):
         """Synchronise and raise MsrError(MSR_ERR_RANGE) if an earlier device-path search left the exact range."""

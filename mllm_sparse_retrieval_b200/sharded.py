@@ -19,6 +19,8 @@ smaller scorer launches lose about as much as the overlap wins (2 GPUs: 668 K QP
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -80,12 +82,12 @@ class PipelinedExchange:
 
 def peer_layout(nq, k, world):
     """Symmetric buffer of ``PeerExchange`` in 4-byte units (every section starts on a 16-byte boundary):
-    2 step buffers x world slots of [scores nq*k | docs nq*k | counts nq(+pad)], then 3 threshold arrays of nq u64, then
-    world flags.  Returns (slot, theta_off, flag_off, total)."""
+    2 step buffers x world slots of [scores nq*k | docs nq*k | counts nq(+pad)], then 3 rotating threshold regions of
+    [theta u64[nq] | quantiles u64[world][nq]], then world flags.  Returns (slot, theta_off, flag_off, total)."""
     al = lambda x: (x + 3) // 4 * 4
     slot = 2 * al(nq * k) + al(nq)
     theta_off = 2 * world * slot
-    flag_off = theta_off + 3 * al(2 * nq)
+    flag_off = theta_off + 3 * al(2 * nq * (1 + world))
     return slot, theta_off, flag_off, flag_off + al(world)
 
 
@@ -98,8 +100,10 @@ class PeerExchange:
     merges step n; a rank can only reach step n+2 after every peer has signalled step n+1, i.e. finished merging step n.
 
     The scorer's pruning threshold is shared the same way (``msr_sparse_set_peer_theta``): theta[q] lives in the symmetric
-    buffer and every raise is pushed to all peers, so a shard with 6 tiles prunes like one with 41.  Three threshold
-    arrays rotate (step n uses n % 3 and clears (n + 2) % 3), so a peer that is one step ahead never has its pushes
+    buffer and every raise is pushed to all peers, and so is every GPU's local ceil(k/world)-th best key per query -- the
+    smallest of those over the GPUs bounds the collection's k-th key far better than any shard's own k-th key does -- so a
+    shard with 6 tiles prunes like one with 41 and hands over short lists.  Three threshold
+    regions rotate (step n uses n % 3 and clears (n + 2) % 3), so a peer that is one step ahead never has its pushes
     wiped, and no array is reused before every rank has finished with it.
 
     Raises (RuntimeError / ImportError) when symmetric memory cannot be set up; callers fall back to
@@ -118,8 +122,11 @@ class PeerExchange:
                       torch.empty((nq, k), dtype=torch.int32, device=self.device),
                       torch.empty((nq,), dtype=torch.int32, device=self.device))
         self.step = 0
-        self.share_theta = share_theta
+        self.share_theta = share_theta and os.environ.get("MSR_SPARSE_NO_PEER_THETA") != "1"   # developer knobs (A/B runs)
+        self.share_quant = self.share_theta and os.environ.get("MSR_SPARSE_NO_PEER_QUANT") != "1"
         self.peers = [r for r in range(world) if r != rank]
+        self.profile = os.environ.get("MSR_PX_PROFILE") == "1"         # CUDA events around the two halves of a step
+        self._ev = []
         torch.cuda.synchronize(self.device)
         self.hdl.barrier(channel=0)                                     # every rank's buffer is zeroed before anyone writes
 
@@ -129,7 +136,8 @@ class PeerExchange:
         return b, b + 4 * al(self.nq * self.k), b + 8 * al(self.nq * self.k)
 
     def _theta_ptr(self, base, which):
-        return base + 4 * (self.theta_off + which * ((2 * self.nq + 3) // 4 * 4))
+        """address of rotating threshold region ``which`` (theta[nq], then quant[world][nq] 8 * nq bytes further on)"""
+        return base + 4 * (self.theta_off + which * ((2 * self.nq * (1 + self.world) + 3) // 4 * 4))
 
     def run(self, index, search, nq=None):
         """search(out_views) runs ONE device-path search of the whole batch on ``index`` (a ``SparseIndex``) writing
@@ -146,11 +154,17 @@ class PeerExchange:
         index.set_peer_outputs([p[0] for p in peers], [p[1] for p in peers], [p[2] for p in peers])
         if self.share_theta:
             # the array two steps ahead is cleared now: nobody can be writing it yet, and nobody will read it before
-            tw = al(2 * self.nq)
+            tw = al(2 * self.nq * (1 + self.world))
             o = self.theta_off + t_clear * tw
             self.buf[o:o + tw].zero_()
-            index.set_peer_theta(self._theta_ptr(self.ptrs[self.rank], t_now), [self._theta_ptr(self.ptrs[r], t_now) for r in self.peers],
-                                 self.nq, self.rank, self.world)
+            mine = self._theta_ptr(self.ptrs[self.rank], t_now)
+            theirs = [self._theta_ptr(self.ptrs[r], t_now) for r in self.peers]
+            index.set_peer_theta(mine, theirs, self.nq, self.rank, self.world,
+                                 local_quant=mine + 8 * self.nq if self.share_quant else 0, peer_quant=[t + 8 * self.nq for t in theirs])
+        if self.profile:
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            self._ev.append(ev)
+            ev[0].record()
         try:
             # the local slot is the search's own output: views into the symmetric buffer
             o = self.slot * (par * self.world + self.rank)
@@ -165,10 +179,23 @@ class PeerExchange:
                 index.set_peer_theta()
         s0, d0, c0 = self._slot_ptrs(self.ptrs[self.rank], par, 0)
         final = self.final if nq == self.nq else tuple(t[:nq] for t in self.final)
+        if self.profile:
+            self._ev[-1][1].record()
         ops.topk_merge_exchange(s0, d0, c0, self.world, nq, self.k, self.slot, self.slot, self.k, final, self.device,
                                 self.rank, self.ptrs[self.rank] + 4 * self.flag_off,
                                 [self.ptrs[r] + 4 * self.flag_off for r in self.peers], self.peers, self.step)
+        if self.profile:
+            self._ev[-1][2].record()
         return final
+
+    def phase_ms(self, last=None):
+        """(search ms, exchange-merge ms incl. the wait for the slowest peer) averaged over the last ``last`` profiled steps."""
+        torch.cuda.synchronize(self.device)
+        ev = self._ev[-last:] if last else self._ev
+        self._ev = []
+        if not ev:
+            return 0.0, 0.0
+        return (sum(e[0].elapsed_time(e[1]) for e in ev) / len(ev), sum(e[1].elapsed_time(e[2]) for e in ev) / len(ev))
 
 
 def make_peer_exchange(nq, k, device, world, rank, kind="auto", group=None):

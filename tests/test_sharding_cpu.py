@@ -125,7 +125,7 @@ def test_peer_exchange_slot_layout_tiles_the_buffer():
         for t in range(3):
             th = px._theta_ptr(base, t)
             assert th % 16 == 0
-            regions.append((th, th + 8 * nq))
+            regions.append((th, th + 8 * nq * (1 + world)))
         regions.append((base + 4 * px.flag_off, base + 4 * px.flag_off + 4 * world))
         regions.sort()
         assert regions[0][0] == base and regions[-1][1] <= base + 4 * total
