@@ -84,9 +84,11 @@ int msr_sparse_index_info(const msr_sparse_index* h, uint32_t info[9]);
  * over kept terms (S5); hits are docs with score > 0 (S7), ordered by score desc, internal id asc (S8).
  * Outputs are [nq,k] row-major: row q = out_counts[q] hits then padding (score 0, doc -1).  out_docs are
  * GLOBAL internal ids (doc_base added).
- * Exact-arithmetic range: every weight <= 65535 and sum_t w_t*max_impact(t) < 2^31 per query, otherwise the
- * query's row is returned empty and the call reports MSR_ERR_RANGE (MSR_HOST) or sets the sticky status
- * readable with msr_sparse_index_status (MSR_DEVICE).  k <= MSR_MAX_K.
+ * Range: the integer kernel is exact while every weight <= 65535 and sum_t w_t*max_impact(t) < 2^31.  A query beyond that
+ * is scored by the WIDE path instead (u64 accumulators; rule S6 reproduced exactly, scores may exceed 2^31 as Lucene's
+ * float32 scores would), on launches the batch makes anyway.  MSR_HOST handles any number of such queries; MSR_DEVICE is
+ * asynchronous and takes one wide pass of 8 queries per call -- if a batch holds more, the first 8 are scored, the others'
+ * rows stay empty and the sticky status (msr_sparse_index_status) reports MSR_ERR_RANGE.  k <= MSR_MAX_K.
  */
 int msr_sparse_search(msr_sparse_index* h, uint32_t nq,
                       const uint64_t* q_indptr, const uint32_t* q_terms, const uint32_t* q_weights,

@@ -49,7 +49,9 @@ int topk_merge_keys_launch(uint32_t nq, uint32_t n_lists, uint32_t stride, const
                            uint32_t* out_counts, cudaStream_t s, uint32_t n_peers, float* const* peer_scores,
                            int32_t* const* peer_docs, uint32_t* const* peer_counts, size_t peer_row0,
                            const unsigned long long* theta, const unsigned long long* quant, uint32_t quant_world,
-                           uint32_t quant_cap);
+                           uint32_t quant_cap, uint32_t wide_ctas, uint32_t wide_first, const uint32_t* wide_q,
+                           const uint32_t* n_wide, const uint64_t* wide_keys, const uint32_t* wide_cnt, uint32_t wide_n_lists,
+                           uint32_t wide_stride);
 
 }  // namespace msr
 
@@ -575,8 +577,10 @@ extern "C" int msr_sparse_index_status(msr_sparse_index* h, void* stream) {
     MSR_CUDA_CHECK(cudaMemsetAsync(h->status, 0, 4, s));
     MSR_CUDA_CHECK(cudaStreamSynchronize(s));
     if (st) {
-        set_error("msr_sparse_search: a query left the exact-arithmetic range (weight > 65535 or "
-                  "sum_t w_t*max_impact(t) >= 2^31); its row was returned empty");
+        set_error("msr_sparse_search (device path): more than %u queries of one batch lie outside the integer kernel's exact range "
+                  "(weight > 65535 or sum_t w_t*max_impact(t) >= 2^31) and need the wide path; the first %u were scored, the rows of "
+                  "the others are empty -- split the batch or use the host path, which runs as many passes as it takes",
+                  kWideMax, kWideMax);
         return MSR_ERR_RANGE;
     }
     return MSR_OK;
@@ -610,7 +614,12 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     size_t off_ok = align_up(off_cnt + (size_t)qc * h->n_tiles * 4, 256);
     size_t off_theta = align_up(off_ok + nq, 256);
     size_t off_tlist = align_up(off_theta + (size_t)qc * 8, 256);
-    size_t off_end = align_up(off_tlist + (size_t)qc * k * 8, 256);
+    // wide path (queries outside the exact integer range): list of such queries, their count, kWideMax key arrays
+    size_t off_wq = align_up(off_tlist + (size_t)qc * k * 8, 256);
+    size_t off_nw = align_up(off_wq + (size_t)nq * 4, 256);
+    size_t off_wkeys = align_up(off_nw + 4, 256);
+    size_t off_wcnt = align_up(off_wkeys + (size_t)kWideMax * h->n_tiles * h->tile_docs * 8, 256);
+    size_t off_end = align_up(off_wcnt + (size_t)kWideMax * h->n_tiles * 4, 256);
     size_t off_qi = off_end, off_qt = 0, off_qw = 0, off_os = 0, off_od = 0, off_oc = 0;
     if (where == MSR_HOST) {
         MSR_REQUIRE(nnz_q == 0 || (q_terms && q_weights), "msr_sparse_search: NULL query arrays");
@@ -640,7 +649,10 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     }
 
     uint8_t* d_ok = (uint8_t*)(base + off_ok);
-    query_prep_kernel<<<(nq + 7) / 8, 256, 0, s>>>(h->term_keep, h->term_maximp, h->n_terms, nq, d_qi, d_qt, d_qw, d_ok, h->status);
+    uint32_t* d_wq = (uint32_t*)(base + off_wq);
+    uint32_t* d_nw = (uint32_t*)(base + off_nw);
+    MSR_CUDA_CHECK(cudaMemsetAsync(d_nw, 0, 4, s));
+    query_prep_kernel<<<(nq + 7) / 8, 256, 0, s>>>(h->term_keep, h->term_maximp, h->n_terms, nq, d_qi, d_qt, d_qw, d_ok, d_wq, d_nw);
     count_launch();
     MSR_CUDA_CHECK(cudaGetLastError());
 
@@ -666,6 +678,8 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     P.merge_min = std::max(1u, k >> (h->n_tiles <= 24 ? 1 : 2));
     if (const char* e = getenv("MSR_SPARSE_MERGE_SHIFT")) P.merge_min = std::max(1u, k >> (uint32_t)std::min(10, std::max(0, atoi(e))));
     P.fast_select = h->fast_select ? 1u : 0u;
+    P.wide_q = d_wq; P.n_wide = d_nw; P.wide_first = 0; P.wide_ctas = 0; P.status = h->status;
+    P.wide_acc = (unsigned long long*)(base + off_wkeys); P.wide_cnt = (uint32_t*)(base + off_wcnt);
     const size_t smem = search_smem_bytes(h->tile_docs);
     for (uint32_t q0 = 0; q0 < nq; q0 += qc) {
         const uint32_t n = std::min(qc, nq - q0);
@@ -684,18 +698,38 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
         if (P.use_theta)      // theta[] and tlist[] are contiguous up to alignment: one clear
             MSR_CUDA_CHECK(cudaMemsetAsync(base + off_theta, 0, off_tlist - off_theta + (size_t)n * k * 8, s));
         static_assert(sizeof(SearchParams) <= 4000, "kernel parameter space");
-        sparse_score_topk_kernel<<<n * h->n_tiles, kThreads, smem, s>>>(P);
+        // the batch's last launch carries the wide path as extra CTAs at the end of the grid (they leave at once when the
+        // prep kernel listed no query); the merge launch below carries the matching extra CTAs
+        const bool last = q0 + n >= nq;
+        P.wide_ctas = last ? kWideMax : 0u;
+        sparse_score_topk_kernel<<<(n + P.wide_ctas) * h->n_tiles, kThreads, smem, s>>>(P);
         count_launch();
         MSR_CUDA_CHECK(cudaGetLastError());
         if (evs) MSR_CUDA_CHECK(cudaEventRecord(evs[1], s));
         rc = topk_merge_keys_launch(n, h->n_tiles, k_stride, P.cand_keys, P.cand_cnt, k, d_os + (size_t)q0 * k,
                                     d_od + (size_t)q0 * k, d_oc + q0, s, where == MSR_DEVICE ? h->n_peers : 0u,
                                     h->peer_scores, h->peer_docs, h->peer_counts, q0, P.use_theta ? P.theta : nullptr,
-                                    P.quant ? P.quant + q0 : nullptr, P.quant_world, P.quant_cap);
+                                    P.quant ? P.quant + q0 : nullptr, P.quant_world, P.quant_cap,
+                                    P.wide_ctas, 0u, d_wq, d_nw, (const uint64_t*)P.wide_acc, P.wide_cnt, h->n_tiles, h->tile_docs);
         if (rc) return rc;
         if (evs) MSR_CUDA_CHECK(cudaEventRecord(evs[2], s));
     }
     if (where == MSR_HOST) {
+        // more than kWideMax queries needed the wide path: the host path knows (it synchronises anyway) and runs the rest
+        uint32_t n_wide = 0;
+        MSR_CUDA_CHECK(cudaMemcpyAsync(&n_wide, d_nw, 4, cudaMemcpyDeviceToHost, s));
+        MSR_CUDA_CHECK(cudaStreamSynchronize(s));
+        for (uint32_t first = kWideMax; first < n_wide; first += kWideMax) {
+            P.q_lo = 0; P.nq = 0; P.wide_first = first; P.wide_ctas = kWideMax;
+            sparse_score_topk_kernel<<<kWideMax * h->n_tiles, kThreads, smem, s>>>(P);
+            count_launch();
+            MSR_CUDA_CHECK(cudaGetLastError());
+            rc = topk_merge_keys_launch(0, h->n_tiles, k_stride, P.cand_keys, P.cand_cnt, k, d_os, d_od, d_oc, s, 0u, h->peer_scores,
+                                        h->peer_docs, h->peer_counts, 0, nullptr, nullptr, 0, 0, kWideMax, first, d_wq, d_nw,
+                                        (const uint64_t*)P.wide_acc, P.wide_cnt, h->n_tiles, h->tile_docs);
+            if (rc) return rc;
+        }
+        if (n_wide > kWideMax) MSR_CUDA_CHECK(cudaMemsetAsync(h->status, 0, 4, s));     // all of them were scored after all
         MSR_CUDA_CHECK(cudaMemcpyAsync(out_scores, d_os, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, s));
         MSR_CUDA_CHECK(cudaMemcpyAsync(out_docs, d_od, (size_t)nq * k * 4, cudaMemcpyDeviceToHost, s));
         MSR_CUDA_CHECK(cudaMemcpyAsync(out_counts, d_oc, (size_t)nq * 4, cudaMemcpyDeviceToHost, s));

@@ -73,6 +73,13 @@ struct SearchParams {
     // shards).  Every GPU therefore also publishes, per query, its local r-th best key with r = ceil(k / world)
     // (quant[g][q], pushed to all GPUs like theta).  If every GPU holds r docs at or above t, the collection holds
     // world * r >= k: min over g of quant[g][q] is a valid -- and for balanced shards nearly exact -- threshold.
+    // wide path (see wide_score_cta): the last wide_ctas CTAs of the grid score the queries the prep kernel listed
+    const uint32_t* wide_q;       // [nq_total] queries outside the exact integer range, in any order
+    const uint32_t* n_wide;       // how many
+    uint32_t wide_first, wide_ctas;
+    unsigned long long* wide_acc; // [kWideMax][n_tiles][tile_docs] accumulators, then ranking keys
+    uint32_t* wide_cnt;           // [kWideMax][n_tiles] keys per (query, tile) for the merge kernel
+    uint32_t* status;
     unsigned long long* quant;    // [quant_world][quant_cap] on this GPU (NULL = off)
     unsigned long long* peer_quant[15];
     uint32_t quant_world, quant_me, quant_cap, quant_rank;
@@ -109,7 +116,7 @@ __device__ __forceinline__ void theta_raise(const SearchParams& P, unsigned long
 __global__ void query_prep_kernel(const uint8_t* __restrict__ keep, const uint32_t* __restrict__ maximp, uint32_t n_terms,
                                   uint32_t nq, const uint64_t* __restrict__ q_indptr, const uint32_t* __restrict__ q_terms,
                                   const uint32_t* __restrict__ q_weights, uint8_t* __restrict__ q_ok,
-                                  uint32_t* __restrict__ status) {
+                                  uint32_t* __restrict__ wide_q, uint32_t* __restrict__ n_wide) {
     const uint32_t q = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
     if (q >= nq) return;
     const uint64_t qs = q_indptr[q], qe = q_indptr[q + 1];
@@ -130,8 +137,60 @@ __global__ void query_prep_kernel(const uint8_t* __restrict__ keep, const uint32
     if (lane == 0) {
         const bool ok = bound < (1ull << 31) && wmax <= 65535u;
         q_ok[q] = ok ? 1 : 0;
-        if (!ok) atomicOr(status, 1u);
+        if (!ok) wide_q[atomicAdd(n_wide, 1u)] = q;            // scored by wide_score_kernel instead (any order)
     }
+}
+
+// Wide path: a query outside the integer kernel's exact range (sum_t w_t * max_impact(t) >= 2^31, or a weight above
+// 65535) is scored here instead, one CTA per (such query, tile), with u64 accumulators in global memory.  Rule S6 --
+// float32(sum of float32(w * tf)), the sum taken in double -- is reproduced exactly: every product is rounded to float32
+// first and is an integer below 2^48, so the u64 sum equals the double sum and one round-to-nearest cast ends it.
+// Terms are applied one after the other (postings of one term hit distinct docs: no atomics).  The accumulators are then
+// turned into ranking keys in place (0 = no hit) and extra CTAs of the merge kernel select the top k out of them and store
+// the row where the query belongs.  Both ride on launches that happen anyway: a batch without such queries pays nothing.
+constexpr uint32_t kWideMax = 8;          // queries per wide pass (the key buffer is kWideMax * n_docs * 8 bytes)
+
+__device__ __forceinline__ void wide_score_cta(const SearchParams& P, uint32_t w, uint32_t tile) {
+    const uint32_t tid = threadIdx.x;
+    const uint32_t nw = *P.n_wide;
+    if (P.wide_first + w >= nw) {
+        if (tid == 0) P.wide_cnt[w * P.n_tiles + tile] = 0;
+        return;
+    }
+    // more flagged queries than one pass takes: the host path runs further passes, the device path reports it (status)
+    if (w == 0 && tile == 0 && tid == 0 && P.wide_first == 0 && nw > kWideMax) atomicOr(P.status, 2u);
+    const uint32_t q = P.wide_q[P.wide_first + w];
+    const uint32_t tile_lo = tile * P.tile_docs, tl = min(P.tile_docs, P.n_docs - tile_lo);
+    unsigned long long* acc = P.wide_acc + ((size_t)w * P.n_tiles + tile) * P.tile_docs;
+    for (uint32_t d = tid; d < tl; d += blockDim.x) acc[d] = 0ull;
+    __syncthreads();
+    const uint32_t* seg_row = P.seg_ptr + (size_t)tile * P.n_terms;
+    for (uint64_t j = P.q_indptr[q]; j < P.q_indptr[q + 1]; ++j) {
+        const uint32_t t = P.q_terms[j], wt = P.q_weights[j];
+        if (t >= P.n_terms || wt == 0 || !P.term_keep[t]) continue;         // uniform over the CTA
+        const float wf = __uint2float_rn(wt);
+        const uint32_t di = P.dense_id[t];
+        if (di != kNotDense) {
+            const uint16_t* row = P.dense_rows + (size_t)di * P.dense_stride + tile_lo;     // the whole impact
+            for (uint32_t d = tid; d < tl; d += blockDim.x) {
+                const uint32_t imp = row[d];
+                if (imp) acc[d] += (unsigned long long)__fmul_rn(wf, __uint2float_rn(imp));
+            }
+        } else {
+            const uint32_t s0 = seg_row[t], s1 = seg_row[t + 1];
+            for (uint32_t p = s0 + tid; p < s1; p += blockDim.x) {
+                const uint32_t v = P.postings[p], imp = v >> 16;               // padding slots carry impact 0
+                if (imp) acc[v & 0xFFFFu] += (unsigned long long)__fmul_rn(wf, __uint2float_rn(imp));
+            }
+        }
+        __syncthreads();
+    }
+    const uint32_t gdoc0 = (uint32_t)P.doc_base + tile_lo;
+    for (uint32_t d = tid; d < tl; d += blockDim.x) {
+        const unsigned long long a = acc[d];
+        acc[d] = a ? make_key(__ull2float_rn(a), gdoc0 + d) : 0ull;
+    }
+    if (tid == 0) P.wide_cnt[w * P.n_tiles + tile] = tl;
 }
 
 __device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t* p) {
@@ -287,6 +346,11 @@ sparse_score_topk_kernel(const SearchParams P) {
     const uint32_t acc_s = (uint32_t)__cvta_generic_to_shared(acc);
 
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    if (blockIdx.x >= P.nq * P.n_tiles) {                       // the grid's tail: wide path
+        const uint32_t x = blockIdx.x - P.nq * P.n_tiles;
+        wide_score_cta(P, x / P.n_tiles, x % P.n_tiles);
+        return;
+    }
     uint32_t q = blockIdx.x % P.nq + P.q_rot;
     if (q >= P.nq) q -= P.nq;
     const uint32_t tile = blockIdx.x / P.nq;
@@ -297,7 +361,7 @@ sparse_score_topk_kernel(const SearchParams P) {
     uint64_t* keys_out = P.cand_keys + ((size_t)q * P.n_tiles + tile) * P.k_stride;
     uint32_t* cnt_out = P.cand_cnt + (size_t)q * P.n_tiles + tile;
 
-    if (!P.q_ok[P.q_lo + q]) {                                  // outside the exact range: empty row (see msr.h)
+    if (!P.q_ok[P.q_lo + q]) {                                  // outside the exact range: wide_score_kernel fills the row
         if (tid == 0) *cnt_out = 0;
         return;
     }

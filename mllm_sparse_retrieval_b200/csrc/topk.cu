@@ -43,6 +43,15 @@ struct MergeParams {
     // lists' r-th keys has at least k keys at or above it, so everything below is dropped before the sort.  For doc-sharded
     // lists of balanced shards that leaves little more than k of the n_lists * k keys.
     uint32_t sorted_lists;
+    // wide path of the sparse search (sparse_kernel.cuh, wide_score_cta): wide_ctas extra CTAs at the end of the grid merge
+    // the per-tile KEY ARRAYS of the queries scored there (lists of tile_docs keys, 0 = no hit) and store each row at its
+    // query's place in the batch (row = wide_q[...] - wide_row0 relative to out_* / peer_*).
+    uint32_t wide_ctas, wide_first, wide_n_lists, wide_stride;
+    const uint32_t* wide_q;
+    const uint32_t* n_wide;
+    const uint64_t* wide_keys;
+    const uint32_t* wide_cnt;
+    long long wide_row0;
     uint32_t vec_ok;                         // set by merge_launch: k % 4 == 0 and every output row base is 16-byte aligned
     uint32_t* flag_local;                    // [world] written by the peers
     uint32_t* flag_peers[kMaxPeers];         // the peers' flag arrays
@@ -92,13 +101,10 @@ __device__ __forceinline__ uint64_t merge_key_at(const MergeParams& P, uint32_t 
 // the shared buffer, one bitonic sort.  Otherwise (small batches, deep k: every tile delivers a full list) the k-th largest
 // key is located by an MSB-first radix select over the lists where they lie (8-bit digits; the lists stay in L2), and only
 // the keys at or above it are gathered and sorted -- 41 lists x 1000 keys took 600 us by repeated sorting, ~30 us this way.
-__global__ void __launch_bounds__(1024)
-topk_merge_kernel(const MergeParams P) {
-    extern __shared__ __align__(16) unsigned char smem_raw[];
-    uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
-    const uint32_t q = blockIdx.x, tid = threadIdx.x, nthr = blockDim.x;
+__device__ __forceinline__ void merge_body(const MergeParams& P, const uint32_t q, const long long orow, uint64_t* buf) {
+    const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     uint32_t fill = 0;
-    __shared__ uint32_t s_total, s_fill, s_hist[256], s_sel[3];
+    __shared__ uint32_t s_total, s_fill, s_hist[256], s_sel[4];
     __shared__ unsigned long long s_floor;
     if (tid == 0) {
         s_total = 0; s_fill = 0;
@@ -192,7 +198,7 @@ topk_merge_kernel(const MergeParams P) {
     } else {
         // radix select of the k-th largest key (keys of real hits are distinct and non-zero)
         const uint32_t n_slots = P.n_lists * P.stride;
-        uint32_t need = P.k;                                    // total > cap >= 2k, so k keys exist
+        uint32_t need = P.k, k_sel = P.k;                       // total > cap >= 2k slots, but some may hold no key (see pass 0)
         uint64_t prefix = 0;                                    // the digits fixed so far (top 8 * pass bits)
         uint32_t pass = 0;
         for (;; ++pass) {
@@ -208,8 +214,13 @@ topk_merge_kernel(const MergeParams P) {
                 uint32_t h[8], sum = 0;
 #pragma unroll
                 for (int i = 0; i < 8; ++i) { h[i] = s_hist[255 - 8 * tid - i]; sum += h[i]; }
-                uint32_t before = warp_incl_scan(sum, tid) - sum;        // keys in higher bins
-                if (before < need && before + sum >= need) {
+                const uint32_t incl = warp_incl_scan(sum, tid);
+                uint32_t before = incl - sum;                            // keys in higher bins
+                // fewer real keys than asked for (key arrays of the wide path hold a 0 for every doc without a hit): take all
+                const uint32_t have = __shfl_sync(0xffffffffu, incl, 31);
+                if (pass == 0) need = min(need, have);
+                if (tid == 0) { s_sel[3] = need; if (need == 0) { s_sel[0] = 0; s_sel[1] = 0; s_sel[2] = 0; } }
+                if (need && before < need && before + sum >= need) {
 #pragma unroll
                     for (int i = 0; i < 8; ++i) {
                         if (before < need && before + h[i] >= need) { s_sel[0] = 255 - 8 * tid - i; s_sel[1] = before; s_sel[2] = h[i]; }
@@ -218,10 +229,12 @@ topk_merge_kernel(const MergeParams P) {
                 }
             }
             __syncthreads();
+            if (pass == 0) { need = s_sel[3]; k_sel = need; }
+            if (need == 0) break;
             const uint32_t bin = s_sel[0], greater = s_sel[1], cnt = s_sel[2];
             prefix = (prefix << 8) | bin;
             // keys above the bin are certain; stop as soon as they and the bin's keys fit the buffer together
-            if ((P.k - need) + greater + cnt <= P.cap || pass == 7) break;
+            if ((k_sel - need) + greater + cnt <= P.cap || pass == 7) break;
             need -= greater;
             __syncthreads();
         }
@@ -243,7 +256,13 @@ topk_merge_kernel(const MergeParams P) {
     } else {
         __syncthreads();
     }
-    const uint32_t n = min(fill, P.k);
+    // keys are sorted best-first; zero keys (pruned slots, docs without a hit in a wide-path key array) sort to the end
+    uint32_t n = min(fill, P.k);
+    {
+        uint32_t lo = 0, hi = n;                               // first zero in buf[0, n)
+        while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if (buf[mid]) lo = mid + 1; else hi = mid; }
+        n = lo;
+    }
     if (P.n_peers && P.vec_ok) {
         // rows leave as 16-byte stores: keys -> (score, doc) in place, then one uint4 per 4 ranks and destination
         __syncthreads();
@@ -262,7 +281,7 @@ topk_merge_kernel(const MergeParams P) {
             const uint4 x = make_uint4(src[0], src[2], src[4], src[6]);
             void* base = what ? (dst ? (void*)P.peer_docs[dst - 1] : (void*)P.out_docs)
                               : (dst ? (void*)P.peer_scores[dst - 1] : (void*)P.out_scores);
-            reinterpret_cast<uint4*>(reinterpret_cast<uint32_t*>(base) + (size_t)q * P.k)[v] = x;
+            reinterpret_cast<uint4*>(reinterpret_cast<uint32_t*>(base) + orow * P.k)[v] = x;
         }
     } else {
         for (uint32_t r = tid; r < P.k; r += nthr) {
@@ -270,18 +289,35 @@ topk_merge_kernel(const MergeParams P) {
             const uint64_t key = ok ? buf[r] : 0;
             const float sc = ok ? key_score(key) : 0.0f;
             const int32_t dc = ok ? (int32_t)key_doc(key) : -1;
-            P.out_scores[(size_t)q * P.k + r] = sc;
-            P.out_docs[(size_t)q * P.k + r] = dc;
+            P.out_scores[orow * P.k + r] = sc;
+            P.out_docs[orow * P.k + r] = dc;
             for (uint32_t p = 0; p < P.n_peers; ++p) {           // the exchange: same row into every peer's slot
-                P.peer_scores[p][(size_t)q * P.k + r] = sc;
-                P.peer_docs[p][(size_t)q * P.k + r] = dc;
+                P.peer_scores[p][orow * P.k + r] = sc;
+                P.peer_docs[p][orow * P.k + r] = dc;
             }
         }
     }
     if (tid == 0) {
-        P.out_counts[q] = n;
-        for (uint32_t p = 0; p < P.n_peers; ++p) P.peer_counts[p][q] = n;
+        P.out_counts[orow] = n;
+        for (uint32_t p = 0; p < P.n_peers; ++p) P.peer_counts[p][orow] = n;
     }
+}
+
+__global__ void __launch_bounds__(1024)
+topk_merge_kernel(const MergeParams P) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* buf = reinterpret_cast<uint64_t*>(smem_raw);
+    if (blockIdx.x < P.nq) {
+        merge_body(P, blockIdx.x, (long long)blockIdx.x, buf);
+        return;
+    }
+    // wide path: this CTA's "lists" are the key arrays of one flagged query, one per tile
+    const uint32_t w = blockIdx.x - P.nq;
+    if (P.wide_first + w >= *P.n_wide) return;
+    MergeParams W = P;
+    W.mode = 0; W.nq = P.wide_ctas; W.n_lists = P.wide_n_lists; W.stride = P.wide_stride;
+    W.keys = P.wide_keys; W.cnts = P.wide_cnt; W.theta = nullptr; W.quant = nullptr; W.sorted_lists = 0;
+    merge_body(W, w, (long long)P.wide_q[P.wide_first + w] - P.wide_row0, buf);
 }
 
 static int merge_launch(MergeParams P, cudaStream_t s) {
@@ -301,7 +337,7 @@ static int merge_launch(MergeParams P, cudaStream_t s) {
     }
     // few queries cannot fill the GPU with CTAs: give each one more threads (the sort and the select scale with them)
     const int threads = P.nq <= 148 ? 1024 : (P.nq <= 2048 ? 512 : kMergeThreads);
-    topk_merge_kernel<<<P.nq, threads, smem, s>>>(P);
+    topk_merge_kernel<<<P.nq + P.wide_ctas, threads, smem, s>>>(P);
     count_launch();
     MSR_CUDA_CHECK(cudaGetLastError());
     return MSR_OK;
@@ -311,9 +347,13 @@ int topk_merge_keys_launch(uint32_t nq, uint32_t n_lists, uint32_t stride, const
                            uint32_t k, float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s,
                            uint32_t n_peers, float* const* peer_scores, int32_t* const* peer_docs,
                            uint32_t* const* peer_counts, size_t peer_row0, const unsigned long long* theta,
-                           const unsigned long long* quant, uint32_t quant_world, uint32_t quant_cap) {
+                           const unsigned long long* quant, uint32_t quant_world, uint32_t quant_cap, uint32_t wide_ctas,
+                           uint32_t wide_first, const uint32_t* wide_q, const uint32_t* n_wide, const uint64_t* wide_keys,
+                           const uint32_t* wide_cnt, uint32_t wide_n_lists, uint32_t wide_stride) {
     MergeParams P{};
     P.theta = theta; P.quant = quant; P.quant_world = quant_world; P.quant_cap = quant_cap;
+    P.wide_ctas = wide_ctas; P.wide_first = wide_first; P.wide_q = wide_q; P.n_wide = n_wide; P.wide_keys = wide_keys;
+    P.wide_cnt = wide_cnt; P.wide_n_lists = wide_n_lists; P.wide_stride = wide_stride; P.wide_row0 = (long long)peer_row0;
     P.nq = nq; P.n_lists = n_lists; P.stride = stride; P.k = k; P.mode = 0;
     P.keys = keys; P.cnts = cnts; P.out_scores = out_scores; P.out_docs = out_docs; P.out_counts = out_counts;
     P.n_peers = n_peers;

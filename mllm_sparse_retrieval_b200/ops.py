@@ -102,7 +102,8 @@ class SparseIndex:
                                                     ctypes.c_void_p(int(local_quant)) if local_quant else None, qarr))
 
     def status(self):
-        """Synchronise and raise MsrError(MSR_ERR_RANGE) if an earlier device-path search left the exact range."""
+        """Synchronise and raise MsrError(MSR_ERR_RANGE) if an earlier device-path search held more than 8 queries outside the
+        integer kernel's exact range (one wide pass per call; the host path takes any number)."""
         with torch.cuda.device(self.device):
             check(_lib.load().msr_sparse_index_status(self._h, current_stream_ptr(self.device)))
 

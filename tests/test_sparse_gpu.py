@@ -93,17 +93,41 @@ def test_score_above_2_24(oracle, lib_built):
     assert s.max() >= 2 ** 24
 
 
-def test_range_error_is_loud(oracle, lib_built):
-    from mllm_sparse_retrieval_b200._lib import MsrError, MSR_ERR_RANGE
+def test_out_of_range_queries_take_the_wide_path(oracle, lib_built):
+    """a query outside the integer kernel's exact range (weight > 65535, or sum_t w_t*max_impact(t) >= 2^31) used
+    to fail the whole batch.  It is now scored by the wide path (u64 accumulators, rule S6 reproduced exactly) and every
+    query of the batch gets its row: one such query among normal ones, all of them, and more than one wide pass holds
+    (host path); bit-exact against the oracle, which rounds every product to float32 and sums in double."""
+    rng = np.random.default_rng(31)
+    n_docs, n_terms = 5000, 60
+    indptr, docids, impacts = random_csr(rng, n_docs, n_terms, 16, max_impact=65535, zipf=False)
+    qi, qt, qw = random_queries(rng, 24, n_terms, 10, max_w=3000, zipf=False)
+    qw = qw.copy()
+    big = [int(qi[5]), int(qi[11]) + 2]                       # queries 5 and 11: one huge weight each
+    qw[big[0]] = 70000                                        # weight above 65535
+    qw[big[1]] = 60000                                        # 60000 * 65535 > 2^31
+    for tile in (0, 512):
+        s, d, c = _check(oracle, indptr, docids, impacts, n_docs, qi, qt, qw, 50, tile_docs=tile)
+        assert s[5, 0] >= 2.0 ** 31 and s[11, 0] >= 2.0 ** 31
+    # every query out of range, more than the 8 a wide pass takes: the host path runs further passes
+    qw2 = (qw.astype(np.int64) * 0 + 66000).astype(np.uint32)
+    _check_host = None
     from mllm_sparse_retrieval_b200.ops import SparseIndex
-    indptr = np.array([0, 2], dtype=np.uint64)
-    idx = SparseIndex(indptr, np.array([0, 1], np.uint32), np.array([65535, 3], np.uint16), 8)
-    qi = np.array([0, 1], dtype=np.uint64)
+    from mllm_sparse_retrieval_b200._lib import MsrError, MSR_ERR_RANGE
+    idx = SparseIndex(indptr, docids, impacts, n_docs, tile_docs=512)
+    hs, hd, hc = idx.search_host(qi, qt, qw2, 50)
+    es, ed, ec = oracle.impact_search_c(indptr, docids, impacts, n_docs, qi, qt, qw2, 50, threads=4)
+    np.testing.assert_array_equal(hd, ed); np.testing.assert_array_equal(hs, es); np.testing.assert_array_equal(hc, ec)
+    # the device path is asynchronous and takes one wide pass: 24 such queries -> the first 8 listed are scored, status says so
+    idx.search(*_dev_queries(qi, qt, qw2), 50)
     with pytest.raises(MsrError) as e:
-        idx.search_host(qi, np.array([0], np.uint32), np.array([70000], np.uint32), 5)
+        idx.status()
     assert e.value.code == MSR_ERR_RANGE
-    s, d, c = idx.search_host(qi, np.array([0], np.uint32), np.array([2], np.uint32), 5)   # handle still usable
-    assert c.tolist() == [2] and d[0, :2].tolist() == [0, 1]
+    s, d, c = idx.search(*_dev_queries(qi, qt, qw), 50)       # handle still usable; 2 wide queries fit one pass
+    idx.status()
+    es, ed, ec = oracle.impact_search_c(indptr, docids, impacts, n_docs, qi, qt, qw, 50, threads=4)
+    np.testing.assert_array_equal(d.cpu().numpy(), ed); np.testing.assert_array_equal(s.cpu().numpy(), es)
+    idx.close()
 
 
 def test_malformed_csr_rejected(lib_built):
