@@ -29,6 +29,25 @@ def _stale(target, deps):
     return any(os.path.getmtime(d) > t for d in deps)
 
 
+def build_variant(defines, name):
+    """Developer knob (A/B measurements): the same sources with extra -D flags -> mllm_sparse_retrieval_b200/<name>.so,
+    loaded instead of libmsr.so through MSR_LIB_PATH.  Objects go to build_<name>/."""
+    nvcc = _nvcc()
+    objdir = os.path.join(PKG, "build_" + name)
+    os.makedirs(objdir, exist_ok=True)
+    srcs = [os.path.join(CSRC, s) for s in SOURCES]
+
+    def one(src):
+        obj = os.path.join(objdir, os.path.basename(src)[:-3] + ".o")
+        subprocess.check_call([nvcc] + NVCC_FLAGS + list(defines) + ["-c", src, "-o", obj])
+        return obj
+    with ThreadPoolExecutor(max_workers=8) as ex:
+        objs = list(ex.map(one, srcs))
+    out = os.path.join(PKG, name + ".so")
+    subprocess.check_call([nvcc, "-shared", "-o", out] + objs + ["-gencode", "arch=compute_100a,code=sm_100a", "-lcudart"])
+    return out
+
+
 def build(force: bool = False, verbose: bool = False) -> str:
     nvcc = _nvcc()
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]

@@ -152,7 +152,7 @@ __global__ void build_scatter_kernel(const uint64_t* __restrict__ indptr, const 
             const uint32_t imp = impacts[p];
             if (imp > 255u) {
                 const uint32_t r = atomicAdd(&dense_cursor[(size_t)tile * n_dense + di], 1u);
-                postings[seg_ptr[(size_t)tile * n_terms + t] + r] = ((imp - 255u) << 16) | (d - tile_lo);
+                postings[seg_ptr[(size_t)tile * n_terms + t] + r] = ((imp - 255u) << 16) | perm32(d - tile_lo);
             }
             continue;
         }
@@ -163,7 +163,7 @@ __global__ void build_scatter_kernel(const uint64_t* __restrict__ indptr, const 
             if (docids[mid] < tile_lo) lo = mid + 1; else hi = mid;
         }
         uint32_t r = (uint32_t)(p - lo);
-        postings[seg_ptr[(size_t)tile * n_terms + t] + r] = ((uint32_t)impacts[p] << 16) | (d - tile_lo);
+        postings[seg_ptr[(size_t)tile * n_terms + t] + r] = ((uint32_t)impacts[p] << 16) | perm32(d - tile_lo);
     }
 }
 
@@ -320,7 +320,7 @@ __global__ void traffic_sum_kernel(const uint32_t* __restrict__ flags, uint32_t 
 }
 
 static size_t search_smem_bytes(uint32_t tile_docs) {
-    return sizeof(StageUnion) + sizeof(SmallState) + (size_t)((tile_docs + 7) & ~7u) * 4;
+    return sizeof(StageUnion) + sizeof(SmallState) + (size_t)((tile_docs + 255) & ~255u) * 4;   // whole 256-doc blocks (one per warp and step)
 }
 
 }  // namespace msr
@@ -349,8 +349,9 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
         // balanced tiles no larger than the default
         uint32_t nt = (n_docs + kDefaultTileDocs - 1) / kDefaultTileDocs;
         tile_docs = (n_docs + nt - 1) / nt;
-        tile_docs = (tile_docs + 31) & ~31u;
+        tile_docs = (tile_docs + 255) & ~255u;
     }
+    tile_docs = (tile_docs + 31) & ~31u;      // accumulator positions are a permutation inside 32-doc groups (perm32)
     const uint32_t n_tiles = (n_docs + tile_docs - 1) / tile_docs;
 
     // canonical CSR on the device
@@ -450,11 +451,11 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
         h->n_dense = 0;
     }
     if (h->n_dense) {
-        if ((e = cudaMalloc(&h->dense_rows, (size_t)h->n_dense * h->dense_stride * 2 + (size_t)kThreads * 16 + 16)) != cudaSuccess) return fail("alloc dense rows");
-        cudaMemsetAsync(h->dense_rows, 0, (size_t)h->n_dense * h->dense_stride * 2 + (size_t)kThreads * 16 + 16, s);
+        if ((e = cudaMalloc(&h->dense_rows, (size_t)h->n_dense * h->dense_stride * 2 + (size_t)kThreads * 16 + 1024)) != cudaSuccess) return fail("alloc dense rows");
+        cudaMemsetAsync(h->dense_rows, 0, (size_t)h->n_dense * h->dense_stride * 2 + (size_t)kThreads * 16 + 1024, s);
         // the kernel loads two slots per thread, the second kThreads slots further on, without a bounds test (the
         // values are dropped): keep those loads inside the allocations
-        const size_t pad8 = (size_t)kThreads * 8 + 16, pad16 = (size_t)kThreads * 16 + 16;
+        const size_t pad8 = (size_t)kThreads * 8 + 512, pad16 = (size_t)kThreads * 16 + 1024;
         if ((e = cudaMalloc(&h->dense_rows8, (size_t)h->n_dense * h->dense_stride + pad8)) != cudaSuccess) return fail("alloc dense rows (u8)");
         cudaMemsetAsync(h->dense_rows8, 0, (size_t)h->n_dense * h->dense_stride + pad8, s);
         if ((e = cudaMalloc(&h->dense_cursor, (size_t)h->n_dense * n_tiles * 4)) != cudaSuccess) return fail("alloc dense cursor");

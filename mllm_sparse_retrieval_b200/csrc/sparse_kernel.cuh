@@ -16,6 +16,7 @@
 // so a reader racing a writer sees old or new keys, each a real doc: no locks, nothing waits on another CTA.
 #pragma once
 #include "common.cuh"
+#include "sparse_dense_mma.cuh"
 
 namespace msr {
 
@@ -162,7 +163,8 @@ __device__ __forceinline__ void wide_score_cta(const SearchParams& P, uint32_t w
     const uint32_t q = P.wide_q[P.wide_first + w];
     const uint32_t tile_lo = tile * P.tile_docs, tl = min(P.tile_docs, P.n_docs - tile_lo);
     unsigned long long* acc = P.wide_acc + ((size_t)w * P.n_tiles + tile) * P.tile_docs;
-    for (uint32_t d = tid; d < tl; d += blockDim.x) acc[d] = 0ull;
+    const uint32_t tlp = (tl + 31) & ~31u;                      // accumulator positions (perm32 permutes inside 32-doc groups)
+    for (uint32_t d = tid; d < tlp; d += blockDim.x) acc[d] = 0ull;
     __syncthreads();
     const uint32_t* seg_row = P.seg_ptr + (size_t)tile * P.n_terms;
     for (uint64_t j = P.q_indptr[q]; j < P.q_indptr[q + 1]; ++j) {
@@ -174,23 +176,23 @@ __device__ __forceinline__ void wide_score_cta(const SearchParams& P, uint32_t w
             const uint16_t* row = P.dense_rows + (size_t)di * P.dense_stride + tile_lo;     // the whole impact
             for (uint32_t d = tid; d < tl; d += blockDim.x) {
                 const uint32_t imp = row[d];
-                if (imp) acc[d] += (unsigned long long)__fmul_rn(wf, __uint2float_rn(imp));
+                if (imp) acc[perm32(d)] += (unsigned long long)__fmul_rn(wf, __uint2float_rn(imp));
             }
         } else {
             const uint32_t s0 = seg_row[t], s1 = seg_row[t + 1];
             for (uint32_t p = s0 + tid; p < s1; p += blockDim.x) {
-                const uint32_t v = P.postings[p], imp = v >> 16;               // padding slots carry impact 0
+                const uint32_t v = P.postings[p], imp = v >> 16;               // padding slots carry impact 0; low half = position
                 if (imp) acc[v & 0xFFFFu] += (unsigned long long)__fmul_rn(wf, __uint2float_rn(imp));
             }
         }
         __syncthreads();
     }
     const uint32_t gdoc0 = (uint32_t)P.doc_base + tile_lo;
-    for (uint32_t d = tid; d < tl; d += blockDim.x) {
+    for (uint32_t d = tid; d < tlp; d += blockDim.x) {
         const unsigned long long a = acc[d];
-        acc[d] = a ? make_key(__ull2float_rn(a), gdoc0 + d) : 0ull;
+        acc[d] = a ? make_key(__ull2float_rn(a), gdoc0 + unperm32(d)) : 0ull;
     }
-    if (tid == 0) P.wide_cnt[w * P.n_tiles + tile] = tl;
+    if (tid == 0) P.wide_cnt[w * P.n_tiles + tile] = tlp;
 }
 
 __device__ __forceinline__ uint32_t ld_stream_u32(const uint32_t* p) {
@@ -216,7 +218,11 @@ struct SegStage {                      // streaming phase view of the union regi
     // terms that need the per-term float32 rounding of S6 from the back.
     alignas(16) uint32_t drow[kSegMax];
     alignas(16) uint32_t dw[kSegMax];
+#if MSR_DENSE_MMA
+    uint32_t qw[kSegMax / 4];          // front list: the four u8 weights of quad i (terms 4i .. 4i+3 of the list), the mma's B operand
+#else
     alignas(16) uint4 db[kSegMax];     // front list: (w, w << 8, w << 16, w << 24), the dp4a selectors of the weight
+#endif
 };
 struct SelStage {                      // radix-select view
     uint32_t hist[kBins];
@@ -235,11 +241,6 @@ struct SmallState {
 };
 static_assert(sizeof(SmallState) % 16 == 0 && sizeof(StageUnion) % 16 == 0, "accumulators must stay 16-byte aligned");
 
-__device__ __forceinline__ uint4 ld_stream_v4(const void* p) {
-    uint4 v;
-    asm("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
-    return v;
-}
 
 // a[0..7] += w * (8 u16 impacts packed in v), any w below 2^16: unpack (ALU pipe) + IMAD (FMA pipe) per impact
 __device__ __forceinline__ void dense_fma8_wide(uint32_t (&a)[8], const uint4 v, const uint32_t w) {
@@ -255,11 +256,6 @@ __device__ __forceinline__ void dense_fma8_wide(uint32_t (&a)[8], const uint4 v,
 __device__ __forceinline__ void dense_dp4a8(uint32_t (&a)[8], const uint2 v, const uint4 b) {
     a[0] = __dp4a(v.x, b.x, a[0]); a[1] = __dp4a(v.x, b.y, a[1]); a[2] = __dp4a(v.x, b.z, a[2]); a[3] = __dp4a(v.x, b.w, a[3]);
     a[4] = __dp4a(v.y, b.x, a[4]); a[5] = __dp4a(v.y, b.y, a[5]); a[6] = __dp4a(v.y, b.z, a[6]); a[7] = __dp4a(v.y, b.w, a[7]);
-}
-__device__ __forceinline__ uint2 ld_stream_v2(const void* p) {
-    uint2 v;
-    asm("ld.global.nc.L1::no_allocate.v2.u32 {%0,%1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(p));
-    return v;
 }
 
 // exclusive scan of one value per thread over the CTA (kThreads threads); returns exclusive prefix, *total = sum
@@ -374,6 +370,9 @@ sparse_score_topk_kernel(const SearchParams P) {
     do {
         __syncthreads();   // previous batch fully consumed
         if (tid == 0) { S->n_dense = 0; S->n_dense_f = 0; }
+#if MSR_DENSE_MMA
+        if (tid < kSegMax / 4) U->seg.qw[tid] = 0;
+#endif
         __syncthreads();
         uint32_t nchunks = 0;
         if (tid < kSegMax) {
@@ -398,7 +397,11 @@ sparse_score_topk_kernel(const SearchParams P) {
                             const uint32_t pos = fast ? atomicAdd(&S->n_dense, 1u) : kSegMax - 1 - atomicAdd(&S->n_dense_f, 1u);
                             if (fast) {
                                 U->seg.drow[pos] = di * (P.dense_row_bytes >> 1);
+#if MSR_DENSE_MMA
+                                atomicOr(&U->seg.qw[pos >> 2], w << (8 * (pos & 3)));
+#else
                                 U->seg.db[pos] = make_uint4(w, w << 8, w << 16, w << 24);
+#endif
                                 start = s0;
                                 len = s1 - s0;
                             } else {
@@ -422,11 +425,75 @@ sparse_score_topk_kernel(const SearchParams P) {
             nchunks = (len + kChunk - 1) / kChunk;
         }
         __syncthreads();
+#if MSR_DENSE_MMA
+        {
+            // dense phase on the integer tensor pipe (sparse_dense_mma.cuh): lane L of a warp owns accumulator positions
+            // 8L .. 8L+7 of the warp's 256-doc block; two slots per thread and step as before
+            const uint32_t nd = S->n_dense, ndf = S->n_dense_f;
+            const bool first = batch == qs;
+            if (first || nd || ndf) {
+                // whole warps only (mma.sync is warp-wide): 32 slots = one 256-doc block per warp and step; slots past the tile's
+                // end read the next tile's rows (or the row padding) into accumulators nobody looks at (positions >= tlp)
+                const uint32_t nslots = ((tl + 255) & ~255u) >> 3;
+                const char* rows = reinterpret_cast<const char*>(P.dense_rows + tile_lo);
+                const char* rows8 = reinterpret_cast<const char*>(P.dense_rows8 + tile_lo);
+                const uint32_t g = lane >> 2, t = lane & 3;
+                const uint32_t m0 = g == t ? 0xFFFFFFFFu : 0u, m1 = g == t + 4 ? 0xFFFFFFFFu : 0u;   // block-diagonal B
+                for (uint32_t slot = tid; slot < nslots; slot += 2 * kThreads) {
+                    const bool two = slot + kThreads < nslots;  // else the second slot's loads are dummies (row padding)
+                    uint32_t pa[8], pb[8];
+                    uint4* ap = reinterpret_cast<uint4*>(acc + 8 * slot);
+                    uint4* cp = ap + 2 * kThreads;
+                    if (first) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) { pa[i] = 0; pb[i] = 0; }
+                    } else {
+                        const uint4 x = ap[0], y = ap[1];
+                        pa[0] = x.x; pa[1] = x.y; pa[2] = x.z; pa[3] = x.w; pa[4] = y.x; pa[5] = y.y; pa[6] = y.z; pa[7] = y.w;
+                        if (two) {
+                            const uint4 x2 = cp[0], y2 = cp[1];
+                            pb[0] = x2.x; pb[1] = x2.y; pb[2] = x2.z; pb[3] = x2.w; pb[4] = y2.x; pb[5] = y2.y; pb[6] = y2.z; pb[7] = y2.w;
+                        }
+                    }
+                    const char* r8 = rows8 + slot * 8u;         // u8 rows: 8 docs = 8 bytes
+                    constexpr uint32_t kB8 = kThreads * 8u;     // byte distance of the second slot in a u8 row
+                    uint32_t d = 0;
+                    for (; d + 4 <= nd; d += 4) {
+                        const uint4 r = *reinterpret_cast<const uint4*>(&U->seg.drow[d]);
+                        const uint32_t W = U->seg.qw[d >> 2];
+                        dense_quad<4>(pa, pb, r8, kB8, r, W & m0, W & m1);
+                    }
+                    if (nd & 3) {
+                        const uint4 r = *reinterpret_cast<const uint4*>(&U->seg.drow[d]);
+                        const uint32_t W = U->seg.qw[d >> 2];
+                        if ((nd & 3) == 3) dense_quad<3>(pa, pb, r8, kB8, r, W & m0, W & m1);
+                        else if ((nd & 3) == 2) dense_quad<2>(pa, pb, r8, kB8, r, W & m0, W & m1);
+                        else dense_quad<1>(pa, pb, r8, kB8, r, W & m0, W & m1);
+                    }
+                    if (ndf) {                                  // weights of 256 and more; S6 terms (u16 rows)
+                        const char* c16 = rows + 2u * (8u * (slot & ~31u) + 32u * g + 16u * (t & 1u));
+                        constexpr uint32_t kB16 = kThreads * 16u;
+                        for (uint32_t f = 0; f < ndf; ++f) {
+                            const uint32_t r = U->seg.drow[kSegMax - 1 - f], wr = U->seg.dw[kSegMax - 1 - f];
+                            dense_wide_term(pa, c16 + r, t >> 1, wr);
+                            dense_wide_term(pb, c16 + r + kB16, t >> 1, wr);
+                        }
+                    }
+                    ap[0] = make_uint4(pa[0], pa[1], pa[2], pa[3]);
+                    ap[1] = make_uint4(pa[4], pa[5], pa[6], pa[7]);
+                    if (two) {
+                        cp[0] = make_uint4(pb[0], pb[1], pb[2], pb[3]);
+                        cp[1] = make_uint4(pb[4], pb[5], pb[6], pb[7]);
+                    }
+                }
+            }
+        }
+#else
         {
             const uint32_t nd = S->n_dense, ndf = S->n_dense_f;
             const bool first = batch == qs;
             if (first || nd || ndf) {
-                const uint32_t nslots = (tl + 7) >> 3;          // 8 docs per thread and step
+                const uint32_t nslots = ((tl + 31) & ~31u) >> 3; // 8 docs per thread and step; whole 32-doc groups (the selection passes read them)
                 const char* rows = reinterpret_cast<const char*>(P.dense_rows + tile_lo);
                 const char* rows8 = reinterpret_cast<const char*>(P.dense_rows8 + tile_lo);
                 // Two slots per thread and step (slot, slot + kThreads): the second one is reached with an immediate
@@ -509,6 +576,7 @@ sparse_score_topk_kernel(const SearchParams P) {
                 }
             }
         }
+#endif
         uint32_t total;
         const uint32_t ex = block_excl_scan(nchunks, S->wsum, &total);
         if (tid < kSegMax) U->seg.pref[tid] = ex;
@@ -573,6 +641,7 @@ sparse_score_topk_kernel(const SearchParams P) {
 
     // ---- phase 2: candidates of the tile by (float32(score) desc, doc asc) ----
     const uint32_t kq = min(P.k, tl);
+    const uint32_t tlp = (tl + 31) & ~31u;                      // accumulator POSITIONS: position i holds doc unperm32(i); past-the-end docs hold 0
     const uint32_t gdoc0 = (uint32_t)P.doc_base + tile_lo;
     unsigned long long* theta_p = P.theta + q;
     uint64_t* tlist = P.tlist + (size_t)q * P.k;
@@ -584,7 +653,7 @@ sparse_score_topk_kernel(const SearchParams P) {
         uint32_t amin = (uint32_t)tf;                           // smallest integer score whose float32 image is >= tf
         while (amin > 1 && __uint2float_rn(amin - 1) >= tf) --amin;
         const uint32_t cap = min(P.k_stride, (uint32_t)kUnionMax);
-        const uint32_t nvec = (tl + 3) >> 2;                     // 4 docs per thread and step (slots past tl hold 0)
+        const uint32_t nvec = tlp >> 2;                          // 4 positions per thread and step
         for (uint32_t j = tid; j < nvec; j += kThreads) {
             const uint4 x = reinterpret_cast<const uint4*>(acc)[j];
             if (max(max(x.x, x.y), max(x.z, x.w)) >= amin) {
@@ -592,8 +661,8 @@ sparse_score_topk_kernel(const SearchParams P) {
 #pragma unroll
                 for (int u = 0; u < 4; ++u) {
                     const uint32_t i = 4 * j + u;
-                    if (e[u] >= amin && i < tl) {
-                        const uint64_t key = make_key(__uint2float_rn(e[u]), gdoc0 + i);
+                    if (e[u] >= amin) {
+                        const uint64_t key = make_key(__uint2float_rn(e[u]), gdoc0 + unperm32(i));
                         if (key >= theta) {
                             const uint32_t pos = atomicAdd(&S->cand_cnt, 1u);
                             if (pos < cap) U->keys[pos] = key;
@@ -670,7 +739,7 @@ sparse_score_topk_kernel(const SearchParams P) {
 
     // 2b. exact radix select of the tile's top-k
     const uint4* acc4 = reinterpret_cast<const uint4*>(acc);
-    const uint32_t nvec4 = (tl + 3) >> 2;
+    const uint32_t nvec4 = tlp >> 2;
     uint32_t tmax = 0;
     {
         // (accumulator slots past tl hold 0, so whole 16-byte vectors are read in all passes of the select)
@@ -695,9 +764,9 @@ sparse_score_topk_kernel(const SearchParams P) {
         return;
     }
     if (hits <= kq) {                                           // S7: fewer hits than k -> all of them
-        for (uint32_t i = tid; i < tl; i += kThreads) {
+        for (uint32_t i = tid; i < tlp; i += kThreads) {
             uint32_t a = acc[i];
-            if (a) keys_out[atomicAdd(&S->out_cnt, 1u)] = make_key(__uint2float_rn(a), gdoc0 + i);
+            if (a) keys_out[atomicAdd(&S->out_cnt, 1u)] = make_key(__uint2float_rn(a), gdoc0 + unperm32(i));
         }
         if (tid == 0) *cnt_out = hits;
         return;
@@ -721,9 +790,9 @@ sparse_score_topk_kernel(const SearchParams P) {
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
                         const uint32_t i = 4 * j + u;
-                        if (e[u] >= g && i < tl) {
+                        if (e[u] >= g) {
                             const uint32_t pos = atomicAdd(&S->cand_cnt, 1u);
-                            if (pos < (uint32_t)kThreads) U->keys[pos] = make_key(__uint2float_rn(e[u]), gdoc0 + i);
+                            if (pos < (uint32_t)kThreads) U->keys[pos] = make_key(__uint2float_rn(e[u]), gdoc0 + unperm32(i));
                         }
                     }
                 }
@@ -803,8 +872,8 @@ sparse_score_topk_kernel(const SearchParams P) {
         const uint32_t e[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            const uint32_t a = e[u], i = 4 * j + u;
-            if (a && i < tl) {
+            const uint32_t a = e[u], i = unperm32(4 * j + u);      // i = doc offset of this position
+            if (a) {
                 uint32_t d = kmax - MSR_SELKEY(a);
                 uint32_t x = d >> s;
                 if (x < pref) {
@@ -824,7 +893,7 @@ sparse_score_topk_kernel(const SearchParams P) {
         bitonic_sort_desc(U->sel.cand, n2);
         for (uint32_t r = tid; r < remaining; r += kThreads) {
             uint32_t i = (uint32_t)(~U->sel.cand[r]);
-            keys_out[n_def + r] = make_key(__uint2float_rn(acc[i]), gdoc0 + i);
+            keys_out[n_def + r] = make_key(__uint2float_rn(acc[perm32(i)]), gdoc0 + i);
         }
     } else {
         // more than kCandMax docs tie exactly at the threshold key: take the `remaining` smallest doc ids (S8)
@@ -833,7 +902,7 @@ sparse_score_topk_kernel(const SearchParams P) {
         uint32_t c = 0;
         for (uint32_t base = lo; base < hi; base += 32) {
             uint32_t i = base + lane;
-            uint32_t a = i < hi ? acc[i] : 0;
+            uint32_t a = i < hi ? acc[perm32(i)] : 0;
             bool f = a && (kmax - MSR_SELKEY(a)) == pref;
             c += __popc(__ballot_sync(0xffffffffu, f));
         }
@@ -844,7 +913,7 @@ sparse_score_topk_kernel(const SearchParams P) {
         for (uint32_t w2 = 0; w2 < warp; ++w2) run += S->wsum[w2];
         for (uint32_t base = lo; base < hi; base += 32) {
             uint32_t i = base + lane;
-            uint32_t a = i < hi ? acc[i] : 0;
+            uint32_t a = i < hi ? acc[perm32(i)] : 0;
             bool f = a && (kmax - MSR_SELKEY(a)) == pref;
             uint32_t b = __ballot_sync(0xffffffffu, f);
             uint32_t r = run + __popc(b & ((1u << lane) - 1u));
