@@ -59,6 +59,7 @@ def parse_args():
     ap.add_argument("--nq-sweep", default="1,4,32,128,1024", help="small-batch latency lines (1 GPU; empty = skip)")
     ap.add_argument("--sweep-k", default="100,1000", help="depths of the small-batch lines (the reference's scripts use 10 / 1000)")
     ap.add_argument("--no-microbench", action="store_true", help="skip the measured ceilings of roofline.binding")
+    ap.add_argument("--no-extra", action="store_true", help="skip the short dense / hybrid blocks of the default line (configs[1], configs[2])")
     ap.add_argument("--workload", default="sparse", choices=["sparse", "dense", "hybrid", "config5"],
                     help="sparse = the headline metric (default); dense / hybrid = the other kernels of the path (bench_extra.py)")
     ap.add_argument("--dense-docs", type=int, default=25000)
@@ -607,6 +608,24 @@ def run_ours(a, rank, world, local_rank):
         res["small_batch"] = small_batch_lines(a, idx, qs0, dev, peak)
     if world == 1 and not a.no_cpu_baseline:
         res["cpu_baseline"] = cpu_baseline(a, coll_np, a.n_docs, qs0.numpy(), a.cpu_seconds)
+    if world == 1 and not a.no_extra and a.workload == "sparse" and a.n_docs == 1_000_000:
+        # the other kernels of the path, measured in the same driver-visible run (BASELINE.json configs[1] and [2]);
+        # the full lines are `bench.py --workload dense|hybrid`
+        del idx
+        torch.cuda.empty_cache()
+        import bench_extra
+        import copy
+        b = copy.copy(a)
+        b.steps, b.warmup, b.cpu_seconds = 5, 3, min(a.cpu_seconds, 8.0)
+        extra = {}
+        for name, fn in (("dense", bench_extra.run_dense), ("hybrid", bench_extra.run_hybrid)):
+            try:
+                r = fn(b, ROOT, ClockSampler, emit=False)
+                extra[name] = {k_: r[k_] for k_ in ("metric", "value", "unit", "ms_per_step", "steps", "config", "e2e", "roofline",
+                                                      "cpu_baseline", "parity_check", "gpu_launches", "dtype") if k_ in r}
+            except SystemExit as e:
+                extra[name] = {"error": f"exit {e.code}"}
+        res["extra"] = extra
     print(json.dumps(res), flush=True)
 
 

@@ -353,6 +353,18 @@ int msr_provenance_hist(int device, uint32_t nq, const double* scores, const uin
                         const uint32_t* counts, uint32_t depth, uint64_t* hist, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
+ * Final ordering of run rows: Python's stable `sorted(run.items(), key=score, reverse=True)` of
+ * /root/reference/src/metrices.py:30 and hybrid.write_trec_run (hybrid.py:20-29), and the removal of the query's own id that
+ * get_run_dict performs (search.py:66-82; order kept), in one kernel.  Row q has counts[q] entries (scores f32 or f64 per
+ * `scores_f64`, docs i32, optional provenance tags u8); an entry whose doc equals self_ids[q] (>= 0) is dropped; the rest
+ * are written to out_* by (score desc, original position asc) when by_score != 0, in their original order otherwise, and
+ * out_counts[q] is what remains.  width <= 2 * MSR_MAX_K.  Not in place.  Device pointers, asynchronous on `stream`.
+ */
+int msr_order_rows(int device, uint32_t nq, uint32_t width, const void* scores, int scores_f64, const int32_t* docs,
+                   const uint8_t* tags, size_t row_stride, const uint32_t* counts, const int32_t* self_ids, int by_score,
+                   void* out_scores, int32_t* out_docs, uint8_t* out_tags, uint32_t* out_counts, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------------
  * Measured ceilings for `roofline.binding` (csrc/microbench.cu; replaces no reference call).  The sparse scorer shares
  * postings across the query batch through L2, so HBM does not bound it; bench.py reports it against these numbers,
  * measured on the same GPU in the same run.  *units_per_s: bytes/s for the two read benchmarks (`bytes` = buffer size;

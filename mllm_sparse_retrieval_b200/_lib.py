@@ -61,6 +61,7 @@ def _declare(lib):
         "msr_collection_destroy": (I, [P]),
         "msr_invert_docs": (I, [I, U32, U32, P, P, P, P, P, P, P, I, P]),
         "msr_recall_hits": (I, [I, U32, P, ctypes.c_size_t, P, P, P, U32, P, P, P, P]),
+        "msr_order_rows": (I, [I, U32, U32, P, I, P, P, ctypes.c_size_t, P, P, I, P, P, P, P, P]),
         "msr_fuse": (I, [I, U32, U32, P, P, P, U32, P, P, P, P, I, I, D, D, P, P, P, P, P]),
     }
     for name, (res, args) in sigs.items():

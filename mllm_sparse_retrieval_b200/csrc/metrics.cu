@@ -62,6 +62,62 @@ provenance_hist_kernel(const double* __restrict__ scores, const uint8_t* __restr
     }
 }
 
+// Final ordering of run rows (the CLI's last step): what Python's stable `sorted(..., key=score, reverse=True)` does in
+// metrices.py:30 / hybrid.write_trec_run, and what get_run_dict does when it drops the query's own id (search.py:66-82),
+// as ONE kernel.  One CTA per row: an entry is valid when it lies inside the row's count and is not the row's `self` doc;
+// its rank is the number of valid entries that sort before it -- by (score desc, position asc) when by_score is set, by
+// position otherwise -- counted against the row held in shared memory (rows have at most 2 * MSR_MAX_K entries).
+template <typename T>
+__device__ __forceinline__ uint64_t order_key(T x);
+template <>
+__device__ __forceinline__ uint64_t order_key<float>(float x) { return (uint64_t)f2ord(x + 0.0f) + 1ull; }   // -0.0 == 0.0, as in Python
+template <>
+__device__ __forceinline__ uint64_t order_key<double>(double x) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(x + 0.0);   // -0.0 == 0.0, as in Python
+    const unsigned long long o = b ^ ((b >> 63) ? ~0ull : 0x8000000000000000ull);
+    return o == ~0ull ? o : o + 1ull;                           // 0 is reserved for "not valid"
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256)
+order_rows_kernel(const T* __restrict__ scores, const int32_t* __restrict__ docs, const uint8_t* __restrict__ tags, size_t row_stride,
+                  const uint32_t* __restrict__ counts, const int32_t* __restrict__ self_ids, uint32_t width, int by_score,
+                  T* __restrict__ out_scores, int32_t* __restrict__ out_docs, uint8_t* __restrict__ out_tags,
+                  uint32_t* __restrict__ out_counts) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    uint64_t* key = reinterpret_cast<uint64_t*>(smem_raw);
+    __shared__ uint32_t s_n;
+    const uint32_t q = blockIdx.x, tid = threadIdx.x;
+    const uint32_t n = min(counts[q], width);
+    const int32_t self = self_ids ? self_ids[q] : -1;
+    const T* srow = scores + (size_t)q * row_stride;
+    const int32_t* drow = docs + (size_t)q * row_stride;
+    if (tid == 0) s_n = 0;
+    __syncthreads();
+    uint32_t mine = 0;
+    for (uint32_t i = tid; i < n; i += 256) {
+        const bool valid = !(self >= 0 && drow[i] == self);
+        key[i] = valid ? (by_score ? order_key<T>(srow[i]) : 1ull) : 0ull;
+        mine += valid;
+    }
+    mine = warp_reduce_add(mine);
+    if ((tid & 31) == 0 && mine) atomicAdd(&s_n, mine);
+    __syncthreads();
+    for (uint32_t i = tid; i < n; i += 256) {
+        const uint64_t k = key[i];
+        if (!k) continue;
+        uint32_t rank = 0;
+        for (uint32_t j = 0; j < n; ++j) {
+            const uint64_t o = key[j];
+            rank += (o > k) || (o == k && j < i);
+        }
+        out_scores[(size_t)q * row_stride + rank] = srow[i];
+        out_docs[(size_t)q * row_stride + rank] = drow[i];
+        if (tags) out_tags[(size_t)q * row_stride + rank] = tags[(size_t)q * row_stride + i];
+    }
+    if (tid == 0) out_counts[q] = s_n;
+}
+
 }  // namespace msr
 
 using namespace msr;
@@ -96,6 +152,37 @@ extern "C" int msr_provenance_hist(int device, uint32_t nq, const double* scores
     if (nq == 0) return MSR_OK;
     MSR_REQUIRE(scores && src && counts, "msr_provenance_hist: NULL input");
     provenance_hist_kernel<<<nq, 256, 0, s>>>(scores, src, row_stride, counts, depth, (unsigned long long*)hist);
+    count_launch();
+    MSR_CUDA_CHECK(cudaGetLastError());
+    return MSR_OK;
+}
+
+extern "C" int msr_order_rows(int device, uint32_t nq, uint32_t width, const void* scores, int scores_f64, const int32_t* docs,
+                              const uint8_t* tags, size_t row_stride, const uint32_t* counts, const int32_t* self_ids,
+                              int by_score, void* out_scores, int32_t* out_docs, uint8_t* out_tags, uint32_t* out_counts,
+                              void* stream) {
+    MSR_REQUIRE(width >= 1 && width <= 2 * MSR_MAX_K, "msr_order_rows: width %u outside [1,%u]", width, 2 * MSR_MAX_K);
+    MSR_REQUIRE(row_stride >= width, "msr_order_rows: row_stride < width");
+    if (nq == 0) return MSR_OK;
+    MSR_REQUIRE(scores && docs && counts && out_scores && out_docs && out_counts, "msr_order_rows: NULL buffer");
+    MSR_REQUIRE(scores != out_scores && docs != out_docs, "msr_order_rows: the permutation is not done in place");
+    MSR_REQUIRE(!tags || out_tags, "msr_order_rows: tags without out_tags");
+    int rc = use_device(device);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    const size_t smem = (size_t)width * 8;
+    static std::atomic<uint64_t> attr_set{0};
+    if (attr_needed(attr_set)) {
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(order_rows_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * MSR_MAX_K * 8));
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(order_rows_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * MSR_MAX_K * 8));
+        attr_mark(attr_set);
+    }
+    if (scores_f64)
+        order_rows_kernel<double><<<nq, 256, smem, s>>>((const double*)scores, docs, tags, row_stride, counts, self_ids, width, by_score,
+                                                        (double*)out_scores, out_docs, out_tags, out_counts);
+    else
+        order_rows_kernel<float><<<nq, 256, smem, s>>>((const float*)scores, docs, tags, row_stride, counts, self_ids, width, by_score,
+                                                       (float*)out_scores, out_docs, out_tags, out_counts);
     count_launch();
     MSR_CUDA_CHECK(cudaGetLastError());
     return MSR_OK;

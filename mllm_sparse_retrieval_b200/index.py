@@ -22,20 +22,74 @@ from collections import Counter
 import numpy as np
 
 CACHE_DIR = "msr_index"
-CACHE_VERSION = 1
+CACHE_VERSION = 2
+
+
+class StringTable:
+    """Read-only list of strings kept as ONE utf-8 blob + offsets (+ an optional order): item i is decoded when it is asked
+    for.  A 10 M-entry docid table is two NumPy arrays instead of 10 M Python objects; the cache stores it as is."""
+
+    def __init__(self, blob, offsets, order=None):
+        self.blob = blob if isinstance(blob, (bytes, bytearray, memoryview)) else np.ascontiguousarray(blob, dtype=np.uint8).tobytes()
+        self.offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        self.order = None if order is None else np.ascontiguousarray(order, dtype=np.uint32)
+
+    @classmethod
+    def from_list(cls, items):
+        enc = [str(x).encode("utf-8") for x in items]
+        off = np.zeros(len(enc) + 1, dtype=np.uint64)
+        np.cumsum([len(e) for e in enc], out=off[1:])
+        return cls(b"".join(enc), off)
+
+    def __len__(self):
+        return len(self.order) if self.order is not None else len(self.offsets) - 1
+
+    def __getitem__(self, i):
+        if isinstance(i, slice):
+            return [self[j] for j in range(*i.indices(len(self)))]
+        i = int(i)
+        if i < 0:
+            i += len(self)
+        if not 0 <= i < len(self):
+            raise IndexError(i)
+        j = int(self.order[i]) if self.order is not None else i
+        return self.blob[int(self.offsets[j]):int(self.offsets[j + 1])].decode("utf-8")
+
+    def __iter__(self):
+        return (self[i] for i in range(len(self)))
+
+    def __eq__(self, other):
+        return len(self) == len(other) and all(a == b for a, b in zip(self, other))
+
+    def tolist(self):
+        return list(self)
 
 
 class ImpactCollection:
-    """Term dictionary + docid table + canonical term-major CSR on the host."""
+    """Term dictionary + docid table + canonical term-major CSR on the host.  ``terms`` / ``docids`` are lists or
+    ``StringTable``s; the string -> id dictionaries are built on first use (a search over pre-encoded queries needs the
+    term dictionary only, a run file the id -> string direction only)."""
 
     def __init__(self, terms, docids, indptr, post_docs, post_impacts):
-        self.terms = list(terms)                              # term id -> string
-        self.term_to_id = {t: i for i, t in enumerate(self.terms)}
-        self.docids = list(docids)                            # internal id -> external docid string (sorted)
-        self.docid_to_internal = {d: i for i, d in enumerate(self.docids)}
+        self.terms = terms if isinstance(terms, StringTable) else list(terms)            # term id -> string
+        self.docids = docids if isinstance(docids, StringTable) else list(docids)        # internal id -> external docid (sorted)
+        self._term_to_id = None
+        self._docid_to_internal = None
         self.indptr = np.ascontiguousarray(indptr, dtype=np.uint64)
         self.post_docs = np.ascontiguousarray(post_docs, dtype=np.uint32)
         self.post_impacts = np.ascontiguousarray(post_impacts, dtype=np.uint16)
+
+    @property
+    def term_to_id(self):
+        if self._term_to_id is None:
+            self._term_to_id = {t: i for i, t in enumerate(self.terms)}
+        return self._term_to_id
+
+    @property
+    def docid_to_internal(self):
+        if self._docid_to_internal is None:
+            self._docid_to_internal = {d: i for i, d in enumerate(self.docids)}
+        return self._docid_to_internal
 
     @property
     def n_docs(self):
@@ -52,7 +106,9 @@ class ImpactCollection:
     # ------------------------------------------------------------------------------------------------------
     @classmethod
     def from_vectors(cls, doc_ids, vectors):
-        """doc_ids: iterable of str; vectors: iterable of {term: int} (the JSONL ``vector`` objects)."""
+        """In-memory collections (tests, a handful of vectors produced on the fly): doc_ids: iterable of str; vectors:
+        iterable of {term: int} (the JSONL ``vector`` objects).  Pure Python and meant for small inputs -- collections
+        on disk go through ``from_jsonl_dir`` (C++ reader + GPU inversion)."""
         doc_ids = [str(d) for d in doc_ids]
         if len(set(doc_ids)) != len(doc_ids):
             raise ValueError("duplicate document ids in the collection")
@@ -88,12 +144,12 @@ class ImpactCollection:
         return cls(terms, [doc_ids[i] for i in order], indptr, d, w)
 
     @classmethod
-    def from_jsonl_files(cls, files, device=None):
+    def from_jsonl_files(cls, files, device=None, host_inversion=False):
         """Native builder: libmsr's C++ JSONL reader (msr_jsonl_parse: dictionary, docid table,
         doc-major postings under rules S1/S2/S8) followed by the inversion to the canonical term-major CSR -- on the GPU
-        (msr_invert_docs: key build + radix sort + histogram scan) when one is present, else a NumPy lexsort on the host
-        (index building is not the search path; the scorer itself has no CPU fallback).  Same numbering as
-        ``from_vectors`` on the parsed lines."""
+        (msr_invert_docs: key build + radix sort + histogram scan).  Same numbering as ``from_vectors`` on the parsed
+        lines.  Needs a CUDA device, like everything else here; ``host_inversion=True`` is the explicit opt-in for tooling
+        on a box without one (a NumPy lexsort instead of msr_invert_docs -- index building only, never the search path)."""
         import ctypes
         from . import _lib
         lib = _lib.load()
@@ -114,40 +170,38 @@ class ImpactCollection:
                                                  _lib.ptr(d_blob), _lib.ptr(d_off), _lib.ptr(t_blob), _lib.ptr(t_off)))
         finally:
             lib.msr_collection_destroy(h)
-        db_, tb_ = d_blob.tobytes(), t_blob.tobytes()
-        docids = [None] * n_docs
-        for i in range(n_docs):
-            docids[int(rank[i])] = db_[int(d_off[i]):int(d_off[i + 1])].decode("utf-8")
-        terms = [tb_[int(t_off[i]):int(t_off[i + 1])].decode("utf-8") for i in range(n_terms)]
+        # string tables stay blobs: docids in internal (sorted) order through `order` = inverse of the parser's rank[]
+        order = np.empty(n_docs, dtype=np.uint32)
+        order[rank] = np.arange(n_docs, dtype=np.uint32)
+        docids = StringTable(d_blob[:db], d_off, order)
+        terms = StringTable(t_blob[:tb], t_off)
         if n_terms == 0 or n_docs == 0:
-            return cls(terms or [""], docids, np.zeros(max(n_terms, 1) + 1, dtype=np.uint64), np.zeros(0, np.uint32), np.zeros(0, np.uint16))
-        use_gpu = False
-        try:
-            import torch
-            use_gpu = torch.cuda.is_available()
-        except ImportError:
-            pass
-        if use_gpu:
-            import torch
-            dev = torch.cuda.current_device() if device is None else torch.device(device).index or 0
-            indptr = np.empty(n_terms + 1, dtype=np.uint64)
-            o_docs = np.empty(nnz, dtype=np.uint32); o_imps = np.empty(nnz, dtype=np.uint16)
-            with torch.cuda.device(dev):
-                _lib.check(lib.msr_invert_docs(dev, n_docs, n_terms, _lib.ptr(doc_indptr), _lib.ptr(p_terms), _lib.ptr(p_imps),
-                                               _lib.ptr(rank), _lib.ptr(indptr), _lib.ptr(o_docs), _lib.ptr(o_imps), 0,
-                                               _lib.current_stream_ptr(dev)))
-            return cls(terms, docids, indptr, o_docs, o_imps)
-        d = np.repeat(rank.astype(np.int64), np.diff(doc_indptr.astype(np.int64)))
-        t = p_terms.astype(np.int64)
-        o = np.lexsort((d, t))
-        indptr = np.zeros(n_terms + 1, dtype=np.uint64)
-        np.cumsum(np.bincount(t, minlength=n_terms), out=indptr[1:])
-        return cls(terms, docids, indptr, d[o], p_imps[o])
+            return cls(terms if n_terms else [""], docids, np.zeros(max(n_terms, 1) + 1, dtype=np.uint64), np.zeros(0, np.uint32),
+                       np.zeros(0, np.uint16))
+        import torch
+        if host_inversion:
+            d = np.repeat(rank.astype(np.int64), np.diff(doc_indptr.astype(np.int64)))
+            t = p_terms.astype(np.int64)
+            o = np.lexsort((d, t))
+            indptr = np.zeros(n_terms + 1, dtype=np.uint64)
+            np.cumsum(np.bincount(t, minlength=n_terms), out=indptr[1:])
+            return cls(terms, docids, indptr, d[o], p_imps[o])
+        if not torch.cuda.is_available():
+            raise RuntimeError("ImpactCollection.from_jsonl_files inverts the collection on the GPU (msr_invert_docs); no CUDA "
+                               "device is visible (host_inversion=True opts into the NumPy inversion for tooling)")
+        dev = torch.cuda.current_device() if device is None else (torch.device(device).index or 0)
+        indptr = np.empty(n_terms + 1, dtype=np.uint64)
+        o_docs = np.empty(nnz, dtype=np.uint32); o_imps = np.empty(nnz, dtype=np.uint16)
+        with torch.cuda.device(dev):
+            _lib.check(lib.msr_invert_docs(dev, n_docs, n_terms, _lib.ptr(doc_indptr), _lib.ptr(p_terms), _lib.ptr(p_imps),
+                                           _lib.ptr(rank), _lib.ptr(indptr), _lib.ptr(o_docs), _lib.ptr(o_imps), 0,
+                                           _lib.current_stream_ptr(dev)))
+        return cls(terms, docids, indptr, o_docs, o_imps)
 
     @classmethod
-    def from_jsonl_dir(cls, path, use_cache=True, native=True):
+    def from_jsonl_dir(cls, path, use_cache=True, host_inversion=False):
         """path = the reference's ``--sparse_index`` directory (holds corpus_*.jsonl; Lucene's own ``index/`` is ignored).
-        native=True builds through libmsr (C++ reader + GPU inversion); False keeps the pure-Python reader."""
+        Built through libmsr (C++ reader + GPU inversion) and cached under ``<path>/msr_index/`` as raw arrays."""
         files = sorted(glob.glob(os.path.join(path, "corpus*.jsonl")))
         if not files:
             raise FileNotFoundError(f"no corpus*.jsonl under {path}")
@@ -157,25 +211,7 @@ class ImpactCollection:
             got = cls._load_cache(cdir, stamp)
             if got is not None:
                 return got
-        if native:
-            coll = cls.from_jsonl_files(files)
-            if use_cache:
-                try:
-                    coll._save_cache(cdir, stamp)
-                except OSError:
-                    pass
-            return coll
-        ids, vecs = [], []
-        for fn in files:
-            with open(fn, "r", encoding="utf-8") as f:
-                for line in f:
-                    line = line.strip()
-                    if not line:
-                        continue
-                    obj = json.loads(line)
-                    ids.append(str(obj["id"]))
-                    vecs.append(obj.get("vector") or {})
-        coll = cls.from_vectors(ids, vecs)
+        coll = cls.from_jsonl_files(files, host_inversion=host_inversion)
         if use_cache:
             try:
                 coll._save_cache(cdir, stamp)
@@ -183,15 +219,23 @@ class ImpactCollection:
                 pass                                     # read-only index directory: rebuild next time
         return coll
 
+    # On-disk cache: raw little-endian arrays, loaded with np.fromfile -- no JSON string lists, no
+    # Python dictionaries:  indptr.u64  docids.u32  impacts.u16  df.u32  terms.blob + terms.off.u64
+    #                       docnames.blob + docnames.off.u64 (+ docnames.order.u32)  meta.json
     def _save_cache(self, cdir, stamp):
         os.makedirs(cdir, exist_ok=True)
-        np.save(os.path.join(cdir, "indptr.npy"), self.indptr)
-        np.save(os.path.join(cdir, "docids.npy"), self.post_docs)
-        np.save(os.path.join(cdir, "impacts.npy"), self.post_impacts)
-        with open(os.path.join(cdir, "terms.json"), "w", encoding="utf-8") as f:
-            json.dump(self.terms, f, ensure_ascii=False)
-        with open(os.path.join(cdir, "docids.json"), "w", encoding="utf-8") as f:
-            json.dump(self.docids, f, ensure_ascii=False)
+        w = lambda name, a: np.ascontiguousarray(a).tofile(os.path.join(cdir, name))
+        w("indptr.u64", self.indptr); w("docids.u32", self.post_docs); w("impacts.u16", self.post_impacts); w("df.u32", self.df)
+        for name, tab in (("terms", self.terms), ("docnames", self.docids)):
+            tab = tab if isinstance(tab, StringTable) else StringTable.from_list(tab)
+            with open(os.path.join(cdir, name + ".blob"), "wb") as f:
+                f.write(tab.blob)
+            w(name + ".off.u64", tab.offsets)
+            op = os.path.join(cdir, name + ".order.u32")
+            if tab.order is not None:
+                w(name + ".order.u32", tab.order)
+            elif os.path.exists(op):
+                os.remove(op)
         with open(os.path.join(cdir, "meta.json"), "w") as f:
             json.dump({"version": CACHE_VERSION, "source": stamp, "n_docs": self.n_docs, "n_terms": self.n_terms,
                        "nnz": int(self.indptr[-1])}, f)
@@ -203,12 +247,17 @@ class ImpactCollection:
                 meta = json.load(f)
             if meta.get("version") != CACHE_VERSION or meta.get("source") != stamp:
                 return None
-            with open(os.path.join(cdir, "terms.json"), encoding="utf-8") as f:
-                terms = json.load(f)
-            with open(os.path.join(cdir, "docids.json"), encoding="utf-8") as f:
-                docids = json.load(f)
-            return cls(terms, docids, np.load(os.path.join(cdir, "indptr.npy")), np.load(os.path.join(cdir, "docids.npy")),
-                       np.load(os.path.join(cdir, "impacts.npy")))
+            r = lambda name, dt: np.fromfile(os.path.join(cdir, name), dtype=dt)
+
+            def table(name):
+                with open(os.path.join(cdir, name + ".blob"), "rb") as f:
+                    blob = f.read()
+                op = os.path.join(cdir, name + ".order.u32")
+                return StringTable(blob, r(name + ".off.u64", np.uint64), r(name + ".order.u32", np.uint32) if os.path.exists(op) else None)
+            coll = cls(table("terms"), table("docnames"), r("indptr.u64", np.uint64), r("docids.u32", np.uint32), r("impacts.u16", np.uint16))
+            if coll.n_docs != meta["n_docs"] or coll.n_terms != meta["n_terms"] or int(coll.indptr[-1]) != meta["nnz"]:
+                return None
+            return coll
         except (OSError, ValueError, KeyError):
             return None
 

@@ -334,6 +334,28 @@ def fuse_lists(d_scores, d_docs, d_counts, s_scores, s_docs, s_counts, self_ids,
     return out
 
 
+def order_rows(scores, docs, counts, self_ids=None, by_score=True, tags=None):
+    """msr_order_rows: stable descending order of each row's valid prefix (Python's ``sorted(..., reverse=True)``), and/or
+    removal of the row's own doc id with the order kept (``get_run_dict(remove_query=True)``).  scores f32/f64 [nq,w] CUDA,
+    docs i32, counts i32; returns (scores, docs, counts[, tags])."""
+    assert scores.is_cuda and scores.dtype in (torch.float32, torch.float64) and docs.dtype == torch.int32
+    scores, docs = scores.contiguous(), docs.contiguous()
+    nq, w = scores.shape
+    dev = scores.device
+    di = _dev_index(dev)
+    o_s, o_d = torch.zeros_like(scores), torch.full_like(docs, -1)
+    o_c = torch.empty((nq,), dtype=torch.int32, device=dev)
+    o_t = torch.zeros_like(tags) if tags is not None else None
+    if self_ids is not None:
+        self_ids = self_ids.to(device=dev, dtype=torch.int32).contiguous()
+    with torch.cuda.device(di):
+        check(_lib.load().msr_order_rows(di, nq, w, ptr(scores), int(scores.dtype == torch.float64), ptr(docs),
+                                         ptr(tags.contiguous()) if tags is not None else None, scores.stride(0),
+                                         ptr(counts.to(torch.int32).contiguous()), ptr(self_ids), int(bool(by_score)), ptr(o_s), ptr(o_d),
+                                         ptr(o_t), ptr(o_c), current_stream_ptr(di)))
+    return (o_s, o_d, o_c) if tags is None else (o_s, o_d, o_c, o_t)
+
+
 RECALL_CUTOFFS = (1, 5, 10, 100, 200)           # metrices.py:9
 
 
@@ -382,36 +404,46 @@ def quantise_topk(logits, top, token_to_term=None, vocab_len=None, doc_mode=Fals
 
 
 def text_token_ids(text, tokenizer, word_tokenize=None, stop_words=None):
-    """Host half of get_text_valid_tokens_values (/root/reference/src/encode.py:97-100, 103): lower-cased words minus
-    English stop-words and punctuation -> tokenizer.encode(word, add_special_tokens=False) -> list(set of token ids).
+    """Candidate token ids of one caption for ``quantise_candidates`` -- the host half of the reference's text quantiser
+    (rule Q2; /root/reference/src/encode.py:97-100,103): the caption is lower-cased and split into words, English
+    stop-words and punctuation marks are dropped, every remaining word is tokenised on its own (no special tokens), and
+    the distinct ids are returned (as a list; the kernel ranks candidates by value, then position).
 
-    ``word_tokenize`` / ``stop_words`` default to nltk's (as in the reference); pass them explicitly where nltk is absent."""
+    ``word_tokenize`` / ``stop_words`` default to nltk's, as in the reference; pass them explicitly where nltk is absent."""
     import string
     if word_tokenize is None or stop_words is None:
-        from nltk import word_tokenize as _wt                      # fails loudly when nltk is missing
-        from nltk.corpus import stopwords as _sw
-        word_tokenize = word_tokenize or _wt
-        stop_words = stop_words if stop_words is not None else _sw.words("english")
-    drop = set(list(stop_words) + list(string.punctuation))
-    words = [i for i in word_tokenize(text.lower()) if i not in drop]
-    token_ids = set()
-    for word in words:
-        token_ids.update(tokenizer.encode(word, add_special_tokens=False))
-    return list(token_ids)
+        import nltk                                                # fails loudly when nltk is missing
+        word_tokenize = word_tokenize or nltk.word_tokenize
+        if stop_words is None:
+            stop_words = nltk.corpus.stopwords.words("english")
+    ignored = frozenset(stop_words) | frozenset(string.punctuation)
+    # The ORDER of the returned list breaks value ties between candidates, and the reference's order is whatever CPython's
+    # set iteration yields after these very insertions -- so the ids must go through one set, word by word, id by id.
+    ids = set()
+    for word in word_tokenize(text.lower()):
+        if word not in ignored:
+            ids.update(tokenizer.encode(word, add_special_tokens=False))
+    return list(ids)
+
+
+def expansion_vocab_mask(tokenizer, vocab_size=None):
+    """u8 [V] mask of the expansion vocabulary (rule behind /root/reference/src/encode.py:38-47), in the form the kernel
+    takes it (msr_quantise_candidates' ``expand_mask``): 1 for a vocabulary entry that -- once one leading word-boundary
+    marker ('\u2581' or a blank) is removed -- is purely alphabetic or purely digits AND starts with an ASCII lower-case
+    letter."""
+    vocab = tokenizer.get_vocab()
+    size = int(vocab_size) if vocab_size is not None else (max(vocab.values()) + 1 if vocab else 0)
+    mask = np.zeros(size, dtype=np.uint8)
+    for tok, tid in vocab.items():
+        body = tok[1:] if tok[:1] in ("\u2581", " ") else tok
+        if 0 <= tid < size and (body.isalpha() or body.isdigit()) and "a" <= body[:1] <= "z":
+            mask[tid] = 1
+    return mask
 
 
 def get_filtered_ids(tokenizer):
-    """/root/reference/src/encode.py:38-47: ids of the vocabulary entries that are alphabetic or numeric words starting
-    with a lower-case ASCII letter (after a leading '▁' / ' ' is dropped) -- the expansion vocabulary."""
-    filtered_ids = set()
-    for token, id in tokenizer.get_vocab().items():
-        if token[0] == '▁' or token[0] == ' ':
-            token = token[1:]
-        if not token.isalpha() and not token.isdigit():
-            continue
-        if ord('a') <= ord(token[0]) <= ord('z'):
-            filtered_ids.add(id)
-    return filtered_ids
+    """The same vocabulary as a set of ids (the reference's container for it, encode.py:38-47)."""
+    return set(np.flatnonzero(expansion_vocab_mask(tokenizer)).tolist())
 
 
 def quantise_candidates(logits, cand_lists, token_to_term=None, vocab_len=None, doc_mode=False, cap=128, fallback_top=10,
@@ -435,9 +467,13 @@ def quantise_candidates(logits, cand_lists, token_to_term=None, vocab_len=None, 
     n_expand = min(int(num_expended_tokens), V, 1024) if filtered_ids is not None else 0      # top_k = min(n, eligible)
     mask = None
     if n_expand > 0:
-        m = np.zeros(V, dtype=np.uint8)
-        ids = np.fromiter((i for i in filtered_ids if 0 <= i < V), dtype=np.int64)
-        m[ids] = 1
+        if isinstance(filtered_ids, np.ndarray) and filtered_ids.dtype == np.uint8:          # expansion_vocab_mask()
+            m = np.zeros(V, dtype=np.uint8)
+            m[:min(V, len(filtered_ids))] = filtered_ids[:V]
+        else:
+            m = np.zeros(V, dtype=np.uint8)
+            ids = np.fromiter((i for i in filtered_ids if 0 <= i < V), dtype=np.int64)
+            m[ids] = 1
         mask = torch.from_numpy(m).to(dev)
     pitch = max(int(cap), int(fallback_top)) + n_expand
     indptr = torch.empty((n + 1,), dtype=torch.int64, device=dev)

@@ -74,6 +74,15 @@ def parse_args(argv=None):
     ap.add_argument("--query_sparse", default=None, help="query.tsv (or its directory) written by encode.py --encode_is_query")
     ap.add_argument("--qrels", default=None, help="optional: lines `qid<TAB>docid [docid ...]` -> Recall@{1,5,10,100,200}")
     ap.add_argument("--run_name", default="fusion")
+    ap.add_argument("--dist", default="auto", choices=["auto", "none", "replicas", "shard"],
+                    help="under torchrun / deepspeed: replicas = query slices per rank, whole index everywhere (the reference's "
+                         "scheme, search.py:180); shard = doc ranges per rank, fused exchange; auto = replicas")
+    ap.add_argument("--query_logits", default=None, help="torch.save({'ids', 'logits' [nq,V]}): encoder output, quantised on the device")
+    ap.add_argument("--vocab", default=None, help="tokenizer vocabulary as JSON (list id -> string, or {string: id})")
+    ap.add_argument("--sparse_length", type=int, default=128, help="terms kept per query vector (arguments.py:48)")
+    ap.add_argument("--is_filtered", type=_str2bool, nargs="?", const=True, default=False, help="filter_token on vocabulary strings (arguments.py:45)")
+    ap.add_argument("--return_all", type=_str2bool, nargs="?", const=True, default=False,
+                    help="replicas mode: gather every rank's rows even without --save_dir (main() then returns the full runs)")
     ns, unknown = ap.parse_known_args(argv)
     if unknown and not ns.quiet:
         print(f"[search] ignoring encoder-side arguments: {' '.join(unknown)}", file=sys.stderr)
@@ -105,15 +114,6 @@ def read_query_tsv(path):
     return ids, texts
 
 
-def _sorted_run(scores, docs, counts):
-    """Stable descending sort of each row's valid prefix (metrices.py:30 / write_trec_run order); torch plumbing."""
-    k = scores.shape[1]
-    pad = torch.arange(k, device=scores.device)[None, :] >= counts[:, None]
-    key = scores.masked_fill(pad, float("-inf"))
-    order = torch.sort(key, dim=1, descending=True, stable=True).indices
-    return torch.gather(scores, 1, order), torch.gather(docs, 1, order)
-
-
 def write_trec_arrays(path, qids, names, scores, docs, counts, run_name):
     """hybrid.write_trec_run for array-form runs (rows already in rank order)."""
     with open(path, "w") as f:
@@ -122,11 +122,11 @@ def write_trec_arrays(path, qids, names, scores, docs, counts, run_name):
             f.writelines(f"{qid} Q0 {names[docs[r, j]]} {j + 1} {scores[r, j]} {run_name}\n" for j in range(n))
 
 
-def recall_at(qids, name_id, docs, counts, qrels, ks=ops.RECALL_CUTOFFS):
-    """Recall@k as the reference computes it (metrices.py:29-100): a query scores a hit at k when ANY of its targets is
-    among its first k ranked docs; queries with an empty list never hit; recall = hits / number of queries.
-    docs i32 [nq, w] CUDA ranked lists of internal ids, counts [nq]; qrels = {qid: set of external docids}.
-    The hit test runs on the device (msr_recall_hits); only the 5 counters come back."""
+def recall_counters(qids, name_id, docs, counts, qrels, ks=ops.RECALL_CUTOFFS):
+    """Hit counters of Recall@k as the reference computes it (metrices.py:29-100): a query scores a hit at k when ANY of its
+    targets is among its first k ranked docs; queries with an empty list never hit.  docs i32 [nq, w] CUDA ranked lists of
+    internal ids, counts [nq]; qrels = {qid: set of external docids}.  The hit test runs on the device (msr_recall_hits);
+    returns (hits i64 [len(ks)], evaluated queries) as device tensors -- recall = hits / number of queries."""
     indptr, flat = [0], []
     for qid in qids:
         for t in sorted(qrels.get(qid, ())):
@@ -134,11 +134,65 @@ def recall_at(qids, name_id, docs, counts, qrels, ks=ops.RECALL_CUTOFFS):
             if i is not None:
                 flat.append(i)
         indptr.append(len(flat))
-    hits, n_eval = ops.recall_hits(docs.contiguous(), counts, torch.tensor(indptr, dtype=torch.int64),
-                                   torch.tensor(flat, dtype=torch.int32), ks)
-    hits = hits.cpu().tolist()
+    return ops.recall_hits(docs.contiguous(), counts, torch.tensor(indptr, dtype=torch.int64),
+                           torch.tensor(flat, dtype=torch.int32), ks)
+
+
+def recall_at(qids, name_id, docs, counts, qrels, ks=ops.RECALL_CUTOFFS):
+    hits, n_eval = recall_counters(qids, name_id, docs, counts, qrels, ks)
     n = max(1, len(qids))
-    return {k: h / n for k, h in zip(ks, hits)}, int(n_eval.item())
+    return {k: h / n for k, h in zip(ks, hits.cpu().tolist())}, int(n_eval.item())
+
+
+def init_distributed(mode):
+    """(rank, world, mode).  The reference is launched as `deepspeed --num_gpus=N src/search.py` and initialises NCCL itself
+    (scripts/search.sh:14, search.py:112-131); under torchrun / deepspeed (WORLD_SIZE > 1) this does the same.
+    mode: replicas = every rank holds the whole index and takes a slice of the queries (what search.py:180 does with a
+    DistributedSampler, without its padding duplicates); shard = every rank holds a doc range, all ranks pass all queries
+    (LuceneImpactSearcher / FaissFlatSearcher with shard=True); auto = replicas."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world == 1 or mode == "none":
+        return 0, 1, "none"
+    import torch.distributed as dist
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return dist.get_rank(), world, ("replicas" if mode == "auto" else mode)
+
+
+def load_query_logits(path, vocab_path):
+    """Encoder output for the string-free sparse path: ``torch.save({"ids": [...], "logits": float tensor [nq, V]})`` (or
+    a (logits, ids) pair) -- the rows the reference's quantiser receives (log(1 + relu(x)), encode.py:56-93) -- and the
+    tokenizer vocabulary as JSON, a list (id -> string) or a {string: id} map."""
+    import json
+    obj = torch.load(path, map_location="cpu")
+    logits, ids = (obj["logits"], obj["ids"]) if isinstance(obj, dict) else obj
+    with open(vocab_path, "r", encoding="utf-8") as f:
+        v = json.load(f)
+    if isinstance(v, dict):
+        size = max(v.values()) + 1
+        vocab = [""] * size
+        for tok, i in v.items():
+            vocab[i] = tok
+    else:
+        vocab = list(v)
+    return [str(x) for x in ids], logits, vocab
+
+
+def gather_rows(rank, world, dev, tensors, counts_total):
+    """replicas mode: rows of every rank (contiguous query slices, rank order) -> the full arrays, on every rank."""
+    import torch.distributed as dist
+    n_max = max(counts_total)
+    out = []
+    for t in tensors:
+        pad = torch.zeros((n_max,) + tuple(t.shape[1:]), dtype=t.dtype, device=dev)
+        pad[:t.shape[0]] = t
+        g = torch.empty((world,) + tuple(pad.shape), dtype=t.dtype, device=dev)
+        dist.all_gather_into_tensor(g, pad)
+        out.append(torch.cat([g[r, :counts_total[r]] for r in range(world)], 0))
+    return out
 
 
 def main(argv=None):
@@ -147,23 +201,42 @@ def main(argv=None):
         raise SystemExit("mllm_sparse_retrieval_b200.search needs a CUDA (sm_100a) device: there is no CPU fallback")
     if sa.passage_reps is None and sa.sparse_index is None:
         raise SystemExit("give --passage_reps and/or --sparse_index")
+    rank, world, mode = init_distributed(ns.dist)
     dev = torch.device("cuda", torch.cuda.current_device())
+    shard = mode == "shard"
     depth = int(sa.depth)
     dense = sparse = None
-    names, name_id = [], {}
+    names, name_id = [], None
+
+    def my_slice(n):
+        """queries this rank answers: all of them, or its contiguous share in replicas mode"""
+        return (n * rank // world, n * (rank + 1) // world) if mode == "replicas" else (0, n)
 
     # ---- sparse side --------------------------------------------------------------------------------------
     if sa.sparse_index is not None:
-        if ns.query_sparse is None:
-            raise SystemExit("--sparse_index needs --query_sparse (query.tsv)")
-        searcher = LuceneImpactSearcher(os.path.join(sa.sparse_index, "index"), None)
+        if ns.query_sparse is None and ns.query_logits is None:
+            raise SystemExit("--sparse_index needs --query_sparse (query.tsv) or --query_logits (+ --vocab)")
+        searcher = LuceneImpactSearcher(os.path.join(sa.sparse_index, "index"), None, shard=shard)
         searcher.set_analyzer(None)
-        s_qids, topics = read_query_tsv(_resolve(ns.query_sparse, "query.tsv"))
-        names = list(searcher.collection.docids)                # internal id -> external docid string
-        name_id = dict(searcher.collection.docid_to_internal)
+        names = searcher.collection.docids                      # internal id -> external docid string
         k_s = min(depth, ops.MSR_MAX_K)
-        ss, sd, sc = searcher.search_arrays(topics, k_s)
-        sparse = (s_qids, torch.from_numpy(ss).to(dev), torch.from_numpy(sd).to(dev), torch.from_numpy(sc.astype(np.int32)).to(dev))
+        if ns.query_logits is not None:
+            # encoder output -> quantiser -> scorer without a string in between (search.py:410-447 builds `' tok' * v`
+            # strings that pyserini counts again; here msr_quantise_topk writes the query CSR the scorer reads)
+            if ns.vocab is None:
+                raise SystemExit("--query_logits needs --vocab (tokenizer vocabulary as JSON)")
+            s_qids, logits, vocab = load_query_logits(ns.query_logits, ns.vocab)
+            lo, hi = my_slice(len(s_qids))
+            t2t = torch.from_numpy(searcher.collection.token_to_term_map(vocab, is_filtered=ns.is_filtered)).to(dev)
+            qi, qt, qw = ops.quantise_topk(logits[lo:hi].to(dev).contiguous(), int(ns.sparse_length), token_to_term=t2t,
+                                           vocab_len=len(vocab))
+            ss, sd, sc = searcher.search_csr(qi, qt, qw, k_s)
+        else:
+            s_qids, topics = read_query_tsv(_resolve(ns.query_sparse, "query.tsv"))
+            lo, hi = my_slice(len(s_qids))
+            ss, sd, sc = searcher.search_arrays(topics[lo:hi], k_s)
+            ss, sd, sc = torch.from_numpy(ss).to(dev), torch.from_numpy(sd).to(dev), torch.from_numpy(sc.astype(np.int32)).to(dev)
+        sparse = (s_qids, ss, sd, sc.to(torch.int32))
 
     # ---- dense side ---------------------------------------------------------------------------------------
     if sa.passage_reps is not None:
@@ -173,20 +246,24 @@ def main(argv=None):
         if not index_files:
             raise SystemExit(f"no corpus*.pkl under {sa.passage_reps}")
         p_reps, p_lookup = pickle_load(index_files[0])          # the reference loads the first shard only (search.py:228-237)
-        retriever = FaissFlatSearcher(p_reps)
+        retriever = FaissFlatSearcher(p_reps, shard=shard)
         retriever.add(p_reps)
         q_reps, d_qids = pickle_load(_resolve(ns.query_reps, "query.pkl"))
         d_qids = [str(x) for x in d_qids]
+        lo, hi = my_slice(len(d_qids))
+        q_mine = q_reps[lo:hi].astype(np.float32)
         k_d = min(depth, ops.MSR_MAX_K, len(p_lookup))
         if sa.batch_size > 0:
-            d_scores, d_idx = retriever.batch_search(q_reps.astype(np.float32), k_d, sa.batch_size, sa.quiet)
+            d_scores, d_idx = retriever.batch_search(q_mine, k_d, sa.batch_size, sa.quiet)
         else:
-            d_scores, d_idx = retriever.search(q_reps.astype(np.float32), k_d)
+            d_scores, d_idx = retriever.search(q_mine, k_d)
         # dense row number -> shared doc numbering (the sparse index's internal ids when both sides exist)
-        if not names:
+        if len(names) == 0:
             names = [str(x) for x in p_lookup]
             row_to_id = np.arange(len(p_lookup), dtype=np.int32)
         else:
+            name_id = dict(searcher.collection.docid_to_internal)
+            names = list(names)
             row_to_id = np.empty(len(p_lookup), dtype=np.int32)
             for r, x in enumerate(p_lookup):
                 x = str(x)
@@ -200,10 +277,16 @@ def main(argv=None):
         dense = (d_qids, torch.from_numpy(d_scores).to(dev), dd.to(torch.int32), dc)
 
     # ---- runs, fusion, order ------------------------------------------------------------------------------
-    lookup = name_id if name_id else {n: i for i, n in enumerate(names)}
+    all_qids = (dense or sparse)[0]
+    lo, hi = my_slice(len(all_qids))
+    qids = all_qids[lo:hi]
+    need_lookup = sa.remove_query or ns.qrels
+    if name_id is None and need_lookup:
+        name_id = (dict(searcher.collection.docid_to_internal) if sparse is not None and dense is None
+                   else {n: i for i, n in enumerate(names)})
 
-    def self_ids(qids):
-        return torch.tensor([lookup.get(q, -1) for q in qids], dtype=torch.int32, device=dev)
+    def self_ids(qs):
+        return torch.tensor([name_id.get(q, -1) for q in qs] if name_id is not None else [-1] * len(qs), dtype=torch.int32, device=dev)
 
     outputs = {}
     if dense is not None and sparse is not None:
@@ -213,30 +296,25 @@ def main(argv=None):
             missing = [q for q in dense[0] if q not in pos]
             if missing:
                 raise KeyError(missing[0])
+            if mode == "replicas":
+                raise SystemExit("--dist replicas needs query.tsv and query.pkl in the same query order")
             sel = torch.tensor([pos[q] for q in dense[0]], device=dev)
             sparse = (dense[0], sparse[1][sel], sparse[2][sel], sparse[3][sel])
-        qids = dense[0]
         fs, fd, fsrc, fc = ops.fuse_lists(dense[1].contiguous(), dense[2].contiguous(), dense[3], sparse[1].contiguous(),
                                           sparse[2].contiguous(), sparse[3], self_ids(qids), sa.remove_query, sa.alpha,
                                           1 - sa.alpha)
-        outputs[ns.run_name] = (qids,) + _sorted_run(fs, fd, fc) + (fc,)
+        outputs[ns.run_name] = ops.order_rows(fs, fd, fc)       # stable, score descending (metrices.py:30)
     for tag, side in (("dense", dense), ("sparse", sparse)):
         if side is None:
             continue
-        qids, s, d, c = side
+        _, s, d, c = side
         if sa.remove_query:                                      # get_run_dict: drop doc == qid, keep the order
-            me = self_ids(qids)[:, None]
-            keep = (d != me) & (torch.arange(s.shape[1], device=dev)[None, :] < c[:, None])
-            order = torch.sort((~keep).to(torch.int8), dim=1, stable=True).indices
-            s, d, c = torch.gather(s, 1, order), torch.gather(d, 1, order), keep.sum(1).to(torch.int32)
-        outputs[tag] = (qids, s, d, c)
+            s, d, c = ops.order_rows(s, d, c, self_ids=self_ids(qids), by_score=False)
+        outputs[tag] = (s, d, c)
 
     main_tag = ns.run_name if ns.run_name in outputs else ("dense" if dense is not None else "sparse")
-    if sa.save_dir:
-        os.makedirs(sa.save_dir, exist_ok=True)
-        for tag, (qids, s, d, c) in outputs.items():
-            write_trec_arrays(os.path.join(sa.save_dir, f"run.{tag}.trec"), qids, names, s.cpu().numpy(), d.cpu().numpy(),
-                              c.cpu().numpy(), tag)
+    # ---- Recall@k: hit counters per rank, ONE all_reduce (the reference gathers 15 Python objects, metrices.py:86-100) --
+    recall = None
     if ns.qrels:
         qrels = {}
         with open(ns.qrels) as f:
@@ -244,12 +322,33 @@ def main(argv=None):
                 parts = line.split()
                 if parts:
                     qrels.setdefault(parts[0], set()).update(parts[1:])
-        qids, s, d, c = outputs[main_tag]
-        rec, n_eval = recall_at(qids, lookup, d, c, qrels)
-        print(f"[{main_tag}] queries: {len(qids)} (non-empty lists: {n_eval})")
+        s, d, c = outputs[main_tag]
+        hits, n_eval = recall_counters(qids, name_id, d, c, qrels)
+        if mode == "replicas":
+            import torch.distributed as dist
+            acc = torch.cat([hits.to(torch.int64), n_eval.reshape(1).to(torch.int64)])
+            dist.all_reduce(acc)
+            hits, n_eval = acc[:-1], acc[-1]
+        recall = ({k: h / max(1, len(all_qids)) for k, h in zip(ops.RECALL_CUTOFFS, hits.cpu().tolist())}, int(n_eval.item()))
+    # ---- run files: written once, by rank 0 ----------------------------------------------------------------------
+    if mode == "replicas" and (sa.save_dir or ns.return_all):
+        per_rank = [len(all_qids) * (r + 1) // world - len(all_qids) * r // world for r in range(world)]
+        outputs = {tag: tuple(gather_rows(rank, world, dev, list(v), per_rank)) for tag, v in outputs.items()}
+        qids = all_qids
+    if sa.save_dir and rank == 0:
+        os.makedirs(sa.save_dir, exist_ok=True)
+        for tag, (s, d, c) in outputs.items():
+            write_trec_arrays(os.path.join(sa.save_dir, f"run.{tag}.trec"), qids, names, s.cpu().numpy(), d.cpu().numpy(),
+                              c.cpu().numpy(), tag)
+    if recall is not None and rank == 0:
+        rec, n_eval = recall
+        print(f"[{main_tag}] queries: {len(all_qids)} (non-empty lists: {n_eval})")
         for k, v in rec.items():
             print(f"Recall@{k}: {v:.4f}")
-    return outputs, names
+    if world > 1:
+        import torch.distributed as dist
+        dist.barrier()
+    return {tag: (qids,) + tuple(v) for tag, v in outputs.items()}, names
 
 
 if __name__ == "__main__":

@@ -99,28 +99,37 @@ class LuceneImpactSearcher:
         return px
 
     # -- array-level API (used by the CLI, the fusion path and the benchmarks) --------------------------------
-    def search_arrays(self, queries, k):
-        """queries: list of strings / token->count maps.  Returns host arrays (scores f32, docs i32 internal ids, counts)."""
-        qi, qt, qw = self.collection.encode_queries(queries)
-        if self.world == 1:
-            return self.index.search_host(qi, qt, qw, k)
+    def search_csr(self, d_qi, d_qt, d_qw, k):
+        """Query CSR already on the device (i64 indptr, i32 terms, i32 weights -- e.g. straight from ops.quantise_topk):
+        returns device tensors (scores f32 [nq,k], docs i32 internal ids, counts i32).  Doc-sharded searchers exchange and
+        merge; every rank must pass the same batch."""
+        nq = int(d_qi.numel()) - 1
         dev = self.device
-        t = lambda a, dt: torch.from_numpy(a.astype(dt)).to(dev)
-        d_qi, d_qt, d_qw = t(qi, np.int64), t(qt, np.int32), t(qw, np.int32)
-        nq = len(queries)
         if nq == 0:
-            return (np.empty((0, k), np.float32), np.empty((0, k), np.int32), np.empty((0,), np.uint32))
+            return (torch.empty((0, k), dtype=torch.float32, device=dev), torch.empty((0, k), dtype=torch.int32, device=dev),
+                    torch.empty((0,), dtype=torch.int32, device=dev))
+        if self.world == 1:
+            out = self.index.search(d_qi, d_qt, d_qw, k)
+            self.index.status()
+            return out
         px = self._peer_exchange(nq, k)
         if px is not None:          # exchange fused into the scorer's last kernel (peer stores), no collective call
             ms, md, mc = px.run(self.index, lambda o: self.index.search(d_qi, d_qt, d_qw, k, out=o), nq=nq)
         else:                       # NCCL all-gather + merge
             ex = PipelinedExchange(nq, k, dev, self.world)
-
-            def chunk(i, lo, hi, o):
-                a0, a1 = int(qi[lo]), int(qi[hi])
-                self.index.search(d_qi[lo:hi + 1] - a0, d_qt[a0:a1], d_qw[a0:a1], k, out=o)
-            ms, md, mc = ex.run(chunk)
+            ms, md, mc = ex.run(lambda i, lo, hi, o: self.index.search(d_qi, d_qt, d_qw, k, out=o))
         self.index.status()
+        return ms, md, mc
+
+    def search_arrays(self, queries, k):
+        """queries: list of strings / token->count maps.  Returns host arrays (scores f32, docs i32 internal ids, counts)."""
+        qi, qt, qw = self.collection.encode_queries(queries)
+        if self.world == 1:
+            return self.index.search_host(qi, qt, qw, k)
+        if len(queries) == 0:
+            return (np.empty((0, k), np.float32), np.empty((0, k), np.int32), np.empty((0,), np.uint32))
+        t = lambda a, dt: torch.from_numpy(a.astype(dt)).to(self.device)
+        ms, md, mc = self.search_csr(t(qi, np.int64), t(qt, np.int32), t(qw, np.int32), k)
         return ms.cpu().numpy(), md.cpu().numpy(), mc.cpu().numpy().astype(np.uint32)
 
     # -- pyserini surface ---------------------------------------------------------------------------------------

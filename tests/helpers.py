@@ -39,3 +39,22 @@ def random_queries(rng, nq, n_terms, q_len, max_w=400, dup=False, zipf=True):
         indptr.append(indptr[-1] + m)
     cat = lambda xs, dt: (np.concatenate(xs) if xs else np.zeros(0)).astype(dt)
     return np.asarray(indptr, dtype=np.uint64), cat(terms, np.uint32), cat(weights, np.uint32)
+
+
+def python_jsonl_collection(path):
+    """The pure-Python reading of a --sparse_index directory (json.loads + ImpactCollection.from_vectors): the yardstick the
+    native builder (C++ reader + GPU inversion) is compared with."""
+    import glob
+    import json
+    import os
+    from mllm_sparse_retrieval_b200.index import ImpactCollection
+    ids, vecs = [], []
+    for fn in sorted(glob.glob(os.path.join(path, "corpus*.jsonl"))):
+        with open(fn, "r", encoding="utf-8") as f:
+            for line in f:
+                line = line.strip()
+                if line:
+                    obj = json.loads(line)
+                    ids.append(str(obj["id"]))
+                    vecs.append(obj.get("vector") or {})
+    return ImpactCollection.from_vectors(ids, vecs)

@@ -1,11 +1,13 @@
 """CPU tests of the native index builder: libmsr's C++ JSONL reader against the pure-Python
-reader (json.loads + ImpactCollection.from_vectors) on the same files.  No GPU: the inversion runs through NumPy here;
+reader (json.loads + ImpactCollection.from_vectors) on the same files.  No GPU: the inversion runs through NumPy here (host_inversion=True, the explicit opt-in);
 tests/test_builder_gpu.py covers msr_invert_docs."""
 import json
 import os
 
 import numpy as np
 import pytest
+
+from helpers import python_jsonl_collection
 
 
 def _same(a, b):
@@ -34,8 +36,8 @@ def test_native_reader_equals_python_reader_on_tricky_lines(lib_built, tmp_path)
     float / string weights, numeric ids, null and empty vectors, nested extra keys, blank lines."""
     from mllm_sparse_retrieval_b200.index import ImpactCollection
     write_tricky(str(tmp_path))
-    a = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=False, native=False)
-    b = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=False, native=True)
+    a = python_jsonl_collection(str(tmp_path))
+    b = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=False, host_inversion=True)
     _same(a, b)
     assert b.docids == ["10", "100", "9", "abc", "n"]                       # UTF-8 byte order (S8)
     assert dict(zip(b.terms, b.df))["dog"] == 3
@@ -51,12 +53,12 @@ def test_native_reader_equals_python_reader_random(lib_built, tmp_path):
             for i in ids[shard::2]:
                 vec = {vocab[j]: int(rng.integers(-2, 400)) for j in rng.choice(len(vocab), int(rng.integers(0, 40)), replace=False)}
                 f.write(json.dumps({"id": str(i), "content": "", "vector": vec}, ensure_ascii=bool(i % 2)) + "\n")
-    a = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=False, native=False)
-    b = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=False, native=True)
+    a = python_jsonl_collection(str(tmp_path))
+    b = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=False, host_inversion=True)
     _same(a, b)
     # the cache written by the native path reloads to the same collection
-    c = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=True)
-    d = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=True)
+    c = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=True, host_inversion=True)
+    d = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=True, host_inversion=True)
     _same(b, c); _same(c, d)
 
 

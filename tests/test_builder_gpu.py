@@ -4,6 +4,8 @@ import json
 
 import numpy as np
 import pytest
+
+from helpers import python_jsonl_collection
 import torch
 
 pytestmark = pytest.mark.gpu
@@ -73,8 +75,8 @@ def test_jsonl_dir_native_gpu_build_searches_like_python_build(oracle, lib_built
         for i in ids:
             vec = {f"w{j}": int(rng.integers(1, 300)) for j in rng.choice(400, 20, replace=False)}
             f.write(json.dumps({"id": str(i), "content": "", "vector": vec}) + "\n")
-    a = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=False, native=False)
-    b = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=False, native=True)
+    a = python_jsonl_collection(str(tmp_path))
+    b = ImpactCollection.from_jsonl_dir(str(tmp_path), use_cache=False)
     assert a.terms == b.terms and a.docids == b.docids
     np.testing.assert_array_equal(a.indptr, b.indptr); np.testing.assert_array_equal(a.post_docs, b.post_docs)
     np.testing.assert_array_equal(a.post_impacts, b.post_impacts)

@@ -120,13 +120,13 @@ def test_collection_doc_order_and_cache(tmp_path):
     rows = [{"id": "99", "content": "", "vector": {"a": 3, "b": 1}}, {"id": "100", "content": "", "vector": {"a": 2}},
             {"id": "9", "content": "", "vector": {"b c": 4, "": 7}}]
     (d / "corpus_0.jsonl").write_text("\n".join(json.dumps(r) for r in rows) + "\n")
-    coll = ImpactCollection.from_jsonl_dir(str(d))
+    coll = ImpactCollection.from_jsonl_dir(str(d), host_inversion=True)      # no GPU in the CPU suite: explicit opt-in
     assert coll.docids == ["100", "9", "99"]
     a = coll.term_to_id["a"]
     lo, hi = int(coll.indptr[a]), int(coll.indptr[a + 1])
     assert coll.post_docs[lo:hi].tolist() == [0, 2] and coll.post_impacts[lo:hi].tolist() == [2, 3]
     assert set(coll.terms) == {"a", "b", "c"}                          # whitespace-analysed key, empty key dropped
-    again = ImpactCollection.from_jsonl_dir(str(d))                    # served from <dir>/msr_index
+    again = ImpactCollection.from_jsonl_dir(str(d))                    # served from <dir>/msr_index (raw arrays, no GPU needed)
     assert (d / "msr_index" / "meta.json").exists()
     assert again.docids == coll.docids and again.terms == coll.terms
     np.testing.assert_array_equal(again.post_docs, coll.post_docs)
