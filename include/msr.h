@@ -174,6 +174,17 @@ int msr_sparse_set_peer_theta(msr_sparse_index* h, uint32_t n_peers, uint64_t* l
                               uint64_t* const* peer_quant);
 
 /*
+ * Publishing half of the fused exchange for searches whose last kernel does not store into peer slots itself (the dense
+ * flat-IP search; the precedent is FAISS IndexShards behind GpuMultipleClonerOptions.shard, /root/reference/src/search.py:
+ * 265-270): rows [nq,k] (scores f32, docs i32, counts) are copied into dst_*[p] for p < n_dst -- this rank's slot in its own
+ * and in every peer's symmetric buffer -- with 16-byte stores when k % 4 == 0 and the bases are aligned.  Follow it with
+ * msr_topk_merge_exchange.  Replaces three NCCL all-gathers.
+ */
+int msr_exchange_publish(int device, uint32_t nq, uint32_t k, const float* scores, const int32_t* docs, const uint32_t* counts,
+                         uint32_t n_dst, float* const* dst_scores, int32_t* const* dst_docs, uint32_t* const* dst_counts,
+                         void* stream);
+
+/*
  * msr_topk_merge_strided behind the exchange's own one-way barrier (replaces a generic two-phase signal-pad barrier):
  * a one-warp kernel first stores `flag_value` into flag_peers[p][my_rank] on every peer (release, system scope; the kernel
  * that produced this GPU's rows precedes it on `stream`) and waits until flag_local[peer_ranks[p]] >= flag_value for every

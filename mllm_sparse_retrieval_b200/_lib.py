@@ -52,6 +52,7 @@ def _declare(lib):
         "msr_provenance_hist": (I, [I, U32, P, P, ctypes.c_size_t, P, U32, P, P]),
         "msr_topk_merge_strided": (I, [I, U32, U32, U32, P, P, P, ctypes.c_size_t, ctypes.c_size_t, U32, P, P, P, P]),
         "msr_sparse_set_peer_outputs": (I, [P, U32, P, P, P]),
+        "msr_exchange_publish": (I, [I, U32, U32, P, P, P, U32, P, P, P, P]),
         "msr_sparse_set_peer_theta": (I, [P, U32, P, P, U32, U32, U32, P, P]),
         "msr_topk_merge_exchange": (I, [I, U32, U32, U32, P, P, P, ctypes.c_size_t, ctypes.c_size_t, U32, P, P, P, U32, U32, P, P, P,
                                         U32, P]),

@@ -276,7 +276,9 @@ static int dense_search_exact(msr_dense_index* h, uint32_t nq, const float* d_q,
 
 __device__ __forceinline__ float cert_E(float qn, float qe, const float* __restrict__ stats, uint32_t dim) {
     const float xn = stats[0], ex = stats[1], qh = qn + qe;
-    const float slack = ((float)dim * 1.1920929e-7f + 9.5367432e-7f) * qh * (xn + ex);
+    // accumulation slack of BOTH passes: fp32 round-to-nearest on the exact side (dim * 2^-24), and the tensor pass, whose
+    // fp32 accumulation is not documented as round-to-nearest (truncation: up to 2^-23 per add) -- 3 * dim * 2^-24 in all
+    const float slack = ((float)dim * 1.7881393e-7f + 9.5367432e-7f) * qh * (xn + ex);
     return (qe * xn + qh * ex + slack) * 1.0001f;
 }
 
@@ -345,8 +347,9 @@ dense_select_kernel(const uint2* __restrict__ cand, const uint32_t* __restrict__
             ok = true; nc = n;
         } else if (n >= kk) {
             const float a_k = key_score(buf[kk - 1]);
-            const float lim = a_k - 2.f * cert_E(qn[q], qe[q], stats, dim);
-            ok = thr[q] <= lim;                                 // NaN anywhere -> not certified
+            const float E = cert_E(qn[q], qe[q], stats, dim);
+            const float lim = a_k - 2.f * E;
+            ok = isfinite(E) && isfinite(a_k) && thr[q] <= lim;  // NaN / inf anywhere (fp16 overflow of q or x) -> not certified
             if (ok) {
                 uint32_t c = 0;
                 for (uint32_t i = tid; i < n; i += kSelThreads) c += key_score(buf[i]) >= lim ? 1u : 0u;

@@ -177,14 +177,15 @@ __global__ void expand_exclude_kernel(const unsigned long long* __restrict__ c_i
     for (unsigned long long j = lo + threadIdx.x; j < hi; j += blockDim.x) dst[(size_t)r * vocab + c_tok[j]] = -INFINITY;
 }
 // appends the finite expansion entries (already in descending order) behind the row's main entries
-__global__ void expand_append_kernel(const float* __restrict__ es, const int32_t* __restrict__ ed, uint32_t n_expand,
-                                     uint32_t row0, uint32_t n_rows, uint32_t pitch, float* __restrict__ ts,
+__global__ void expand_append_kernel(const float* __restrict__ es, const int32_t* __restrict__ ed, const uint32_t* __restrict__ ec,
+                                     uint32_t n_expand, uint32_t row0, uint32_t n_rows, uint32_t pitch, float* __restrict__ ts,
                                      int32_t* __restrict__ td, uint32_t* __restrict__ cnt) {
     const uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r >= n_rows) return;
     const size_t row = (size_t)row0 + r;
     uint32_t n = cnt[row];
-    for (uint32_t j = 0; j < n_expand && n < pitch; ++j) {
+    const uint32_t have = min(ec[r], n_expand);                 // entries the select really returned (the rest is padding)
+    for (uint32_t j = 0; j < have && n < pitch; ++j) {
         const float v = es[(size_t)r * n_expand + j];
         if (v == -INFINITY) break;
         ts[row * pitch + n] = v;
@@ -197,6 +198,17 @@ __global__ void expand_append_kernel(const float* __restrict__ es, const int32_t
 }  // namespace msr
 
 using namespace msr;
+
+// quantise_map_kernel keeps 2 * pitch words per warp in dynamic shared memory: above 48 KB that needs the opt-in attribute
+static int map_kernel_smem(size_t bytes) {
+    MSR_REQUIRE(bytes <= 200 * 1024, "quantiser: %zu bytes of shared memory per block (entries per row too large)", bytes);
+    static std::atomic<uint64_t> attr_set{0};
+    if (bytes > 48 * 1024 && attr_needed(attr_set)) {
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(quantise_map_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        attr_mark(attr_set);
+    }
+    return MSR_OK;
+}
 
 extern "C" int msr_quantise_topk(int device, uint32_t n_rows, uint32_t vocab, const void* logits, int dtype,
                                  size_t row_stride, uint32_t top, uint32_t vocab_len, const int32_t* token_to_term,
@@ -232,6 +244,7 @@ extern "C" int msr_quantise_topk(int device, uint32_t n_rows, uint32_t vocab, co
         rows = f32; stride = vocab;
     }
     rc = topk_rows_launch(n_rows, vocab, rows, stride, kk, 0, ts, td, tc, s);
+    if (rc == MSR_OK) rc = map_kernel_smem((size_t)4 * 2 * kk * 4);
     if (rc == MSR_OK) {
         const uint32_t wpb = 4;
         quantise_map_kernel<<<(n_rows + wpb - 1) / wpb, wpb * 32, (size_t)wpb * 2 * kk * 4, s>>>(
@@ -317,10 +330,11 @@ extern "C" int msr_quantise_candidates(int device, uint32_t n_rows, uint32_t voc
             count_launch(2);
             rc = topk_rows_launch(nr, vocab, masked, vocab, n_expand, 0, es, ed, ec, s);
             if (rc) break;
-            expand_append_kernel<<<(nr + 127) / 128, 128, 0, s>>>(es, ed, n_expand, r0, nr, pitch, ts, td, tc);
+            expand_append_kernel<<<(nr + 127) / 128, 128, 0, s>>>(es, ed, ec, n_expand, r0, nr, pitch, ts, td, tc);
             count_launch();
         }
     }
+    if (rc == MSR_OK) rc = map_kernel_smem((size_t)4 * 2 * pitch * 4);
     if (rc == MSR_OK) {
         const uint32_t wpb = 4;
         quantise_map_kernel<<<(n_rows + wpb - 1) / wpb, wpb * 32, (size_t)wpb * 2 * pitch * 4, s>>>(

@@ -105,7 +105,7 @@ __device__ __forceinline__ void merge_body(const MergeParams& P, const uint32_t 
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     uint32_t fill = 0;
     __shared__ uint32_t s_total, s_fill, s_hist[256], s_sel[4];
-    __shared__ unsigned long long s_floor;
+    __shared__ unsigned long long s_floor, s_rmin;
     if (tid == 0) {
         s_total = 0; s_fill = 0;
         unsigned long long t = 0;
@@ -117,17 +117,22 @@ __device__ __forceinline__ void merge_body(const MergeParams& P, const uint32_t 
                 t = max(t, m);
             }
         }
-        if (P.mode == 1 && P.sorted_lists && P.n_lists > 1) {
-            const uint32_t r = (P.k + P.n_lists - 1) / P.n_lists;
-            unsigned long long m = ~0ull;
-            for (uint32_t j = 0; j < P.n_lists; ++j) {
-                const size_t ci = P.cnt_list_stride ? (size_t)j * P.cnt_list_stride + q : (size_t)j * P.nq + q;
-                const size_t ro = P.list_stride ? (size_t)j * P.list_stride + (size_t)q * P.stride : ((size_t)j * P.nq + q) * P.stride;
-                m = (min(P.cnts[ci], P.stride) >= r) ? min(m, (unsigned long long)make_key(P.scores[ro + r - 1], (uint32_t)P.docs[ro + r - 1])) : 0ull;
-            }
-            t = max(t, m);
-        }
         s_floor = t;
+        s_rmin = ~0ull;
+    }
+    if (P.mode == 1 && P.sorted_lists && P.n_lists > 1) {
+        // one thread per list (independent loads), smallest r-th key by a shared-memory atomicMin
+        __syncthreads();
+        const uint32_t r = (P.k + P.n_lists - 1) / P.n_lists;
+        for (uint32_t j = tid; j < P.n_lists; j += nthr) {
+            const size_t ci = P.cnt_list_stride ? (size_t)j * P.cnt_list_stride + q : (size_t)j * P.nq + q;
+            const size_t ro = P.list_stride ? (size_t)j * P.list_stride + (size_t)q * P.stride : ((size_t)j * P.nq + q) * P.stride;
+            const unsigned long long x = (min(P.cnts[ci], P.stride) >= r)
+                                             ? (unsigned long long)make_key(P.scores[ro + r - 1], (uint32_t)P.docs[ro + r - 1]) : 0ull;
+            atomicMin(&s_rmin, x);
+        }
+        __syncthreads();
+        if (tid == 0) s_floor = max(s_floor, s_rmin);
     }
     __syncthreads();
     {
@@ -600,6 +605,60 @@ extern "C" int msr_topk_merge_strided(int device, uint32_t n_lists, uint32_t nq,
     P.out_scores = out_scores; P.out_docs = out_docs; P.out_counts = out_counts;
     P.sorted_lists = 1;
     return merge_launch(P, (cudaStream_t)stream);
+}
+
+// rows of a finished local search -> this rank's slot on every GPU of the exchange (16-byte stores when aligned)
+struct PublishParams {
+    uint32_t nq, k, n_dst, vec_ok;
+    const float* scores; const int32_t* docs; const uint32_t* counts;
+    float* dst_scores[kMaxPeers]; int32_t* dst_docs[kMaxPeers]; uint32_t* dst_counts[kMaxPeers];
+};
+__global__ void __launch_bounds__(128)
+exchange_publish_kernel(const PublishParams P) {
+    const uint32_t q = blockIdx.x, tid = threadIdx.x;
+    const size_t row = (size_t)q * P.k;
+    if (P.vec_ok) {
+        const uint32_t nv = P.k >> 2;
+        for (uint32_t i = tid; i < 2 * nv * P.n_dst; i += 128) {
+            const uint32_t v = i % nv, what = (i / nv) & 1u, dst = i / (2 * nv);
+            const uint4 x = reinterpret_cast<const uint4*>(what ? (const void*)(P.docs + row) : (const void*)(P.scores + row))[v];
+            reinterpret_cast<uint4*>(what ? (void*)(P.dst_docs[dst] + row) : (void*)(P.dst_scores[dst] + row))[v] = x;
+        }
+    } else {
+        for (uint32_t r = tid; r < P.k; r += 128) {
+            const float s = P.scores[row + r];
+            const int32_t d = P.docs[row + r];
+            for (uint32_t p = 0; p < P.n_dst; ++p) { P.dst_scores[p][row + r] = s; P.dst_docs[p][row + r] = d; }
+        }
+    }
+    if (tid == 0) {
+        const uint32_t c = P.counts[q];
+        for (uint32_t p = 0; p < P.n_dst; ++p) P.dst_counts[p][q] = c;
+    }
+}
+
+extern "C" int msr_exchange_publish(int device, uint32_t nq, uint32_t k, const float* scores, const int32_t* docs,
+                                    const uint32_t* counts, uint32_t n_dst, float* const* dst_scores, int32_t* const* dst_docs,
+                                    uint32_t* const* dst_counts, void* stream) {
+    MSR_REQUIRE(k >= 1 && k <= MSR_MAX_K, "msr_exchange_publish: k=%u outside [1,%u]", k, MSR_MAX_K);
+    MSR_REQUIRE(n_dst >= 1 && n_dst <= (uint32_t)kMaxPeers, "msr_exchange_publish: 1..%d destinations", kMaxPeers);
+    if (nq == 0) return MSR_OK;
+    MSR_REQUIRE(scores && docs && counts && dst_scores && dst_docs && dst_counts, "msr_exchange_publish: NULL buffer");
+    int rc = use_device(device);
+    if (rc) return rc;
+    PublishParams P{};
+    P.nq = nq; P.k = k; P.n_dst = n_dst; P.scores = scores; P.docs = docs; P.counts = counts;
+    auto al16 = [](const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; };
+    P.vec_ok = (k & 3u) == 0 && al16(scores) && al16(docs);
+    for (uint32_t p = 0; p < n_dst; ++p) {
+        MSR_REQUIRE(dst_scores[p] && dst_docs[p] && dst_counts[p], "msr_exchange_publish: NULL destination %u", p);
+        P.dst_scores[p] = dst_scores[p]; P.dst_docs[p] = dst_docs[p]; P.dst_counts[p] = dst_counts[p];
+        P.vec_ok = P.vec_ok && al16(dst_scores[p]) && al16(dst_docs[p]);
+    }
+    exchange_publish_kernel<<<nq, 128, 0, (cudaStream_t)stream>>>(P);
+    count_launch();
+    MSR_CUDA_CHECK(cudaGetLastError());
+    return MSR_OK;
 }
 
 extern "C" int msr_topk_merge_exchange(int device, uint32_t n_lists, uint32_t nq, uint32_t k_in, const float* scores,

@@ -212,6 +212,18 @@ def topk_merge_exchange(scores_ptr, docs_ptr, counts_ptr, n_lists, nq, k_in, lis
     return out
 
 
+def exchange_publish(scores, docs, counts, dst_scores, dst_docs, dst_counts):
+    """msr_exchange_publish: rows of a finished local search (CUDA tensors f32 / i32 / i32) -> raw device addresses of this
+    rank's slot on every GPU of the exchange."""
+    nq, k = scores.shape
+    di = _dev_index(scores.device)
+    n = len(dst_scores)
+    arr = lambda xs: (ctypes.c_void_p * max(1, n))(*[ctypes.c_void_p(int(x)) for x in xs])
+    with torch.cuda.device(di):
+        check(_lib.load().msr_exchange_publish(di, nq, k, ptr(scores.contiguous()), ptr(docs.contiguous()), ptr(counts.contiguous()), n,
+                                               arr(dst_scores), arr(dst_docs), arr(dst_counts), current_stream_ptr(di)))
+
+
 def topk_rows(scores, k, col_base=0):
     """Radix-select top-k of each row of a CUDA fp32 matrix by (score desc, column asc)."""
     assert scores.is_cuda and scores.dtype == torch.float32 and scores.stride(1) == 1

@@ -179,25 +179,38 @@ class FaissFlatSearcher:
         self.device = dev
         self.rank, self.world = _dist_info(shard)
         self._n_global = 0
+        self._segments = []                       # doc-sharded: (first global id, rows) of every block this rank holds
+        self._row_global = None                   # local row -> global id (device, built on first search)
+        self._px, self._px_failed = {}, False
         self.index = _FlatIPIndex(init_reps.shape[1], dev)
 
     def add(self, p_reps: np.ndarray):
         p_reps = np.asarray(p_reps)
         if self.world > 1:
-            # doc-sharded: this rank keeps rows [lo,hi) of the block being added; ids stay global
+            # doc-sharded (faiss IndexShards behind GpuMultipleClonerOptions.shard, search.py:265-270): of every block
+            # added, this rank keeps rows [lo,hi); local row numbers grow with the global ids, so "smaller id wins"
+            # means the same thing before and after the mapping back
             n = p_reps.shape[0]
             lo, hi = n * self.rank // self.world, n * (self.rank + 1) // self.world
-            if self.index.ntotal == 0:
-                self.index = _FlatIPIndex(p_reps.shape[1], self.device, doc_base=self._n_global + lo)
-            elif self._shard_base_next != self._n_global + lo:
-                raise NotImplementedError("doc-sharded FaissFlatSearcher supports a single add() (the reference "
-                                          "loads one corpus pickle, search.py:228-237)")
             self.index.add(p_reps[lo:hi])
-            self._shard_base_next = self._n_global + hi
-            self._n_global += n
+            self._segments.append((self._n_global + lo, hi - lo))
+            self._row_global = None
         else:
             self.index.add(p_reps)
-            self._n_global += p_reps.shape[0]
+        self._n_global += p_reps.shape[0]
+
+    def _peer_exchange(self, nq, k):
+        kind = os.environ.get("MSR_EXCHANGE", "auto")
+        if kind == "nccl" or self._px_failed:
+            return None
+        px = self._px.get(k)
+        if px is None or px.nq < nq:
+            px = make_peer_exchange(max(nq, 64), k, self.device, self.world, self.rank, kind=kind)
+            if px is None:
+                self._px_failed = True
+                return None
+            self._px[k] = px
+        return px
 
     def search(self, q_reps: np.ndarray, k: int):
         q_reps = np.asarray(q_reps, dtype=np.float32)
@@ -205,16 +218,31 @@ class FaissFlatSearcher:
             return self.index.search(q_reps, k)
         dev = self.device
         kk = min(int(k), ops.MSR_MAX_K)
-        s, ids = self.index.search(torch.from_numpy(q_reps).to(dev), kk)
         nq = q_reps.shape[0]
-        cnt = (ids >= 0).sum(1).to(torch.int32)
-        g_s = torch.empty((self.world, nq, kk), dtype=torch.float32, device=dev)
-        g_d = torch.empty((self.world, nq, kk), dtype=torch.int32, device=dev)
-        g_c = torch.empty((self.world, nq), dtype=torch.int32, device=dev)
-        torch.distributed.all_gather_into_tensor(g_s, s.contiguous())
-        torch.distributed.all_gather_into_tensor(g_d, ids.to(torch.int32).contiguous())
-        torch.distributed.all_gather_into_tensor(g_c, cnt)
-        ms, md, mc = ops.topk_merge(g_s, g_d, g_c, kk)
+        if nq == 0:
+            return np.empty((0, kk), np.float32), np.empty((0, kk), np.int64)
+        if self._row_global is None:
+            self._row_global = torch.cat([torch.arange(g0, g0 + n, dtype=torch.int32, device=dev) for g0, n in self._segments]
+                                         or [torch.zeros(0, dtype=torch.int32, device=dev)])
+        if self.index.ntotal:
+            s, ids = self.index.search(torch.from_numpy(q_reps).to(dev), kk)
+            cnt = (ids >= 0).sum(1).to(torch.int32)
+            gids = self._row_global[ids.clamp(min=0)]           # local row -> global id (indexing only)
+        else:                                                   # this rank holds no rows (fewer docs than ranks)
+            s = torch.zeros((nq, kk), dtype=torch.float32, device=dev)
+            gids = torch.full((nq, kk), -1, dtype=torch.int32, device=dev)
+            cnt = torch.zeros((nq,), dtype=torch.int32, device=dev)
+        px = self._peer_exchange(nq, kk)
+        if px is not None:          # rows stored into every GPU's slot over NVLink, one-warp barrier, merge: no collective call
+            ms, md, mc = px.exchange_rows(s.contiguous(), gids.contiguous(), cnt)
+        else:
+            g_s = torch.empty((self.world, nq, kk), dtype=torch.float32, device=dev)
+            g_d = torch.empty((self.world, nq, kk), dtype=torch.int32, device=dev)
+            g_c = torch.empty((self.world, nq), dtype=torch.int32, device=dev)
+            torch.distributed.all_gather_into_tensor(g_s, s.contiguous())
+            torch.distributed.all_gather_into_tensor(g_d, gids.contiguous())
+            torch.distributed.all_gather_into_tensor(g_c, cnt)
+            ms, md, mc = ops.topk_merge(g_s, g_d, g_c, kk)
         ms, md, mc = ms.cpu().numpy(), md.cpu().numpy().astype(np.int64), mc.cpu().numpy()
         pad = np.arange(kk)[None, :] >= mc[:, None]
         ms[pad] = -3.4028234663852886e38

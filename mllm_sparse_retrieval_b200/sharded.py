@@ -188,6 +188,24 @@ class PeerExchange:
             self._ev[-1][2].record()
         return final
 
+    def exchange_rows(self, scores, docs, counts):
+        """The exchange for a search that is already done (the dense flat-IP search): this rank's rows -- CUDA tensors
+        scores f32 [nq,k], docs i32 [nq,k] (global ids), counts i32 [nq], sorted best-first -- are stored into its slot on
+        every GPU (msr_exchange_publish), then one-warp flag kernel + merge (msr_topk_merge_exchange).  nq <= capacity, the
+        same on every rank.  Returns the merged (scores, docs, counts)."""
+        nq = int(scores.shape[0])
+        assert 0 < nq <= self.nq and scores.shape[1] == self.k
+        par = self.step & 1
+        self.step += 1
+        slots = [self._slot_ptrs(self.ptrs[r], par, self.rank) for r in range(self.world)]
+        ops.exchange_publish(scores, docs, counts, [p[0] for p in slots], [p[1] for p in slots], [p[2] for p in slots])
+        s0, d0, c0 = self._slot_ptrs(self.ptrs[self.rank], par, 0)
+        final = self.final if nq == self.nq else tuple(t[:nq] for t in self.final)
+        ops.topk_merge_exchange(s0, d0, c0, self.world, nq, self.k, self.slot, self.slot, self.k, final, self.device,
+                                self.rank, self.ptrs[self.rank] + 4 * self.flag_off,
+                                [self.ptrs[r] + 4 * self.flag_off for r in self.peers], self.peers, self.step)
+        return final
+
     def phase_ms(self, last=None):
         """(search ms, exchange-merge ms incl. the wait for the slowest peer) averaged over the last ``last`` profiled steps."""
         torch.cuda.synchronize(self.device)

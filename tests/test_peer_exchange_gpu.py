@@ -161,3 +161,52 @@ def test_one_process_drives_two_devices(oracle, lib_built):
         ref_i = np.argsort(-(xq.astype(np.float64) @ x.T.astype(np.float64)), axis=1, kind="stable")[:, :10]
         np.testing.assert_array_equal(np.asarray(di), ref_i)
         D.close()
+
+
+def _dense_worker(rank, world, port, out_path):
+    sys.path.insert(0, ROOT)
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dev = torch.device("cuda", rank)
+    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=dev)
+    try:
+        from mllm_sparse_retrieval_b200.searchers import FaissFlatSearcher
+        rng = np.random.default_rng(5)
+        x1 = rng.standard_normal((700, 128)).astype(np.float32)
+        x2 = rng.standard_normal((301, 128)).astype(np.float32)
+        x2[7] = x1[3]                                                      # an exact tie across the two blocks AND the two shards
+        q = rng.standard_normal((90, 128)).astype(np.float32)
+        res = {}
+        for kind in ("p2p", "nccl"):
+            os.environ["MSR_EXCHANGE"] = kind
+            S = FaissFlatSearcher(x1, shard=True, device=dev)
+            S.add(x1)
+            S.add(x2)                                                      # a second block: the reference's own loop over shards
+            for n, k in ((40, 10), (90, 100), (25, 100)):
+                s, i = S.search(q[:n], k)
+                res[f"{kind}_s{n}_{k}"], res[f"{kind}_i{n}_{k}"] = s, i
+            assert (kind == "p2p") == bool(S._px), "the fused exchange was not the path taken"
+        np.savez(out_path + f".{rank}.npz", **res)
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs with peer access")
+def test_sharded_dense_searcher_uses_fused_exchange(oracle, lib_built, tmp_path):
+    """FaissFlatSearcher(shard=True) on two GPUs, two add() blocks: rows published into peer slots + one-warp barrier + merge
+    == NCCL all-gather + merge == unsharded float64 oracle (ids exact, scores within 1e-3 relative)."""
+    out = str(tmp_path / "dx")
+    mp.spawn(_dense_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    rng = np.random.default_rng(5)
+    x1 = rng.standard_normal((700, 128)).astype(np.float32)
+    x2 = rng.standard_normal((301, 128)).astype(np.float32)
+    x2[7] = x1[3]
+    q = rng.standard_normal((90, 128)).astype(np.float32)
+    x = np.concatenate([x1, x2])
+    for n, k in ((40, 10), (90, 100), (25, 100)):
+        es, ei = oracle.flat_ip_search_numpy(x, q[:n], k)
+        for r in range(2):
+            got = np.load(out + f".{r}.npz")
+            for kind in ("p2p", "nccl"):
+                np.testing.assert_array_equal(got[f"{kind}_i{n}_{k}"], ei)
+                np.testing.assert_allclose(got[f"{kind}_s{n}_{k}"], es, rtol=1e-3, atol=1e-6)
