@@ -679,6 +679,8 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     P.merge_min = std::max(1u, k >> (h->n_tiles <= 24 ? 1 : 2));
     if (const char* e = getenv("MSR_SPARSE_MERGE_SHIFT")) P.merge_min = std::max(1u, k >> (uint32_t)std::min(10, std::max(0, atoi(e))));
     P.fast_select = h->fast_select ? 1u : 0u;
+    P.tile_group = 1;
+    if (const char* e = getenv("MSR_SPARSE_TILE_GROUP")) P.tile_group = (uint32_t)std::min(64, std::max(1, atoi(e)));
     P.wide_q = d_wq; P.n_wide = d_nw; P.wide_first = 0; P.wide_ctas = 0; P.status = h->status;
     P.wide_acc = (unsigned long long*)(base + off_wkeys); P.wide_cnt = (uint32_t*)(base + off_wcnt);
     const size_t smem = search_smem_bytes(h->tile_docs);

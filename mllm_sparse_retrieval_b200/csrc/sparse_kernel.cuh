@@ -62,6 +62,7 @@ struct SearchParams {
     uint32_t use_theta;
     uint32_t merge_min;           // a tile re-publishes the query's threshold list when it adds >= this many candidates
     uint32_t fast_select;         // exact select through the per-thread-maxima bound first (MSR_SPARSE_FAST_SELECT, default 1)
+    uint32_t tile_group;          // tiles whose CTAs are interleaved in the grid (MSR_SPARSE_TILE_GROUP, default 1)
     // Doc-sharded search over several GPUs (msr_sparse_set_peer_theta): theta[] then lives in symmetric memory and every
     // raise is ALSO pushed into the same slot of the other GPUs' arrays (fire-and-forget red.max over NVLink).  A key is
     // (float32 score, GLOBAL doc id), so "at least k docs of the COLLECTION reach theta" holds on every GPU and each shard
@@ -347,9 +348,20 @@ sparse_score_topk_kernel(const SearchParams P) {
         wide_score_cta(P, x / P.n_tiles, x % P.n_tiles);
         return;
     }
-    uint32_t q = blockIdx.x % P.nq + P.q_rot;
+    // Grid order: tiles in groups of tile_group; inside a group the tile index runs fastest, then the query.  With
+    // tile_group = 1 this is plain tile-major order (all CTAs in flight read ONE tile's slice of the index).
+    uint32_t q, tile;
+    if (P.tile_group <= 1) {
+        q = blockIdx.x % P.nq;
+        tile = blockIdx.x / P.nq;
+    } else {
+        const uint32_t per = P.nq * P.tile_group, grp = blockIdx.x / per, rem = blockIdx.x - grp * per;
+        const uint32_t g_cur = min(P.tile_group, P.n_tiles - grp * P.tile_group);
+        q = rem / g_cur;
+        tile = grp * P.tile_group + rem % g_cur;
+    }
+    q += P.q_rot;
     if (q >= P.nq) q -= P.nq;
-    const uint32_t tile = blockIdx.x / P.nq;
     const uint32_t tile_lo = tile * P.tile_docs;
     const uint32_t tl = min(P.tile_docs, P.n_docs - tile_lo);
     const uint64_t qs = P.q_indptr[P.q_lo + q], qe = P.q_indptr[P.q_lo + q + 1];

@@ -63,7 +63,11 @@ class SparseIndex:
             _lib.load().msr_sparse_index_destroy(self._h)
             self._h = None
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:                                       # interpreter shutdown: module globals may be gone already
+            pass
 
     def search(self, q_indptr, q_terms, q_weights, k, out=None):
         """Device path: CUDA tensors (int64 indptr, int32 terms/weights) -> (scores f32, docs i32, counts i32) [nq,k].
@@ -252,7 +256,11 @@ class DenseIndex:
             _lib.load().msr_dense_index_destroy(self._h)
             self._h = None
 
-    __del__ = close
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:                                       # interpreter shutdown: module globals may be gone already
+            pass
 
     @property
     def ntotal(self):
