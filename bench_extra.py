@@ -250,7 +250,7 @@ def run_config5(a, rank, world, local_rank, root, ClockSampler):
     import torch.distributed as dist
     from mllm_sparse_retrieval_b200 import synth
     from mllm_sparse_retrieval_b200.ops import DenseIndex, SparseIndex, fuse_lists, kernel_launches
-    from mllm_sparse_retrieval_b200.sharded import PipelinedExchange
+    from mllm_sparse_retrieval_b200.sharded import PipelinedExchange, make_peer_exchange
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     per_gpu, V, k, H = a.c5_docs_per_gpu, a.vocab, a.k, a.dense_dim
@@ -293,7 +293,12 @@ def run_config5(a, rank, world, local_rank, root, ClockSampler):
     ex_s = PipelinedExchange(qs.nq, k, dev, world, chunks=a.chunks if world > 1 else 1)
     q_chunks = [qs.slice(lo, hi) for lo, hi in ex_s.chunks()]
 
+    # fused exchange over peer memory (shared thresholds, peer stores, one-warp barrier) when it can be set up
+    px = make_peer_exchange(qs.nq, k, dev, world, rank, kind=a.exchange) if (world > 1 and a.chunks == 1) else None
+
     def sparse_step():
+        if px is not None:
+            return px.run(sidx, lambda o: sidx.search(qs.indptr, qs.terms, qs.weights, k, out=o))
         return ex_s.run(lambda i, lo, hi, o: sidx.search(q_chunks[i].indptr, q_chunks[i].terms, q_chunks[i].weights, k, out=o))
 
     # ---- dense shard: generated on the device block by block ----
@@ -317,8 +322,27 @@ def run_config5(a, rank, world, local_rank, root, ClockSampler):
         didx.search(dq[lo:hi], k, mode=0, out=(o[0], o[1]))
         fallback[0] += didx.last_fallback
 
+    # dense exchange: rows published into peer slots after each batch (msr_exchange_publish + one-warp barrier + merge) on
+    # the search's own stream.  (Round 1 overlapped an NCCL all-gather of batch i with the GEMM of batch i+1: the NCCL
+    # kernels took SMs from the persistent one-CTA-per-SM GEMM, whose statically scheduled late CTAs then stretched every
+    # pass from 7.5 to 10.3 ms.)
+    px_d = make_peer_exchange(dbatch, k, dev, world, rank, kind=a.exchange) if world > 1 else None
+    d_final = (torch.empty((a.c5_dense_nq, k), dtype=torch.float32, device=dev), torch.empty((a.c5_dense_nq, k), dtype=torch.int32, device=dev),
+               torch.empty((a.c5_dense_nq,), dtype=torch.int32, device=dev))
+    d_loc = (torch.empty((dbatch, k), dtype=torch.float32, device=dev), torch.empty((dbatch, k), dtype=torch.int64, device=dev))
+    d_cnt = torch.full((dbatch,), k, dtype=torch.int32, device=dev)
+
     def dense_step():
-        return ex_d.run(dense_chunk)
+        if px_d is None:
+            return ex_d.run(dense_chunk)
+        for lo in range(0, a.c5_dense_nq, dbatch):
+            hi = min(a.c5_dense_nq, lo + dbatch)
+            n = hi - lo
+            didx.search(dq[lo:hi], k, mode=0, out=(d_loc[0][:n], d_loc[1][:n]))
+            fallback[0] += didx.last_fallback
+            ms_, md_, mc_ = px_d.exchange_rows(d_loc[0][:n], d_loc[1][:n].to(torch.int32), d_cnt[:n])
+            d_final[0][lo:hi].copy_(ms_); d_final[1][lo:hi].copy_(md_); d_final[2][lo:hi].copy_(mc_)
+        return d_final
     build_s = time.time() - t_build
 
     # ---- timed regions (device-resident inputs; max over ranks) ----
