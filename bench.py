@@ -1,17 +1,24 @@
 #!/usr/bin/env python
 """bench.py -- headline benchmark: sparse top-100 queries/sec on the synthetic 1M-doc vocab-sparse index
-(BASELINE.json configs[3]), doc-sharded over N GPUs with an NCCL all-gather merge.
+(BASELINE.json configs[3]), doc-sharded over N GPUs with the exchange fused into our own kernels.
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P bench.py --gpus N ...
 
-One step = ALL nq queries scored against the whole collection.
+One step = ALL nq queries scored against the whole collection; the steps cycle through rotations of the query order.
   value : queries/sec with the query CSR already resident in HBM (device path of the C ABI), max over ranks.
   e2e   : the same through msr_sparse_search(MSR_HOST): queries in pinned host memory, H2D + D2H inside the timed step.
   roofline : sparse_score_topk_kernel, algorithmic bytes (6 B/posting + 8 B/term + 8 B/result) over the
-             kernel's own CUDA-event time (msr_sparse_profile), against MEASURED_PEAKS.json's HBM copy bandwidth.
-  cpu_baseline : oracle/impact_oracle.c (Lucene-impact restatement, one query per thread, all host cores) on a
-             bounded sample of the same queries.  Real Lucene/pyserini is unavailable on this box (no JVM).
+             kernel's own CUDA-event time (msr_sparse_profile), against MEASURED_PEAKS.json's HBM copy bandwidth;
+             roofline.binding = the kernel's ncu counters over the same time against ceilings measured in this run
+             (msr_microbench): which resource actually binds.
+  parity_check : last timed step (device and e2e) == oracle on 256 random rows; at N > 1 every row == unsharded search.
+  small_batch : latency at the reference's own operating points (nq 1..1024, depth 100 / 1000), L2 flushed.
+  query_construction : encoder logits -> quantiser -> scorer on the device, against the reference's string round trip.
+  extra : short dense (configs[1]) and hybrid (configs[2]) lines.
+  cpu_baseline : the fastest of three CPU ports of the Lucene impact search (oracle/impact_tuned.c, impact_oracle.c; all
+             bit-identical to the oracle), one query per thread on all host cores, bounded sample.  Real Lucene/pyserini
+             is unavailable on this box (no JVM).
 """
 from __future__ import annotations
 
@@ -314,6 +321,67 @@ def measured_ceilings(dev_index):
                    "read with 8-byte ld.global.nc.L1::no_allocate, 8 in flight per thread, 2 x 512 threads per SM; red.shared.add.u32 "
                    "one bank per lane; independent dp4a chains (fma pipe) and PRMT chains (alu pipe), their sum = the issue ceiling; "
                    "conflict-free 16-byte ld.shared (l1tex data-pipe wavefronts)"}
+
+
+def query_construction_line(a, idx, qs, dev):
+    """SURVEY 8(f) row 1 end to end: encoder output -> query -> search.  (i) logits [nq, V] on the device ->
+    msr_quantise_topk -> query CSR -> scorer, nothing leaves the GPU; (ii) what the reference does (search.py:419-422 +
+    pyserini): `' tok' * v` strings built on the host, counted again (Counter(text.split())), then searched through the
+    host path -- on a bounded sample.  The logits are synthetic rows whose top-q_len entries ARE the bench queries
+    (value = weight / 100), so both paths must return the bench's own results."""
+    import torch
+    from collections import Counter
+    from mllm_sparse_retrieval_b200 import ops
+    nq, V, k = qs.nq, a.vocab, a.k
+    lens = torch.diff(qs.indptr)
+    top = int(lens.max())
+    logits = torch.zeros((nq, V), dtype=torch.float16, device=dev)
+    rows = torch.repeat_interleave(torch.arange(nq, device=dev), lens)
+    logits[rows, qs.terms.long()] = (qs.weights.float() / 100).half()
+    t2t = torch.arange(V, dtype=torch.int32, device=dev)
+    out = (torch.empty((nq, k), dtype=torch.float32, device=dev), torch.empty((nq, k), dtype=torch.int32, device=dev),
+           torch.empty((nq,), dtype=torch.int32, device=dev))
+
+    def step():
+        qi, qt, qw = ops.quantise_topk(logits, top, token_to_term=t2t, vocab_len=V)
+        return idx.search(qi, qt, qw, k, out=out)
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(3):
+        step()
+    e1.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / 3
+    ref = idx.search(qs.indptr, qs.terms, qs.weights, k)
+    same = all(torch.equal(x, y) for x, y in zip(out, ref))
+    # the reference's way, bounded sample
+    n_s = min(nq, 256)
+    qi, qt, qw = (x.cpu().numpy() for x in (qs.indptr, qs.terms, qs.weights))
+    t0 = time.perf_counter()
+    texts = []
+    for q in range(n_s):
+        text = ""
+        for j in range(int(qi[q]), int(qi[q + 1])):
+            text += (" t%d" % qt[j]) * int(qw[j])                # query += (' ' + token) * v
+        texts.append(text)
+    hi_, ht_, hw_ = [0], [], []
+    for text in texts:                                            # TokFreqQueryEncoder + dictionary lookup
+        for tok, w in Counter(text.strip().split()).items():
+            ht_.append(int(tok[1:])); hw_.append(w)
+        hi_.append(len(ht_))
+    idx.search_host(np.asarray(hi_, np.uint64), np.asarray(ht_, np.uint32), np.asarray(hw_, np.uint32), k)
+    dt = time.perf_counter() - t0
+    del logits
+    torch.cuda.empty_cache()
+    return {"device_path": {"value": nq / (ms * 1e-3), "unit": UNIT, "ms_per_step": ms,
+                            "what": f"fp16 logits [{nq}, {V}] resident on the GPU -> msr_quantise_topk (top-{top}, rint(x*100), duplicate merge) -> "
+                                    f"msr_sparse_search(MSR_DEVICE); {nq * V * 2 >> 20} MB of activations read per step"},
+            "string_path": {"value": n_s / dt, "unit": UNIT, "sample": f"{n_s} of {nq} queries, {dt:.2f} s, 1 host core: "
+                            "`' tok' * v` strings -> Counter(text.split()) -> msr_sparse_search(MSR_HOST)"},
+            "parity_check": "device-path rows == the bench's own results, bit-exact" if same else "MISMATCH"}
 
 
 def small_batch_lines(a, idx, qs, dev, peak_gbs):
@@ -620,6 +688,8 @@ def run_ours(a, rank, world, local_rank):
         res["small_batch"] = small_batch_lines(a, idx, qs0, dev, peak)
     if world == 1 and not a.no_cpu_baseline:
         res["cpu_baseline"] = cpu_baseline(a, coll_np, a.n_docs, qs0.numpy(), a.cpu_seconds)
+    if world == 1 and not a.no_extra and a.workload == "sparse" and a.nq * a.vocab * 2 <= (8 << 30):
+        res["query_construction"] = query_construction_line(a, idx, qs0, dev)
     if world == 1 and not a.no_extra and a.workload == "sparse" and a.n_docs == 1_000_000:
         # the other kernels of the path, measured in the same driver-visible run (BASELINE.json configs[1] and [2]);
         # the full lines are `bench.py --workload dense|hybrid`
