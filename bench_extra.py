@@ -320,7 +320,6 @@ def run_config5(a, rank, world, local_rank, root, ClockSampler):
 
     def dense_chunk(i, lo, hi, o):
         didx.search(dq[lo:hi], k, mode=0, out=(o[0], o[1]))
-        fallback[0] += didx.last_fallback
 
     # dense exchange: rows published into peer slots after each batch (msr_exchange_publish + one-warp barrier + merge) on
     # the search's own stream.  (Round 1 overlapped an NCCL all-gather of batch i with the GEMM of batch i+1: the NCCL
@@ -339,7 +338,6 @@ def run_config5(a, rank, world, local_rank, root, ClockSampler):
             hi = min(a.c5_dense_nq, lo + dbatch)
             n = hi - lo
             didx.search(dq[lo:hi], k, mode=0, out=(d_loc[0][:n], d_loc[1][:n]))
-            fallback[0] += didx.last_fallback
             ms_, md_, mc_ = px_d.exchange_rows(d_loc[0][:n], d_loc[1][:n].to(torch.int32), d_cnt[:n])
             d_final[0][lo:hi].copy_(ms_); d_final[1][lo:hi].copy_(md_); d_final[2][lo:hi].copy_(mc_)
         return d_final
@@ -366,7 +364,7 @@ def run_config5(a, rank, world, local_rank, root, ClockSampler):
     didx.profile(True)
     ms_dense = timed(dense_step, a.steps, 0)
     tc_ms, rs_ms, n_blk = didx.profile(False)
-    n_fb = fallback[0] // a.steps
+    n_fb = didx.last_fallback                               # uncertified queries of the last batch (device-side counter)
 
     # ---- e2e: pinned host query buffers in, merged lists back to pinned host memory on rank 0 ----
     h_q = tuple(t.cpu().pin_memory() for t in (qs.indptr, qs.terms, qs.weights))

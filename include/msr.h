@@ -229,8 +229,10 @@ int msr_dense_index_info(const msr_dense_index* h, uint32_t info[5]);
  * sides + fp32 accumulation), the docs with a(d) >= a_k - 2E (a_k = k-th best a) provably contain the exact top-k; they
  * are re-scored in fp32 with the accumulation order of mode 1.  A query is certified when its buffer did not overflow,
  * holds >= k docs and the threshold was <= a_k - 2E; uncertified queries are re-run by mode 1.  Both modes therefore
- * return identical ids and bit-identical scores.  Mode 2 (and auto with nq >= 16, n_docs >= 4096) synchronises
- * `stream` inside the call even with MSR_DEVICE.  Needs dim % 8 == 0 (auto falls back to mode 1).
+ * return identical ids and bit-identical scores.  Needs dim % 8 == 0 (auto falls back to mode 1).  With MSR_DEVICE the
+ * call is asynchronous in every mode: the uncertified queries of a query block are listed, re-run and scattered by launches
+ * that take their count from device memory (at most 128 per block; more sets a sticky flag that msr_dense_last_fallback
+ * reports as MSR_ERR_RANGE -- those queries kept their tensor-core rows).  MSR_HOST re-runs any number of them.
  */
 int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* queries, uint32_t k,
                      float* out_scores, int64_t* out_ids, int mode, int where, void* stream);
@@ -241,7 +243,10 @@ int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* queries, uint
  * plus their count, then switches event recording on (enable != 0) or off.  Searches synchronise internally.
  */
 int msr_dense_profile(msr_dense_index* h, int enable, double* tc_ms, double* rescore_ms, uint64_t* launches);
-/* Queries of the last mode-2 (or auto) search on this handle whose certificate failed and that were re-run exactly. */
+/*
+ * Queries of the last mode-2 (or auto) search on this handle whose certificate failed and that were re-run exactly.
+ * Synchronises the device (the device path counts there).  MSR_ERR_RANGE: see msr_dense_search.
+ */
 int msr_dense_last_fallback(const msr_dense_index* h, uint32_t* n);
 /*
  * The tensor-core pass of mode 2 on its own (tests, benchmarks, profiling): out_scores[q*ld + d] =
@@ -310,6 +315,15 @@ int msr_fuse(int device, uint32_t nq,
              uint32_t k_s, const float* s_scores, const int32_t* s_docs, const uint32_t* s_counts,
              const int32_t* self_ids, int remove_query, int dense_f32, double w_dense, double w_sparse,
              double* out_scores, int32_t* out_docs, uint8_t* out_src, uint32_t* out_counts, void* stream);
+/*
+ * msr_fuse for runs whose scores are arbitrary Python floats -- e.g. runs re-read with hybrid.read_trec_run
+ * (/root/reference/src/hybrid.py:8-17), where float('0.1') is not float32(0.1): both score arrays are double and the whole
+ * combination is float64, as the reference computes it on such runs (the dense_f32 = 0 typing of msr_fuse).
+ */
+int msr_fuse_f64(int device, uint32_t nq, uint32_t k_d, const double* d_scores, const int32_t* d_docs,
+                 const uint32_t* d_counts, uint32_t k_s, const double* s_scores, const int32_t* s_docs,
+                 const uint32_t* s_counts, const int32_t* self_ids, int remove_query, double w_dense, double w_sparse,
+                 double* out_scores, int32_t* out_docs, uint8_t* out_src, uint32_t* out_counts, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
  * Index builder: replaces the offline Lucene indexing step of the reference,

@@ -64,6 +64,7 @@ def _declare(lib):
         "msr_recall_hits": (I, [I, U32, P, ctypes.c_size_t, P, P, P, U32, P, P, P, P]),
         "msr_order_rows": (I, [I, U32, U32, P, I, P, P, ctypes.c_size_t, P, P, I, P, P, P, P, P]),
         "msr_fuse": (I, [I, U32, U32, P, P, P, U32, P, P, P, P, I, I, D, D, P, P, P, P, P]),
+        "msr_fuse_f64": (I, [I, U32, U32, P, P, P, U32, P, P, P, P, I, D, D, P, P, P, P, P]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)        # AttributeError if the .so does not export a declared symbol

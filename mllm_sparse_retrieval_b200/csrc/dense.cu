@@ -21,7 +21,8 @@
 
 namespace msr {
 int topk_rows_launch(uint32_t nq, uint32_t n, const float* scores, size_t row_stride, uint32_t k, int32_t col_base,
-                     float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s);
+                     float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s, const uint32_t* nq_dev = nullptr,
+                     uint32_t nq_off = 0);
 }
 
 struct msr_dense_index {
@@ -33,7 +34,9 @@ struct msr_dense_index {
     float* err16 = nullptr;          // [capacity] || v32 - float(v16) ||_2 per row (certificate of mode 2)
     float* stats = nullptr;          // [2] max row norm, max row fp16 error over the whole index (certificate of mode 2)
     msr::Workspace ws;
-    uint32_t last_fallback = 0;      // queries of the last mode-2 search that needed the exact pass
+    uint32_t last_fallback = 0;      // queries of the last mode-2 search that needed the exact pass (host-side view)
+    uint32_t* d_fail = nullptr;      // device: [0] uncertified queries of the last search, [1] != 0: more than one chunk's
+                                     // kDenseFallbackMax of them (device path: the rest kept their uncertified rows)
     // optional per-kernel timing (msr_dense_profile): events bracket the fused GEMM pass and the re-score of every block
     bool profiling = false;
     cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
@@ -46,6 +49,7 @@ namespace msr {
 constexpr int kIpThreads = 256;
 constexpr int kIpWarps = kIpThreads / 32;
 constexpr int kIpQ = 4;              // queries held in shared memory per pass
+constexpr uint32_t kDenseFallbackMax = 128;  // uncertified queries per query block that the device re-runs on its own
 
 // fp32 -> fp16 copy + per-row quantisation error norm (overflow to inf makes the error inf: mode 2 then certifies nothing)
 __global__ void dense_convert_kernel(const float* __restrict__ src, __half* __restrict__ dst,
@@ -82,10 +86,16 @@ __global__ void dense_convert_kernel(const float* __restrict__ src, __half* __re
 // deterministic and independent of nq / batch composition.
 __global__ void __launch_bounds__(kIpThreads)
 dense_ip_exact_kernel(const float* __restrict__ docs, uint32_t n_docs, uint32_t dim, const float* __restrict__ queries,
-                      uint32_t nq, float* __restrict__ scores, size_t row_stride) {
+                      uint32_t nq, float* __restrict__ scores, size_t row_stride, const uint32_t* __restrict__ nq_dev,
+                      uint32_t nq_off) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float* qs = reinterpret_cast<float*>(smem_raw);           // [kIpQ][dim]
+    if (nq_dev) {                                             // the count lives on the device (mode-2 fallback list)
+        const uint32_t have = *nq_dev;
+        nq = min(nq, have > nq_off ? have - nq_off : 0u);
+    }
     const uint32_t q0 = blockIdx.y * kIpQ;
+    if (q0 >= nq) return;
     const uint32_t nqb = min((uint32_t)kIpQ, nq - q0);
     for (uint32_t i = threadIdx.x; i < kIpQ * dim; i += kIpThreads) {
         uint32_t qq = i / dim;
@@ -158,6 +168,11 @@ extern "C" int msr_dense_index_create(int device, uint32_t dim, int32_t doc_base
     msr_dense_index* h = new (std::nothrow) msr_dense_index();
     if (!h) { set_error("msr_dense_index_create: out of host memory"); return MSR_ERR_NOMEM; }
     h->device = device; h->dim = dim; h->doc_base = doc_base;
+    if (cudaMalloc(&h->d_fail, 8) != cudaSuccess || cudaMemset(h->d_fail, 0, 8) != cudaSuccess) {
+        set_error("msr_dense_index_create: device allocation failed");
+        delete h;
+        return MSR_ERR_CUDA;
+    }
     *out = h;
     return MSR_OK;
 }
@@ -165,7 +180,7 @@ extern "C" int msr_dense_index_create(int device, uint32_t dim, int32_t doc_base
 extern "C" int msr_dense_index_destroy(msr_dense_index* h) {
     if (!h) return MSR_OK;
     cudaSetDevice(h->device);
-    cudaFree(h->v32); cudaFree(h->v16); cudaFree(h->err16); cudaFree(h->stats);
+    cudaFree(h->v32); cudaFree(h->v16); cudaFree(h->err16); cudaFree(h->stats); cudaFree(h->d_fail);
     for (cudaEvent_t e : h->ev) if (e) cudaEventDestroy(e);
     h->ws.release();
     delete h;
@@ -227,7 +242,7 @@ namespace msr {
 // Exact pass over queries that are already on the device; writes FAISS-convention outputs [nq,k].
 // scratch holds score rows [qc, n_docs] + top-k staging [qc,kk] (f32, i32) + counts [qc].
 static int dense_search_exact(msr_dense_index* h, uint32_t nq, const float* d_q, uint32_t k, float* d_os, int64_t* d_oi,
-                              unsigned char* scratch, size_t scratch_bytes, cudaStream_t s) {
+                              unsigned char* scratch, size_t scratch_bytes, cudaStream_t s, const uint32_t* nq_dev = nullptr) {
     const uint32_t kk = std::min(k, h->n_docs);
     const size_t row_stride = align_up(h->n_docs, 4);
     const size_t per_q = row_stride * 4 + (size_t)kk * 8 + 4;
@@ -245,11 +260,13 @@ static int dense_search_exact(msr_dense_index* h, uint32_t nq, const float* d_q,
     }
     for (uint32_t q0 = 0; q0 < nq; q0 += qc) {
         const uint32_t n = std::min(qc, nq - q0);
-        dim3 grid(std::min<uint32_t>((h->n_docs + kIpWarps - 1) / kIpWarps, 148 * 8), (n + kIpQ - 1) / kIpQ);
-        dense_ip_exact_kernel<<<grid, kIpThreads, smem, s>>>(h->v32, h->n_docs, h->dim, d_q + (size_t)q0 * h->dim, n, rows, row_stride);
+        // device-counted launches (mode-2 fallback, usually empty) keep the grid small: an empty list then costs ~10 us of
+        // no-op CTAs instead of ~85
+        dim3 grid(std::min<uint32_t>((h->n_docs + kIpWarps - 1) / kIpWarps, nq_dev ? 148 : 148 * 8), (n + kIpQ - 1) / kIpQ);
+        dense_ip_exact_kernel<<<grid, kIpThreads, smem, s>>>(h->v32, h->n_docs, h->dim, d_q + (size_t)q0 * h->dim, n, rows, row_stride, nq_dev, q0);
         count_launch();
         MSR_CUDA_CHECK(cudaGetLastError());
-        int rc = topk_rows_launch(n, h->n_docs, rows, row_stride, kk, h->doc_base, ts, td, tc, s);
+        int rc = topk_rows_launch(n, h->n_docs, rows, row_stride, kk, h->doc_base, ts, td, tc, s, nq_dev, q0);
         if (rc) return rc;
         dense_finish_kernel<<<(unsigned)(((size_t)n * k + 255) / 256), 256, 0, s>>>(ts, td, tc, n, kk, k, d_os + (size_t)q0 * k,
                                                                                    d_oi + (size_t)q0 * k);
@@ -432,16 +449,34 @@ dense_final_kernel(const float* __restrict__ es, const int32_t* __restrict__ can
     }
 }
 
+// P5 (device side): list the uncertified queries of a block (at most kDenseFallbackMax are re-run here), count them
+__global__ void dense_fail_list_kernel(const uint32_t* __restrict__ flags, uint32_t n, uint32_t* __restrict__ gidx,
+                                       uint32_t* __restrict__ n_list, uint32_t* __restrict__ fail, uint32_t cap) {
+    __shared__ uint32_t s_n;
+    if (threadIdx.x == 0) s_n = 0;
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x)
+        if (!flags[i]) { const uint32_t p = atomicAdd(&s_n, 1u); if (p < cap) gidx[p] = i; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        *n_list = min(s_n, cap);
+        if (s_n) atomicAdd(&fail[0], s_n);
+        if (s_n > cap) atomicOr(&fail[1], 1u);
+    }
+}
+
 __global__ void gather_rows_kernel(const float* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t n, uint32_t dim,
-                                   float* __restrict__ dst) {
+                                   float* __restrict__ dst, const uint32_t* __restrict__ n_dev) {
     const uint32_t r = blockIdx.x;
+    if (n_dev) n = min(n, *n_dev);
     if (r >= n) return;
     for (uint32_t i = threadIdx.x; i < dim; i += blockDim.x) dst[(size_t)r * dim + i] = src[(size_t)idx[r] * dim + i];
 }
 __global__ void scatter_results_kernel(const float* __restrict__ s_in, const int64_t* __restrict__ i_in,
                                        const uint32_t* __restrict__ idx, uint32_t n, uint32_t k, float* __restrict__ s_out,
-                                       int64_t* __restrict__ i_out) {
+                                       int64_t* __restrict__ i_out, const uint32_t* __restrict__ n_dev) {
     const uint32_t r = blockIdx.x;
+    if (n_dev) n = min(n, *n_dev);
     if (r >= n) return;
     for (uint32_t j = threadIdx.x; j < k; j += blockDim.x) {
         s_out[(size_t)idx[r] * k + j] = s_in[(size_t)r * k + j];
@@ -462,7 +497,7 @@ struct TcLayout {
     uint32_t nqb, kk, cap, m, stride, r;
     size_t ld_m, exact_bytes;
     size_t o_q16, o_samp, o_ts, o_td, o_tc, o_thr, o_cnt, o_cand, o_cd, o_es, o_ccnt, o_flags, o_qn, o_qe, o_gq, o_gos, o_goi,
-        o_gidx, o_exact, total;
+        o_gidx, o_nlist, o_exact, total;
 };
 
 static TcLayout make_tc_layout(const msr_dense_index* h, uint32_t nq, uint32_t k) {
@@ -499,6 +534,7 @@ static TcLayout make_tc_layout(const msr_dense_index* h, uint32_t nq, uint32_t k
     L.o_qn = take((size_t)nqb * 4); L.o_qe = take((size_t)nqb * 4);
     L.o_gq = take((size_t)nqb * h->dim * 4); L.o_gos = take((size_t)nqb * k * 4); L.o_goi = take((size_t)nqb * k * 8);
     L.o_gidx = take((size_t)nqb * 4);
+    L.o_nlist = take(4);
     L.o_exact = take(L.exact_bytes);
     L.total = o;
     return L;
@@ -507,7 +543,7 @@ static TcLayout make_tc_layout(const msr_dense_index* h, uint32_t nq, uint32_t k
 // Mode 2 over queries already on the device.  Synchronises the stream once per query block (to read the
 // certificate flags); *n_fallback counts the queries that had to be re-run by the exact pass.
 static int dense_search_tc(msr_dense_index* h, uint32_t nq, const float* d_q, uint32_t k, float* d_os, int64_t* d_oi,
-                           unsigned char* base, const TcLayout& L, cudaStream_t s, uint32_t* n_fallback) {
+                           unsigned char* base, const TcLayout& L, cudaStream_t s, uint32_t* n_fallback, bool on_device) {
     std::vector<uint32_t> flags, fail;
     static std::atomic<uint64_t> attr_set{0};
     if (attr_needed(attr_set)) {
@@ -557,6 +593,31 @@ static int dense_search_tc(msr_dense_index* h, uint32_t nq, const float* d_q, ui
                                                                      d_oi + (size_t)q0 * k);
         count_launch(3);
         MSR_CUDA_CHECK(cudaGetLastError());
+        if (on_device) {
+            // MSR_DEVICE stays asynchronous: the uncertified queries are listed, re-run by the exact pass and scattered over
+            // the tensor-core rows by launches that take their count from device memory (an empty list costs four short
+            // launches); at most kDenseFallbackMax per query block -- more sets the sticky flag msr_dense_last_fallback reports
+            uint32_t* gidx = (uint32_t*)(base + L.o_gidx);
+            uint32_t* n_list = (uint32_t*)(base + L.o_nlist);
+            float* gq = (float*)(base + L.o_gq); float* gos = (float*)(base + L.o_gos); int64_t* goi = (int64_t*)(base + L.o_goi);
+            const uint32_t F = std::min(kDenseFallbackMax, n);   // the scratch rows are sized for the block's own queries
+            dense_fail_list_kernel<<<1, 256, 0, s>>>(d_flags, n, gidx, n_list, h->d_fail, F);
+            gather_rows_kernel<<<F, 256, 0, s>>>(q, gidx, F, h->dim, gq, n_list);
+            count_launch(2);
+            rc = dense_search_exact(h, F, gq, k, gos, goi, base + L.o_exact, L.exact_bytes, s, n_list);
+            if (rc) return rc;
+            scatter_results_kernel<<<F, 128, 0, s>>>(gos, goi, gidx, F, k, d_os + (size_t)q0 * k, d_oi + (size_t)q0 * k, n_list);
+            count_launch();
+            MSR_CUDA_CHECK(cudaGetLastError());
+            if (h->profiling) {
+                MSR_CUDA_CHECK(cudaStreamSynchronize(s));
+                float a = 0, b = 0;
+                MSR_CUDA_CHECK(cudaEventElapsedTime(&a, h->ev[0], h->ev[1]));
+                MSR_CUDA_CHECK(cudaEventElapsedTime(&b, h->ev[2], h->ev[3]));
+                h->prof_tc_ms += a; h->prof_rescore_ms += b; h->prof_launches += 1;
+            }
+            continue;
+        }
         flags.resize(n);
         MSR_CUDA_CHECK(cudaMemcpyAsync(flags.data(), d_flags, (size_t)n * 4, cudaMemcpyDeviceToHost, s));
         MSR_CUDA_CHECK(cudaStreamSynchronize(s));
@@ -575,11 +636,11 @@ static int dense_search_tc(msr_dense_index* h, uint32_t nq, const float* d_q, ui
         float* gq = (float*)(base + L.o_gq); float* gos = (float*)(base + L.o_gos); int64_t* goi = (int64_t*)(base + L.o_goi);
         MSR_CUDA_CHECK(cudaMemcpyAsync(gidx, fail.data(), fail.size() * 4, cudaMemcpyHostToDevice, s));
         const uint32_t nf = (uint32_t)fail.size();
-        gather_rows_kernel<<<nf, 256, 0, s>>>(q, gidx, nf, h->dim, gq);
+        gather_rows_kernel<<<nf, 256, 0, s>>>(q, gidx, nf, h->dim, gq, nullptr);
         count_launch();
         rc = dense_search_exact(h, nf, gq, k, gos, goi, base + L.o_exact, L.exact_bytes, s);
         if (rc) return rc;
-        scatter_results_kernel<<<nf, 128, 0, s>>>(gos, goi, gidx, nf, k, d_os + (size_t)q0 * k, d_oi + (size_t)q0 * k);
+        scatter_results_kernel<<<nf, 128, 0, s>>>(gos, goi, gidx, nf, k, d_os + (size_t)q0 * k, d_oi + (size_t)q0 * k, nullptr);
         count_launch();
         MSR_CUDA_CHECK(cudaGetLastError());
         MSR_CUDA_CHECK(cudaStreamSynchronize(s));               // `fail` (pageable) must outlive the copy
@@ -626,7 +687,8 @@ extern "C" int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* qu
     }
     if (use_tc) {
         h->last_fallback = 0;
-        rc = dense_search_tc(h, nq, d_q, k, d_os, d_oi, base, L, s, &h->last_fallback);
+        MSR_CUDA_CHECK(cudaMemsetAsync(h->d_fail, 0, 8, s));
+        rc = dense_search_tc(h, nq, d_q, k, d_os, d_oi, base, L, s, &h->last_fallback, where == MSR_DEVICE);
     } else {
         rc = dense_search_exact(h, nq, d_q, k, d_os, d_oi, base, sb, s);
     }
@@ -677,6 +739,17 @@ extern "C" int msr_dense_profile(msr_dense_index* h, int enable, double* tc_ms, 
 
 extern "C" int msr_dense_last_fallback(const msr_dense_index* h, uint32_t* n) {
     MSR_REQUIRE(h && n, "msr_dense_last_fallback: NULL argument");
-    *n = h->last_fallback;
+    int rc = use_device(h->device);
+    if (rc) return rc;
+    MSR_CUDA_CHECK(cudaDeviceSynchronize());                    // the device path counts on the device
+    uint32_t f[2] = {0, 0};
+    MSR_CUDA_CHECK(cudaMemcpy(f, h->d_fail, 8, cudaMemcpyDeviceToHost));
+    *n = h->last_fallback + f[0];
+    if (f[1]) {
+        set_error("msr_dense_search (device path): more than %u uncertified queries in one query block; the first %u were re-run "
+                  "exactly, the others kept their tensor-core rows -- re-run the batch with mode 1 or through the host path",
+                  kDenseFallbackMax, kDenseFallbackMax);
+        return MSR_ERR_RANGE;
+    }
     return MSR_OK;
 }

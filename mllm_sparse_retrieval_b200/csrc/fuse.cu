@@ -20,8 +20,8 @@ constexpr int kFuseWarps = kFuseThreads / 32;
 
 struct FuseParams {
     uint32_t nq, k_d, k_s, table;            // table = power of two >= 2*k_s
-    const float* d_scores; const int32_t* d_docs; const uint32_t* d_counts;
-    const float* s_scores; const int32_t* s_docs; const uint32_t* s_counts;
+    const void* d_scores; const int32_t* d_docs; const uint32_t* d_counts;     // scores: float, or double (msr_fuse_f64)
+    const void* s_scores; const int32_t* s_docs; const uint32_t* s_counts;
     const int32_t* self_ids;
     int remove_query, dense_f32;
     double w_dense, w_sparse;
@@ -35,38 +35,43 @@ struct FuseSmall {
 
 __device__ __forceinline__ uint32_t hash_doc(uint32_t d) { return d * 2654435761u; }
 
-__device__ __forceinline__ float block_minmax(float v, bool is_max, float* scratch) {
-    // scratch: kFuseWarps floats
+template <typename T>
+__device__ __forceinline__ T block_minmax(T v, bool is_max, T* scratch) {
+    // scratch: kFuseWarps values
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-        float t = __shfl_xor_sync(0xffffffffu, v, o);
-        v = is_max ? fmaxf(v, t) : fminf(v, t);
+        T t = __shfl_xor_sync(0xffffffffu, v, o);
+        v = is_max ? (t > v ? t : v) : (t < v ? t : v);
     }
     __syncthreads();
     if (lane == 0) scratch[warp] = v;
     __syncthreads();
-    float r = scratch[0];
+    T r = scratch[0];
 #pragma unroll
-    for (int w = 1; w < kFuseWarps; ++w) r = is_max ? fmaxf(r, scratch[w]) : fminf(r, scratch[w]);
+    for (int w = 1; w < kFuseWarps; ++w) r = is_max ? (scratch[w] > r ? scratch[w] : r) : (scratch[w] < r ? scratch[w] : r);
     return r;
 }
 
+// T = float: scores as the searchers return them (dense np.float32 or, with dense_f32 = 0, Python floats that are float32
+// values).  T = double (msr_fuse_f64, dense_f32 = 0 only): runs of arbitrary Python floats, e.g. re-read from a TREC file --
+// float('0.1') is not float32(0.1), and the reference combines the doubles it parsed.
+template <typename T>
 __global__ void __launch_bounds__(kFuseThreads)
 fuse_kernel(const FuseParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     FuseSmall* S = reinterpret_cast<FuseSmall*>(smem_raw);
-    float* scratch = reinterpret_cast<float*>(smem_raw + sizeof(FuseSmall));              // kFuseWarps
-    uint32_t* tkeys = reinterpret_cast<uint32_t*>(scratch + kFuseWarps);                  // [table]
+    T* scratch = reinterpret_cast<T*>(smem_raw + sizeof(FuseSmall));                      // kFuseWarps (room for doubles)
+    uint32_t* tkeys = reinterpret_cast<uint32_t*>(smem_raw + sizeof(FuseSmall) + kFuseWarps * 8);   // [table]
     uint32_t* tvals = tkeys + P.table;                                                    // [table]
     uint8_t* matched = reinterpret_cast<uint8_t*>(tvals + P.table);                       // [k_s]
 
     const uint32_t q = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t nd = P.d_counts ? min(P.d_counts[q], P.k_d) : 0;
     const uint32_t ns = P.s_counts ? min(P.s_counts[q], P.k_s) : 0;
-    const float* ds = P.d_scores + (size_t)q * P.k_d;
+    const T* ds = reinterpret_cast<const T*>(P.d_scores) + (size_t)q * P.k_d;
     const int32_t* dd = P.d_docs + (size_t)q * P.k_d;
-    const float* ss = P.s_scores + (size_t)q * P.k_s;
+    const T* ss = reinterpret_cast<const T*>(P.s_scores) + (size_t)q * P.k_s;
     const int32_t* sd = P.s_docs + (size_t)q * P.k_s;
     const int32_t self = (P.remove_query && P.self_ids) ? P.self_ids[q] : -1;
     const uint32_t kout = P.k_d + P.k_s;
@@ -75,14 +80,14 @@ fuse_kernel(const FuseParams P) {
     uint8_t* osrc = P.out_src + (size_t)q * kout;
 
     // 1. min / max over the full lists (0/0 for an empty list)
-    float mn = INFINITY, mx = -INFINITY;
-    for (uint32_t i = tid; i < nd; i += kFuseThreads) { float v = ds[i]; mn = fminf(mn, v); mx = fmaxf(mx, v); }
-    float dmin = block_minmax(mn, false, scratch), dmax = block_minmax(mx, true, scratch);
-    mn = INFINITY; mx = -INFINITY;
-    for (uint32_t i = tid; i < ns; i += kFuseThreads) { float v = ss[i]; mn = fminf(mn, v); mx = fmaxf(mx, v); }
-    float smin = block_minmax(mn, false, scratch), smax = block_minmax(mx, true, scratch);
-    if (nd == 0) { dmin = 0.f; dmax = 0.f; }
-    if (ns == 0) { smin = 0.f; smax = 0.f; }
+    T mn = (T)INFINITY, mx = (T)-INFINITY;
+    for (uint32_t i = tid; i < nd; i += kFuseThreads) { T v = ds[i]; mn = v < mn ? v : mn; mx = v > mx ? v : mx; }
+    T dmin = block_minmax<T>(mn, false, scratch), dmax = block_minmax<T>(mx, true, scratch);
+    mn = (T)INFINITY; mx = (T)-INFINITY;
+    for (uint32_t i = tid; i < ns; i += kFuseThreads) { T v = ss[i]; mn = v < mn ? v : mn; mx = v > mx ? v : mx; }
+    T smin = block_minmax<T>(mn, false, scratch), smax = block_minmax<T>(mx, true, scratch);
+    if (nd == 0) { dmin = 0; dmax = 0; }
+    if (ns == 0) { smin = 0; smax = 0; }
 
     // 2. sparse list -> hash table
     for (uint32_t i = tid; i < P.table; i += kFuseThreads) tkeys[i] = 0xFFFFFFFFu;
@@ -103,7 +108,7 @@ fuse_kernel(const FuseParams P) {
     __syncthreads();
 
     // normalisation constants, typed as the reference computes them
-    const float d_den32 = __fsub_rn(dmax, dmin);
+    const float d_den32 = __fsub_rn((float)dmax, (float)dmin);
     const bool d_den_small = 1e-9 > (double)d_den32;          // Python max(np.float32, 1e-9)
     const float d_den = d_den_small ? (float)1e-9 : d_den32;
     const float wd32 = (float)P.w_dense;                      // weak Python float * np.float32 -> float32
@@ -125,7 +130,7 @@ fuse_kernel(const FuseParams P) {
 #pragma unroll
         for (int w = 0; w < kFuseWarps; ++w) { uint32_t x = S->wsum[w]; if (w < (int)warp) before += x; total += x; }
         if (f) {
-            float sc = __fmul_rn(wd32, __fdiv_rn(__fsub_rn(ds[i], dmin), d_den));
+            float sc = __fmul_rn(wd32, __fdiv_rn(__fsub_rn((float)ds[i], (float)dmin), d_den));
             double sc64 = __dmul_rn(P.w_dense, __ddiv_rn(__dsub_rn((double)ds[i], (double)dmin), d_den64));
             uint8_t src = 1;
             uint32_t slot = hash_doc((uint32_t)doc) & mask;
@@ -182,6 +187,21 @@ fuse_kernel(const FuseParams P) {
 
 using namespace msr;
 
+static int fuse_launch(const FuseParams& P, bool f64, void* stream) {
+    const size_t smem = sizeof(FuseSmall) + kFuseWarps * 8 + (size_t)P.table * 8 + ((P.k_s + 15) & ~15u);
+    static std::atomic<uint64_t> attr_set{0};
+    if (attr_needed(attr_set)) {
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(fuse_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(fuse_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        attr_mark(attr_set);
+    }
+    if (f64) fuse_kernel<double><<<P.nq, kFuseThreads, smem, (cudaStream_t)stream>>>(P);
+    else fuse_kernel<float><<<P.nq, kFuseThreads, smem, (cudaStream_t)stream>>>(P);
+    count_launch();
+    MSR_CUDA_CHECK(cudaGetLastError());
+    return MSR_OK;
+}
+
 extern "C" int msr_fuse(int device, uint32_t nq, uint32_t k_d, const float* d_scores, const int32_t* d_docs,
                         const uint32_t* d_counts, uint32_t k_s, const float* s_scores, const int32_t* s_docs,
                         const uint32_t* s_counts, const int32_t* self_ids, int remove_query, int dense_f32,
@@ -201,14 +221,27 @@ extern "C" int msr_fuse(int device, uint32_t nq, uint32_t k_d, const float* d_sc
     P.s_scores = s_scores; P.s_docs = s_docs; P.s_counts = s_counts;
     P.self_ids = self_ids; P.remove_query = remove_query; P.dense_f32 = dense_f32; P.w_dense = w_dense; P.w_sparse = w_sparse;
     P.out_scores = out_scores; P.out_docs = out_docs; P.out_src = out_src; P.out_counts = out_counts;
-    const size_t smem = sizeof(FuseSmall) + kFuseWarps * 4 + (size_t)P.table * 8 + ((k_s + 15) & ~15u);
-    static std::atomic<uint64_t> attr_set{0};
-    if (attr_needed(attr_set)) {
-        MSR_CUDA_CHECK(cudaFuncSetAttribute(fuse_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        attr_mark(attr_set);
-    }
-    fuse_kernel<<<nq, kFuseThreads, smem, (cudaStream_t)stream>>>(P);
-    count_launch();
-    MSR_CUDA_CHECK(cudaGetLastError());
-    return MSR_OK;
+    return fuse_launch(P, false, stream);
+}
+
+extern "C" int msr_fuse_f64(int device, uint32_t nq, uint32_t k_d, const double* d_scores, const int32_t* d_docs,
+                            const uint32_t* d_counts, uint32_t k_s, const double* s_scores, const int32_t* s_docs,
+                            const uint32_t* s_counts, const int32_t* self_ids, int remove_query, double w_dense,
+                            double w_sparse, double* out_scores, int32_t* out_docs, uint8_t* out_src, uint32_t* out_counts,
+                            void* stream) {
+    MSR_REQUIRE(k_d >= 1 && k_s >= 1 && k_d <= MSR_MAX_K && k_s <= MSR_MAX_K, "msr_fuse_f64: k_d/k_s outside [1,%u]", MSR_MAX_K);
+    if (nq == 0) return MSR_OK;
+    MSR_REQUIRE(d_scores && d_docs && d_counts && s_scores && s_docs && s_counts, "msr_fuse_f64: NULL input");
+    MSR_REQUIRE(out_scores && out_docs && out_src && out_counts, "msr_fuse_f64: NULL output");
+    int rc = use_device(device);
+    if (rc) return rc;
+    FuseParams P{};
+    P.nq = nq; P.k_d = k_d; P.k_s = k_s;
+    P.table = 2;
+    while (P.table < 2 * k_s) P.table <<= 1;
+    P.d_scores = d_scores; P.d_docs = d_docs; P.d_counts = d_counts;
+    P.s_scores = s_scores; P.s_docs = s_docs; P.s_counts = s_counts;
+    P.self_ids = self_ids; P.remove_query = remove_query; P.dense_f32 = 0; P.w_dense = w_dense; P.w_sparse = w_sparse;
+    P.out_scores = out_scores; P.out_docs = out_docs; P.out_src = out_src; P.out_counts = out_counts;
+    return fuse_launch(P, true, stream);
 }

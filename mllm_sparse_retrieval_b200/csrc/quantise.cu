@@ -28,7 +28,8 @@
 namespace msr {
 
 int topk_rows_launch(uint32_t nq, uint32_t n, const float* scores, size_t row_stride, uint32_t k, int32_t col_base,
-                     float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s);
+                     float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s, const uint32_t* nq_dev = nullptr,
+                     uint32_t nq_off = 0);
 
 constexpr int kQuantMaxTop = 1024;
 

@@ -387,6 +387,8 @@ struct RowsParams {
     float* out_scores;
     int32_t* out_docs;
     uint32_t* out_counts;
+    const uint32_t* nq_dev;      // optional: rows [nq_off, *nq_dev) exist (count kept on the device); others are skipped
+    uint32_t nq_off;
 };
 
 struct RowsSmem {
@@ -423,6 +425,7 @@ topk_rows_kernel(const RowsParams P) {
     uint64_t* outk = reinterpret_cast<uint64_t*>(smem_raw + sizeof(RowsSmem));   // pow2_ceil(k) keys
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t q = blockIdx.x;
+    if (P.nq_dev && P.nq_off + q >= *P.nq_dev) return;
     const float* row = P.scores + (size_t)q * P.row_stride;
     const uint32_t n = P.n;
     if (tid == 0) { S->vmax = 0; S->hits = 0; S->out_cnt = 0; S->cand_cnt = 0; }
@@ -549,8 +552,10 @@ topk_rows_kernel(const RowsParams P) {
 }
 
 int topk_rows_launch(uint32_t nq, uint32_t n, const float* scores, size_t row_stride, uint32_t k, int32_t col_base,
-                     float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s) {
+                     float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s, const uint32_t* nq_dev,
+                     uint32_t nq_off) {
     RowsParams P{};
+    P.nq_dev = nq_dev; P.nq_off = nq_off;
     P.nq = nq; P.n = n; P.k = k; P.col_base = col_base; P.scores = scores; P.row_stride = row_stride;
     P.out_scores = out_scores; P.out_docs = out_docs; P.out_counts = out_counts;
     uint32_t n2 = 2;
@@ -701,5 +706,5 @@ extern "C" int msr_topk_rows(int device, uint32_t nq, uint32_t n, const float* s
     MSR_REQUIRE(row_stride >= n, "msr_topk_rows: row_stride < n");
     int rc = use_device(device);
     if (rc) return rc;
-    return topk_rows_launch(nq, n, scores, row_stride, k, col_base, out_scores, out_docs, out_counts, (cudaStream_t)stream);
+    return topk_rows_launch(nq, n, scores, row_stride, k, col_base, out_scores, out_docs, out_counts, (cudaStream_t)stream, nullptr, 0);
 }

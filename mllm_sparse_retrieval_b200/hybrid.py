@@ -65,7 +65,7 @@ def _run_is_f32(run):
     return False
 
 
-def _fuse_two(runs, weights, device):
+def _fuse_two(runs, weights, device, dtype=np.float32):
     dense, sparse = runs
     qids = list(dict.fromkeys(list(dense.keys()) + list(sparse.keys())))
     for qid in qids:
@@ -76,8 +76,8 @@ def _fuse_two(runs, weights, device):
     k_s = max(1, max((len(sparse[q]["docs"]) for q in qids), default=1))
     if k_d > ops.MSR_MAX_K or k_s > ops.MSR_MAX_K:
         raise ValueError(f"run depth above {ops.MSR_MAX_K} is not supported by msr_fuse")
-    d_s = np.zeros((nq, k_d), np.float32); d_d = np.full((nq, k_d), -1, np.int32); d_c = np.zeros(nq, np.int32)
-    s_s = np.zeros((nq, k_s), np.float32); s_d = np.full((nq, k_s), -1, np.int32); s_c = np.zeros(nq, np.int32)
+    d_s = np.zeros((nq, k_d), dtype); d_d = np.full((nq, k_d), -1, np.int32); d_c = np.zeros(nq, np.int32)
+    s_s = np.zeros((nq, k_s), dtype); s_d = np.full((nq, k_s), -1, np.int32); s_c = np.zeros(nq, np.int32)
     names, name_id = [], {}
 
     def intern(doc):
@@ -116,7 +116,10 @@ def _fuse_impl(runs, weights, device=None):
     dense_f32 = _run_is_f32(runs[0])
     if _run_is_f32(runs[1]):
         raise NotImplementedError("the second run must hold Python floats (Lucene hit scores), as in the reference")
-    qids, names, (d_s, d_d, d_c, d_mm), (s_s, s_d, s_c, s_mm) = _fuse_two(runs, weights, dev)
+    # runs of Python floats (e.g. re-read with read_trec_run) are combined from the doubles themselves (msr_fuse_f64):
+    # float('0.1') is not float32(0.1).  np.float32 dense runs keep the float32 / float64 typing of rule H3 (msr_fuse).
+    dt = np.float32 if dense_f32 else np.float64
+    qids, names, (d_s, d_d, d_c, d_mm), (s_s, s_d, s_c, s_mm) = _fuse_two(runs, weights, dev, dt)
     # min/max over the unfiltered lists: re-attach the removed entry (if any) as a trailing list element whose doc
     # id equals the self id, so the kernel's own min/max (taken before removal) reproduces the run dict's values.
     nq = len(qids)
@@ -125,7 +128,7 @@ def _fuse_impl(runs, weights, device=None):
 
     def attach(S, D, C, MM):
         k = S.shape[1]
-        S2 = np.zeros((nq, k + 2), np.float32); D2 = np.full((nq, k + 2), -1, np.int32)
+        S2 = np.zeros((nq, k + 2), dt); D2 = np.full((nq, k + 2), -1, np.int32)
         S2[:, :k] = S; D2[:, :k] = D
         C2 = C.copy()
         for r in range(nq):
@@ -133,7 +136,7 @@ def _fuse_impl(runs, weights, device=None):
             lo = S[r, :n].min() if n else None
             hi = S[r, :n].max() if n else None
             for v, cur, better in ((MM[r, 0], lo, lambda a, b: a < b), (MM[r, 1], hi, lambda a, b: a > b)):
-                if cur is None or better(np.float32(v), np.float32(cur)):
+                if cur is None or better(dt(v), dt(cur)):
                     if n == 0 and v == 0:
                         continue
                     S2[r, C2[r]] = v; D2[r, C2[r]] = sentinel; C2[r] += 1

@@ -336,7 +336,9 @@ class DenseIndex:
 
 def fuse_lists(d_scores, d_docs, d_counts, s_scores, s_docs, s_counts, self_ids, remove_query, w_dense, w_sparse,
                dense_f32=True):
-    """Kernel (d) on CUDA tensors: returns (scores f64 [nq,kd+ks], docs i32, src u8, counts i32)."""
+    """Kernel (d) on CUDA tensors: returns (scores f64 [nq,kd+ks], docs i32, src u8, counts i32).  float32 score tensors go
+    through msr_fuse (rule H3 typing per ``dense_f32``); float64 score tensors -- runs of arbitrary Python floats -- through
+    msr_fuse_f64."""
     nq, k_d = d_scores.shape
     k_s = s_scores.shape[1]
     dev = d_scores.device
@@ -345,6 +347,15 @@ def fuse_lists(d_scores, d_docs, d_counts, s_scores, s_docs, s_counts, self_ids,
            torch.empty((nq, k_d + k_s), dtype=torch.int32, device=dev),
            torch.empty((nq, k_d + k_s), dtype=torch.uint8, device=dev),
            torch.empty((nq,), dtype=torch.int32, device=dev))
+    if d_scores.dtype == torch.float64 or s_scores.dtype == torch.float64:
+        assert d_scores.dtype == s_scores.dtype == torch.float64 and not dense_f32, "float64 runs: both lists, dense_f32=False"
+        with torch.cuda.device(di):
+            check(_lib.load().msr_fuse_f64(di, nq, k_d, ptr(d_scores.contiguous()), ptr(d_docs.contiguous()),
+                                           ptr(d_counts.contiguous()), k_s, ptr(s_scores.contiguous()), ptr(s_docs.contiguous()),
+                                           ptr(s_counts.contiguous()), ptr(self_ids), int(bool(remove_query)), float(w_dense),
+                                           float(w_sparse), ptr(out[0]), ptr(out[1]), ptr(out[2]), ptr(out[3]),
+                                           current_stream_ptr(di)))
+        return out
     with torch.cuda.device(di):
         check(_lib.load().msr_fuse(di, nq, k_d, ptr(d_scores.contiguous()), ptr(d_docs.contiguous()),
                                    ptr(d_counts.contiguous()), k_s, ptr(s_scores.contiguous()), ptr(s_docs.contiguous()),

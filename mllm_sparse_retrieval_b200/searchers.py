@@ -226,6 +226,7 @@ class FaissFlatSearcher:
                                          or [torch.zeros(0, dtype=torch.int32, device=dev)])
         if self.index.ntotal:
             s, ids = self.index.search(torch.from_numpy(q_reps).to(dev), kk)
+            self.index._ix.last_fallback                         # device path: raises if uncertified queries overflowed
             cnt = (ids >= 0).sum(1).to(torch.int32)
             gids = self._row_global[ids.clamp(min=0)]           # local row -> global id (indexing only)
         else:                                                   # this rank holds no rows (fewer docs than ranks)

@@ -230,3 +230,24 @@ def test_search_cli_writes_reference_format_runs(oracle, lib_built, tmp_path):
     exp_counts = oracle.recall_counts(ranked, {q: sorted(qrels[q]) for q in qids})
     assert {k: round(v * len(qids)) for k, v in rec.items()} == exp_counts
     assert n_eval == len(qids)
+
+
+def test_fuse_on_trec_read_runs_is_float64_exact(lib_built, tmp_path):
+    """runs of arbitrary Python floats (re-read with read_trec_run: float('0.1') is not float32(0.1)) are combined
+    from the doubles themselves (msr_fuse_f64) -- bit-exact against the reference's own fuse() on such runs
+    (tests/golden/make_fuse_f64_golden.py)."""
+    from mllm_sparse_retrieval_b200.hybrid import fuse, read_trec_run
+    with open(os.path.join(os.path.dirname(GOLDEN), "reference_fuse_f64.json")) as f:
+        fx = json.load(f)
+    for ci, case in enumerate(fx["cases"]):
+        runs = []
+        for ri, text in enumerate(case["trec"]):
+            p = tmp_path / f"c{ci}_r{ri}.trec"
+            p.write_text(text)
+            runs.append(read_trec_run(str(p)))
+        fused = fuse(runs, [case["alpha"], 1 - case["alpha"]])
+        for qid, exp in case["fused"].items():
+            got = list(fused[qid].items())
+            assert [d for d, _ in got] == [d for d, _ in exp]
+            for (_, gv), (_, ev) in zip(got, exp):
+                assert type(gv) is float and gv == float.fromhex(ev), (ci, qid, gv, float.fromhex(ev))
