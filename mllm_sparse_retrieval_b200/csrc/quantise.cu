@@ -27,6 +27,9 @@
 
 namespace msr {
 
+int topk_rows_launch_typed(int dtype, uint32_t nq, uint32_t n, const void* scores, size_t row_stride, uint32_t k,
+                           int32_t col_base, float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s,
+                           const uint32_t* nq_dev, uint32_t nq_off);
 int topk_rows_launch(uint32_t nq, uint32_t n, const float* scores, size_t row_stride, uint32_t k, int32_t col_base,
                      float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s, const uint32_t* nq_dev = nullptr,
                      uint32_t nq_off = 0);
@@ -228,23 +231,14 @@ extern "C" int msr_quantise_topk(int device, uint32_t n_rows, uint32_t vocab, co
     }
     MSR_REQUIRE(logits && out_terms && out_weights, "msr_quantise_topk: NULL buffer");
     const uint32_t kk = top;
-    // stream-ordered scratch: fp32 rows (when converting), top values / ids / counts
+    // stream-ordered scratch: top values / ids / counts
     AsyncScratch scratch(s);
-    float* f32 = nullptr; float* ts = nullptr; int32_t* td = nullptr; uint32_t* tc = nullptr;
-    if (dtype != 0) MSR_CUDA_CHECK(scratch.alloc(&f32, (size_t)n_rows * vocab * 4));
+    float* ts = nullptr; int32_t* td = nullptr; uint32_t* tc = nullptr;
     MSR_CUDA_CHECK(scratch.alloc(&ts, (size_t)n_rows * top * 4));
     MSR_CUDA_CHECK(scratch.alloc(&td, (size_t)n_rows * top * 4));
     MSR_CUDA_CHECK(scratch.alloc(&tc, (size_t)n_rows * 4));
-    const float* rows = (const float*)logits;
-    size_t stride = row_stride;
-    if (dtype != 0) {
-        const unsigned g = (unsigned)std::min<size_t>(((size_t)n_rows * vocab + 255) / 256, 148 * 32);
-        if (dtype == 1) rows_to_f32_kernel<__half><<<g, 256, 0, s>>>((const __half*)logits, row_stride, n_rows, vocab, f32);
-        else rows_to_f32_kernel<__nv_bfloat16><<<g, 256, 0, s>>>((const __nv_bfloat16*)logits, row_stride, n_rows, vocab, f32);
-        count_launch();
-        rows = f32; stride = vocab;
-    }
-    rc = topk_rows_launch(n_rows, vocab, rows, stride, kk, 0, ts, td, tc, s);
+    // rows are selected in place in their own type (no fp32 staging copy)
+    rc = topk_rows_launch_typed(dtype, n_rows, vocab, logits, row_stride, kk, 0, ts, td, tc, s, nullptr, 0);
     if (rc == MSR_OK) rc = map_kernel_smem((size_t)4 * 2 * kk * 4);
     if (rc == MSR_OK) {
         const uint32_t wpb = 4;

@@ -5,6 +5,9 @@
 //    (float32 score desc, doc id asc): rounds of "append lists, bitonic-sort in shared memory, keep k".
 //  * topk_rows_kernel: radix-select (11-bit digits on the distance to the row maximum) over a dense fp32 score
 //    row with the same deterministic tie-break; used by the dense path's exact pass and exposed as msr_topk_rows.
+#include <cuda_bf16.h>
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace msr {
@@ -382,7 +385,7 @@ constexpr int kRowCandMax = 1024;
 struct RowsParams {
     uint32_t nq, n, k;
     int32_t col_base;
-    const float* scores;
+    const void* scores;          // rows of float, __half or __nv_bfloat16 (kernel template); row_stride in elements
     size_t row_stride;
     float* out_scores;
     int32_t* out_docs;
@@ -418,6 +421,13 @@ __device__ __forceinline__ uint32_t rows_block_excl_scan(uint32_t v, uint32_t* w
 // key 0 is reserved for "not a candidate" (-inf / NaN are never returned)
 __device__ __forceinline__ uint32_t row_key(float x) { return (x > -INFINITY) ? f2ord(x) : 0u; }
 
+// rows are read in place in their own type: fp16 / bf16 activation rows of the quantiser need no fp32 staging copy
+// (2.6 GB read + 5.2 GB written + 5.2 GB per select pass at 10 K x 131 072), and a 256 KB row stays in L2 between the passes
+__device__ __forceinline__ float row_load(const float* r, uint32_t i) { return r[i]; }
+__device__ __forceinline__ float row_load(const __half* r, uint32_t i) { return __half2float(r[i]); }
+__device__ __forceinline__ float row_load(const __nv_bfloat16* r, uint32_t i) { return __bfloat162float(r[i]); }
+
+template <typename T>
 __global__ void __launch_bounds__(kRowThreads)
 topk_rows_kernel(const RowsParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -426,14 +436,14 @@ topk_rows_kernel(const RowsParams P) {
     const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const uint32_t q = blockIdx.x;
     if (P.nq_dev && P.nq_off + q >= *P.nq_dev) return;
-    const float* row = P.scores + (size_t)q * P.row_stride;
+    const T* row = reinterpret_cast<const T*>(P.scores) + (size_t)q * P.row_stride;
     const uint32_t n = P.n;
     if (tid == 0) { S->vmax = 0; S->hits = 0; S->out_cnt = 0; S->cand_cnt = 0; }
     __syncthreads();
     {
         uint32_t m = 0, h = 0;
         for (uint32_t i = tid; i < n; i += kRowThreads) {
-            uint32_t kx = row_key(row[i]);
+            uint32_t kx = row_key(row_load(row, i));
             m = max(m, kx);
             h += (kx != 0);
         }
@@ -452,7 +462,7 @@ topk_rows_kernel(const RowsParams P) {
     __syncthreads();
     if (hits > 0 && hits <= P.k) {
         for (uint32_t i = tid; i < n; i += kRowThreads) {
-            float x = row[i];
+            float x = row_load(row, i);
             if (row_key(x)) outk[atomicAdd(&S->out_cnt, 1u)] = make_key(x, (uint32_t)(P.col_base + (int32_t)i));
         }
     } else if (hits > 0) {
@@ -463,7 +473,7 @@ topk_rows_kernel(const RowsParams P) {
             for (uint32_t i = tid; i < kRowBins; i += kRowThreads) S->hist[i] = 0;
             __syncthreads();
             for (uint32_t i = tid; i < n; i += kRowThreads) {
-                uint32_t kx = row_key(row[i]);
+                uint32_t kx = row_key(row_load(row, i));
                 if (kx) {
                     uint32_t d = kmax - kx;
                     uint32_t hi = sh_prev >= 32 ? 0u : (d >> sh_prev);
@@ -495,7 +505,7 @@ topk_rows_kernel(const RowsParams P) {
         const uint32_t n_def = kq - remaining;
         const bool collect = cand_count <= (uint32_t)kRowCandMax;
         for (uint32_t i = tid; i < n; i += kRowThreads) {
-            float xv = row[i];
+            float xv = row_load(row, i);
             uint32_t kx = row_key(xv);
             if (kx) {
                 uint32_t d = kmax - kx;
@@ -511,7 +521,7 @@ topk_rows_kernel(const RowsParams P) {
             bitonic_sort_desc(S->cand, n2);
             for (uint32_t r = tid; r < remaining; r += kRowThreads) {
                 uint32_t i = (uint32_t)(~S->cand[r]);
-                outk[n_def + r] = make_key(row[i], (uint32_t)(P.col_base + (int32_t)i));
+                outk[n_def + r] = make_key(row_load(row, i), (uint32_t)(P.col_base + (int32_t)i));
             }
         } else {
             const uint32_t per = ((n + kRowWarps - 1) / kRowWarps + 31) & ~31u;
@@ -519,7 +529,7 @@ topk_rows_kernel(const RowsParams P) {
             uint32_t c = 0;
             for (uint32_t base = lo; base < hi; base += 32) {
                 uint32_t i = base + lane;
-                uint32_t kx = i < hi ? row_key(row[i]) : 0;
+                uint32_t kx = i < hi ? row_key(row_load(row, i)) : 0;
                 bool f = kx && (kmax - kx) == pref;
                 c += __popc(__ballot_sync(0xffffffffu, f));
             }
@@ -530,7 +540,7 @@ topk_rows_kernel(const RowsParams P) {
             for (uint32_t w2 = 0; w2 < warp; ++w2) run += S->wsum[w2];
             for (uint32_t base = lo; base < hi; base += 32) {
                 uint32_t i = base + lane;
-                float xv = i < hi ? row[i] : 0.f;
+                float xv = i < hi ? row_load(row, i) : 0.f;
                 uint32_t kx = i < hi ? row_key(xv) : 0;
                 bool f = kx && (kmax - kx) == pref;
                 uint32_t b = __ballot_sync(0xffffffffu, f);
@@ -551,9 +561,20 @@ topk_rows_kernel(const RowsParams P) {
     if (tid == 0) P.out_counts[q] = kq;
 }
 
+int topk_rows_launch_typed(int dtype, uint32_t nq, uint32_t n, const void* scores, size_t row_stride, uint32_t k,
+                           int32_t col_base, float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s,
+                           const uint32_t* nq_dev, uint32_t nq_off);
+
 int topk_rows_launch(uint32_t nq, uint32_t n, const float* scores, size_t row_stride, uint32_t k, int32_t col_base,
                      float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s, const uint32_t* nq_dev,
                      uint32_t nq_off) {
+    return topk_rows_launch_typed(0, nq, n, scores, row_stride, k, col_base, out_scores, out_docs, out_counts, s, nq_dev, nq_off);
+}
+
+// dtype: 0 = f32, 1 = f16, 2 = bf16 (the numbering of msr_quantise_topk)
+int topk_rows_launch_typed(int dtype, uint32_t nq, uint32_t n, const void* scores, size_t row_stride, uint32_t k,
+                           int32_t col_base, float* out_scores, int32_t* out_docs, uint32_t* out_counts, cudaStream_t s,
+                           const uint32_t* nq_dev, uint32_t nq_off) {
     RowsParams P{};
     P.nq_dev = nq_dev; P.nq_off = nq_off;
     P.nq = nq; P.n = n; P.k = k; P.col_base = col_base; P.scores = scores; P.row_stride = row_stride;
@@ -563,11 +584,15 @@ int topk_rows_launch(uint32_t nq, uint32_t n, const float* scores, size_t row_st
     const size_t smem = sizeof(RowsSmem) + (size_t)n2 * 8;
     static std::atomic<uint64_t> attr_set{0};
     if (attr_needed(attr_set)) {
-        MSR_CUDA_CHECK(cudaFuncSetAttribute(topk_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            (int)(sizeof(RowsSmem) + MSR_MAX_K * 8)));
+        const int mx = (int)(sizeof(RowsSmem) + MSR_MAX_K * 8);
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(topk_rows_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(topk_rows_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(topk_rows_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
         attr_mark(attr_set);
     }
-    topk_rows_kernel<<<nq, kRowThreads, smem, s>>>(P);
+    if (dtype == 1) topk_rows_kernel<__half><<<nq, kRowThreads, smem, s>>>(P);
+    else if (dtype == 2) topk_rows_kernel<__nv_bfloat16><<<nq, kRowThreads, smem, s>>>(P);
+    else topk_rows_kernel<float><<<nq, kRowThreads, smem, s>>>(P);
     count_launch();
     MSR_CUDA_CHECK(cudaGetLastError());
     return MSR_OK;
