@@ -521,7 +521,7 @@ static TcLayout make_tc_layout(const msr_dense_index* h, uint32_t nq, uint32_t k
     const size_t per_q = (size_t)h->dim * 2 + L.ld_m * 4 + (size_t)L.r * 8 + (size_t)cap * 16 + (size_t)h->dim * 4 + (size_t)k * 12 + 64;
     uint32_t nqb = (uint32_t)std::min<size_t>(nq, std::max<size_t>(128, ((size_t)3 << 30) / per_q / 128 * 128));
     L.nqb = nqb;
-    L.exact_bytes = dense_scratch_bytes(h, std::min<uint32_t>(nqb, 64), k);
+    L.exact_bytes = dense_scratch_bytes(h, std::min<uint32_t>(nqb, kDenseFallbackMax), k);   // one pass for a full fallback list
     size_t o = 0;
     auto take = [&](size_t bytes) { size_t at = o; o = align_up(o + bytes, 256); return at; };
     L.o_q16 = take((size_t)nqb * h->dim * 2);

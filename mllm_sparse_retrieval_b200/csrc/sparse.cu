@@ -455,7 +455,7 @@ extern "C" int msr_sparse_index_build(int device, uint32_t n_docs, uint32_t n_te
         cudaMemsetAsync(h->dense_rows, 0, (size_t)h->n_dense * h->dense_stride * 2 + (size_t)kThreads * 16 + 1024, s);
         // the kernel loads two slots per thread, the second kThreads slots further on, without a bounds test (the
         // values are dropped): keep those loads inside the allocations
-        const size_t pad8 = (size_t)kThreads * 8 + 512, pad16 = (size_t)kThreads * 16 + 1024;
+        const size_t pad8 = (size_t)kThreads * 8 + 512;
         if ((e = cudaMalloc(&h->dense_rows8, (size_t)h->n_dense * h->dense_stride + pad8)) != cudaSuccess) return fail("alloc dense rows (u8)");
         cudaMemsetAsync(h->dense_rows8, 0, (size_t)h->n_dense * h->dense_stride + pad8, s);
         if ((e = cudaMalloc(&h->dense_cursor, (size_t)h->n_dense * n_tiles * 4)) != cudaSuccess) return fail("alloc dense cursor");
@@ -679,8 +679,6 @@ extern "C" int msr_sparse_search(msr_sparse_index* h, uint32_t nq, const uint64_
     P.merge_min = std::max(1u, k >> (h->n_tiles <= 24 ? 1 : 2));
     if (const char* e = getenv("MSR_SPARSE_MERGE_SHIFT")) P.merge_min = std::max(1u, k >> (uint32_t)std::min(10, std::max(0, atoi(e))));
     P.fast_select = h->fast_select ? 1u : 0u;
-    P.tile_group = 1;
-    if (const char* e = getenv("MSR_SPARSE_TILE_GROUP")) P.tile_group = (uint32_t)std::min(64, std::max(1, atoi(e)));
     P.wide_q = d_wq; P.n_wide = d_nw; P.wide_first = 0; P.wide_ctas = 0; P.status = h->status;
     P.wide_acc = (unsigned long long*)(base + off_wkeys); P.wide_cnt = (uint32_t*)(base + off_wcnt);
     const size_t smem = search_smem_bytes(h->tile_docs);
