@@ -260,9 +260,9 @@ static int dense_search_exact(msr_dense_index* h, uint32_t nq, const float* d_q,
     }
     for (uint32_t q0 = 0; q0 < nq; q0 += qc) {
         const uint32_t n = std::min(qc, nq - q0);
-        // device-counted launches (mode-2 fallback, usually empty) keep the grid small: an empty list then costs ~10 us of
+        // device-counted launches (mode-2 fallback, usually empty) keep the grid small: an empty list then costs a few us of
         // no-op CTAs instead of ~85
-        dim3 grid(std::min<uint32_t>((h->n_docs + kIpWarps - 1) / kIpWarps, nq_dev ? 148 : 148 * 8), (n + kIpQ - 1) / kIpQ);
+        dim3 grid(std::min<uint32_t>((h->n_docs + kIpWarps - 1) / kIpWarps, nq_dev ? 37 : 148 * 8), (n + kIpQ - 1) / kIpQ);
         dense_ip_exact_kernel<<<grid, kIpThreads, smem, s>>>(h->v32, h->n_docs, h->dim, d_q + (size_t)q0 * h->dim, n, rows, row_stride, nq_dev, q0);
         count_launch();
         MSR_CUDA_CHECK(cudaGetLastError());
