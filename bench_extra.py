@@ -316,7 +316,6 @@ def run_config5(a, rank, world, local_rank, root, ClockSampler):
     ex_d = PipelinedExchange(a.c5_dense_nq, k, dev, world, chunks=max(1, a.c5_dense_nq // dbatch), min_chunk=dbatch,
                              id_dtype=torch.int64)
     ex_d.local[2].fill_(k)
-    fallback = [0]
 
     def dense_chunk(i, lo, hi, o):
         didx.search(dq[lo:hi], k, mode=0, out=(o[0], o[1]))
@@ -360,11 +359,19 @@ def run_config5(a, rank, world, local_rank, root, ClockSampler):
     clocks = sampler.stop(t0, t1) if rank == 0 else None
     dense_step()
     dense_step()
-    fallback[0] = 0
     didx.profile(True)
     ms_dense = timed(dense_step, a.steps, 0)
     tc_ms, rs_ms, n_blk = didx.profile(False)
-    n_fb = didx.last_fallback                               # uncertified queries of the last batch (device-side counter)
+    # uncertified queries of one whole step, summed over every batch and every rank (outside the timed region: reading the
+    # device-side counter synchronises).  One of them re-reads a rank's whole fp32 shard and every rank waits for it.
+    n_fb = 0
+    for lo in range(0, a.c5_dense_nq, dbatch):
+        didx.search(dq[lo:min(a.c5_dense_nq, lo + dbatch)], k, mode=0)
+        n_fb += didx.last_fallback
+    if world > 1:
+        t_fb = torch.tensor([n_fb], dtype=torch.int64, device=dev)
+        dist.all_reduce(t_fb, op=dist.ReduceOp.SUM)
+        n_fb = int(t_fb.item())
 
     # ---- e2e: pinned host query buffers in, merged lists back to pinned host memory on rank 0 ----
     h_q = tuple(t.cpu().pin_memory() for t in (qs.indptr, qs.terms, qs.weights))

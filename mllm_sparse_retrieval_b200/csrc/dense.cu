@@ -94,16 +94,18 @@ dense_ip_exact_kernel(const float* __restrict__ docs, uint32_t n_docs, uint32_t 
         const uint32_t have = *nq_dev;
         nq = min(nq, have > nq_off ? have - nq_off : 0u);
     }
-    const uint32_t q0 = blockIdx.y * kIpQ;
-    if (q0 >= nq) return;
+    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool vec = (dim & 3) == 0;
+    // groups of kIpQ queries: one per blockIdx.y, or (device-counted launches: gridDim.y == 1) all of them in turn, so that an
+    // empty list costs one wave of no-op CTAs and a listed query still gets the whole chip's bandwidth
+    for (uint32_t q0 = blockIdx.y * kIpQ; q0 < nq; q0 += gridDim.y * kIpQ) {
     const uint32_t nqb = min((uint32_t)kIpQ, nq - q0);
+    __syncthreads();                                          // the previous group's queries are no longer read
     for (uint32_t i = threadIdx.x; i < kIpQ * dim; i += kIpThreads) {
         uint32_t qq = i / dim;
         qs[i] = qq < nqb ? queries[(size_t)(q0 + qq) * dim + (i - qq * dim)] : 0.f;
     }
     __syncthreads();
-    const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const bool vec = (dim & 3) == 0;
     for (uint32_t row = blockIdx.x * kIpWarps + warp; row < n_docs; row += gridDim.x * kIpWarps) {
         const float* d = docs + (size_t)row * dim;
         float acc[kIpQ];
@@ -138,6 +140,7 @@ dense_ip_exact_kernel(const float* __restrict__ docs, uint32_t n_docs, uint32_t 
             for (int j = 1; j < kIpQ; ++j) if ((int)lane == j) v = acc[j];
             scores[(size_t)(q0 + lane) * row_stride + row] = v;
         }
+    }
     }
 }
 
@@ -260,9 +263,9 @@ static int dense_search_exact(msr_dense_index* h, uint32_t nq, const float* d_q,
     }
     for (uint32_t q0 = 0; q0 < nq; q0 += qc) {
         const uint32_t n = std::min(qc, nq - q0);
-        // device-counted launches (mode-2 fallback, usually empty) keep the grid small: an empty list then costs a few us of
-        // no-op CTAs instead of ~85
-        dim3 grid(std::min<uint32_t>((h->n_docs + kIpWarps - 1) / kIpWarps, nq_dev ? 37 : 148 * 8), (n + kIpQ - 1) / kIpQ);
+        // device-counted launches (mode-2 fallback, usually empty): ONE grid row that walks the listed query groups itself --
+        // an empty list is one wave of no-op CTAs, a listed query is answered at the full width of the chip
+        dim3 grid(std::min<uint32_t>((h->n_docs + kIpWarps - 1) / kIpWarps, 148 * 8), nq_dev ? 1 : (n + kIpQ - 1) / kIpQ);
         dense_ip_exact_kernel<<<grid, kIpThreads, smem, s>>>(h->v32, h->n_docs, h->dim, d_q + (size_t)q0 * h->dim, n, rows, row_stride, nq_dev, q0);
         count_launch();
         MSR_CUDA_CHECK(cudaGetLastError());
@@ -515,7 +518,13 @@ static TcLayout make_tc_layout(const msr_dense_index* h, uint32_t nq, uint32_t k
         L.m = std::min<uint32_t>(N, std::min<uint32_t>(65536, std::max<uint32_t>(2048, N / 16)));
         L.stride = N / L.m;
         const double lam = (double)L.kk * L.m / N;
-        L.r = (uint32_t)std::min<double>(std::ceil(lam + 4.0 * std::sqrt(lam) + 2.0), (double)std::min<uint32_t>(L.m, MSR_MAX_K));
+        // rank of the sample that estimates the threshold: the sample holds Poisson(lam) of the true top-k, and the estimate
+        // is too high (query re-run by the exact pass, which reads the whole fp32 index) when it holds r or more.  4 sigma
+        // leaves ~2e-5 per query -- one re-run per step over 8 GPUs x 4096 queries at config 5, 3 ms each, and every GPU
+        // waits for it -- so take 6 sigma (~1e-9) where the expected survivor count r * N / m stays below a quarter of cap.
+        const double r4 = std::ceil(lam + 4.0 * std::sqrt(lam) + 2.0), r6 = std::ceil(lam + 6.0 * std::sqrt(lam) + 4.0);
+        const double r_cap = std::floor((double)cap / 4.0 * L.m / N);
+        L.r = (uint32_t)std::min<double>(std::max(r4, std::min(r6, r_cap)), (double)std::min<uint32_t>(L.m, MSR_MAX_K));
     }
     L.ld_m = align_up(std::max<uint32_t>(L.m, 4), 4);
     const size_t per_q = (size_t)h->dim * 2 + L.ld_m * 4 + (size_t)L.r * 8 + (size_t)cap * 16 + (size_t)h->dim * 4 + (size_t)k * 12 + 64;
