@@ -255,6 +255,25 @@ int msr_dense_last_fallback(const msr_dense_index* h, uint32_t* n);
  */
 int msr_dense_tc_scores(msr_dense_index* h, uint32_t nq, const float* queries, float* out_scores, size_t ld,
                         void* stream);
+/*
+ * msr_dense_search(mode 1, MSR_DEVICE) for callers that may not allocate.  NO COUNTERPART IN THE REFERENCE: added
+ * for code under CUDA graph capture, tight serving loops and harnesses that forbid
+ * cudaMalloc.  msr_dense_search keeps its score rows and top-k staging in the handle's grow-only workspace (cudaMalloc on
+ * first use and on growth); this entry point calls no cudaMalloc / cudaFree / allocating library routine: its scratch is
+ * a file-scope `static __device__` array of MSR_STATIC_SCRATCH_BYTES inside libmsr.so, which every GPU that loads the
+ * library holds until the process exits (its device address is taken once per device with cudaGetSymbolAddress).
+ * Same arguments, same kernels and therefore the same ids and bit-identical scores as mode 1: queries [nq,dim] fp32,
+ * out_scores fp32 [nq,k], out_ids int64 [nq,k], all DEVICE pointers; asynchronous on `stream`.
+ * Limit: four score rows + their staging must fit, (4*ceil4(n_docs) + 8*min(k,n_docs) + 4) * 4 + 4096 <=
+ * MSR_STATIC_SCRATCH_BYTES, i.e. n_docs <= ~2.09 M at k = 100; beyond it the call returns MSR_ERR_INVALID with the sizes
+ * in msr_last_error() and launches nothing.  Any nq (queries are taken in passes of as many rows as fit).
+ * Every call on a GPU shares the one array and finds the last call's contents in it: nothing is read before the call has
+ * written it and the count words are cleared first, so calls in stream order are independent -- but two calls that
+ * OVERLAP on the same GPU (different streams, no ordering between them) race on it and return garbage.
+ */
+#define MSR_STATIC_SCRATCH_BYTES (32u << 20)
+int msr_dense_search_static(msr_dense_index* h, uint32_t nq, const float* queries, uint32_t k, float* out_scores,
+                            int64_t* out_ids, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------------
  * On-device query / document vector construction.

@@ -47,6 +47,7 @@ def _declare(lib):
         "msr_dense_profile": (I, [P, I, ctypes.POINTER(D), ctypes.POINTER(D), ctypes.POINTER(U64)]),
         "msr_dense_last_fallback": (I, [P, ctypes.POINTER(U32)]),
         "msr_dense_tc_scores": (I, [P, U32, P, P, ctypes.c_size_t, P]),
+        "msr_dense_search_static": (I, [P, U32, P, U32, P, P, P]),
         "msr_quantise_topk": (I, [I, U32, U32, P, I, ctypes.c_size_t, U32, U32, P, I, P, P, P, P]),
         "msr_quantise_candidates": (I, [I, U32, U32, P, I, ctypes.c_size_t, P, P, U32, U32, U32, P, I, P, U32, P, P, P, P]),
         "msr_provenance_hist": (I, [I, U32, P, P, ctypes.c_size_t, P, U32, P, P]),

@@ -762,3 +762,74 @@ extern "C" int msr_dense_last_fallback(const msr_dense_index* h, uint32_t* n) {
     }
     return MSR_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// msr_dense_search_static: the exact pass (mode 1, device pointers) for callers that may not allocate
+// ---------------------------------------------------------------------------------------------------------
+// No counterpart in the reference.  Callers under CUDA graph capture, in a
+// tight serving loop or in a harness that forbids cudaMalloc cannot use msr_dense_search, whose score rows and top-k
+// staging live in the handle's grow-only workspace (Workspace::reserve = cudaMalloc on first use and on growth).  Here the
+// same scratch is a file-scope device array of MSR_STATIC_SCRATCH_BYTES: every GPU that loads libmsr.so holds it until
+// the process exits, every call on that GPU shares it, and it keeps the last call's contents.
+//
+// In host code `g_static_scratch` is only a host-side stand-in for the symbol, NOT a device address: its device address is
+// asked for once per device, with that device current (cudaGetSymbolAddress), and that pointer is what the kernels get.
+static __device__ __align__(256) unsigned char g_static_scratch[MSR_STATIC_SCRATCH_BYTES];
+
+namespace msr {
+
+constexpr int kStaticMaxDevices = 64;
+static std::atomic<unsigned char*> g_static_ptr[kStaticMaxDevices];
+
+// device address of g_static_scratch on the CURRENT device (the caller has made h->device current)
+static int static_scratch_ptr(int device, unsigned char** out) {
+    MSR_REQUIRE(device >= 0 && device < kStaticMaxDevices, "msr_dense_search_static: device %d outside [0,%d)", device, kStaticMaxDevices);
+    unsigned char* p = g_static_ptr[device].load(std::memory_order_acquire);
+    if (!p) {
+        void* sym = nullptr;
+        MSR_CUDA_CHECK(cudaGetSymbolAddress(&sym, g_static_scratch));
+        MSR_REQUIRE(sym != nullptr, "msr_dense_search_static: cudaGetSymbolAddress returned NULL on device %d", device);
+        p = (unsigned char*)sym;
+        g_static_ptr[device].store(p, std::memory_order_release);   // racing threads store the same address
+    }
+    *out = p;
+    return MSR_OK;
+}
+
+}  // namespace msr
+
+extern "C" int msr_dense_search_static(msr_dense_index* h, uint32_t nq, const float* queries, uint32_t k, float* out_scores,
+                                       int64_t* out_ids, void* stream) {
+    MSR_REQUIRE(h, "msr_dense_search_static: NULL handle");
+    MSR_REQUIRE(k >= 1 && k <= MSR_MAX_K, "msr_dense_search_static: k=%u outside [1,%u]", k, MSR_MAX_K);
+    MSR_REQUIRE(h->n_docs > 0, "msr_dense_search_static: the index is empty");
+    // one group of kIpQ score rows + its top-k staging must fit the static array (dense_search_exact then walks the
+    // queries in passes of as many rows as fit)
+    const size_t per_q = align_up(h->n_docs, 4) * 4 + (size_t)std::min(k, h->n_docs) * 8 + 4;
+    const size_t need = per_q * kIpQ + 4096;
+    MSR_REQUIRE(need <= (size_t)MSR_STATIC_SCRATCH_BYTES,
+                "msr_dense_search_static: n_docs=%u, k=%u need %zu bytes of scratch (%d score rows of n_docs fp32 + top-k staging), "
+                "the static array holds MSR_STATIC_SCRATCH_BYTES=%zu (n_docs <= ~%zu at this k); use msr_dense_search",
+                h->n_docs, k, need, kIpQ, (size_t)MSR_STATIC_SCRATCH_BYTES,
+                ((size_t)MSR_STATIC_SCRATCH_BYTES - 4096) / kIpQ / 4 - (size_t)std::min(k, h->n_docs) * 2 - 4);
+    if (nq == 0) return MSR_OK;
+    MSR_REQUIRE(queries && out_scores && out_ids, "msr_dense_search_static: NULL buffer");
+    int rc = use_device(h->device);
+    if (rc) return rc;
+    unsigned char* scratch = nullptr;
+    rc = static_scratch_ptr(h->device, &scratch);
+    if (rc) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    // Nothing in the scratch is read before this call has written it (score rows: every doc column of every row of a pass;
+    // staging lists and counts: written by the row top-k before the finishing kernel reads them), so the last call's
+    // contents are harmless.  The per-row count words are the one thing a reader could take for carried-over state: they
+    // start at zero anyway (same layout arithmetic as dense_search_exact).
+    {
+        const size_t row_stride = align_up(h->n_docs, 4), kk = std::min(k, h->n_docs);
+        size_t qc = std::min<size_t>(nq, std::max<size_t>(1, ((size_t)MSR_STATIC_SCRATCH_BYTES - 1024) / per_q));
+        if (qc >= (size_t)kIpQ) qc = qc / kIpQ * kIpQ;
+        const size_t off_counts = align_up(qc * row_stride * 4, 256) + 2 * align_up(qc * kk * 4, 256);
+        MSR_CUDA_CHECK(cudaMemsetAsync(scratch + off_counts, 0, qc * 4, s));
+    }
+    return dense_search_exact(h, nq, queries, k, out_scores, out_ids, scratch, (size_t)MSR_STATIC_SCRATCH_BYTES, s);
+}

@@ -305,6 +305,20 @@ class DenseIndex:
                                                   current_stream_ptr(self.device)))
         return out[:, :n]
 
+    def search_static(self, queries, k, out):
+        """msr_dense_search_static: the exact pass (mode 1) with its scratch in libmsr.so's static device array -- the call
+        itself allocates nothing, so the CALLER passes everything: ``queries`` a contiguous CUDA fp32 tensor [nq,dim],
+        ``out`` = (scores f32 [nq,k], ids i64 [nq,k]) contiguous CUDA tensors.  No counterpart in the reference.
+        Raises when the index is too large for MSR_STATIC_SCRATCH_BYTES."""
+        assert queries.is_cuda and queries.dtype == torch.float32 and queries.is_contiguous() and queries.shape[1] == self.dim
+        nq = int(queries.shape[0])
+        s, i = out
+        assert s.is_cuda and i.is_cuda and s.dtype == torch.float32 and i.dtype == torch.int64
+        assert s.is_contiguous() and i.is_contiguous() and tuple(s.shape) == (nq, k) and tuple(i.shape) == (nq, k)
+        check(_lib.load().msr_dense_search_static(self._h, nq, ptr(queries), int(k), ptr(s), ptr(i),
+                                                  current_stream_ptr(self.device)))
+        return out
+
     def search(self, queries, k, mode=0, out=None):
         """numpy / CPU tensor in -> host arrays out (host path, H2D + D2H inside the call); CUDA tensor in -> CUDA
         tensors out (device path).  ``out`` = preallocated (scores, ids) of the matching kind."""
