@@ -659,10 +659,11 @@ sparse_score_topk_kernel(const SearchParams P) {
         const uint32_t cap = min(P.k_stride, (uint32_t)kUnionMax);
         const uint32_t nvec = tlp >> 2;                          // 4 positions per thread and step
 #ifndef MSR_THETA_UNROLL
-#define MSR_THETA_UNROLL 1
+#define MSR_THETA_UNROLL 2
 #endif
         // MSR_THETA_UNROLL independent 16-byte accumulator loads per step before any is tested (the pass is shared-memory
-        // latency-bound: 10 % of the samples for 5 % of the instructions)
+        // latency-bound: 10 % of the samples for 5 % of the instructions).  Measured (profiles/r2_theta_unroll_ab.txt):
+        // 1 -> 19.278 ms, 2 -> 19.236 ms, 4 -> 19.283 ms per scorer launch on config 4, repeatable to 0.003 ms.
         for (uint32_t j0 = tid; j0 < nvec; j0 += MSR_THETA_UNROLL * kThreads) {
             uint4 xs[MSR_THETA_UNROLL];
 #pragma unroll
