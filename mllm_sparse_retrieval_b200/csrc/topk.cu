@@ -427,8 +427,63 @@ __device__ __forceinline__ float row_load(const float* r, uint32_t i) { return r
 __device__ __forceinline__ float row_load(const __half* r, uint32_t i) { return __half2float(r[i]); }
 __device__ __forceinline__ float row_load(const __nv_bfloat16* r, uint32_t i) { return __bfloat162float(r[i]); }
 
+#ifndef MSR_ROW_INFLIGHT
+#define MSR_ROW_INFLIGHT 2
+#endif
+// 16 bytes of a row -> floats
+__device__ __forceinline__ void row_unpack(const float*, const uint4 x, float (&v)[4]) {
+    v[0] = __uint_as_float(x.x); v[1] = __uint_as_float(x.y); v[2] = __uint_as_float(x.z); v[3] = __uint_as_float(x.w);
+}
+__device__ __forceinline__ void row_unpack(const __half*, const uint4 x, float (&v)[8]) {
+    const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        v[2 * j] = __half2float(__ushort_as_half((unsigned short)(w[j] & 0xFFFFu)));
+        v[2 * j + 1] = __half2float(__ushort_as_half((unsigned short)(w[j] >> 16)));
+    }
+}
+__device__ __forceinline__ void row_unpack(const __nv_bfloat16*, const uint4 x, float (&v)[8]) {
+    const uint32_t w[4] = {x.x, x.y, x.z, x.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { v[2 * j] = __uint_as_float(w[j] << 16); v[2 * j + 1] = __uint_as_float(w[j] & 0xFFFF0000u); }
+}
+
+// f(i, row[i]) for every i < n, each element once, over the whole CTA: 16-byte loads (MSR_ROW_INFLIGHT in flight per thread) over the
+// aligned body of the row, scalar loads for the few elements before and after it.  A pass over a 131 072-wide fp16 row
+// with one 2-byte load per thread and step moved 64 bytes per warp instruction; this moves 512.
+template <typename T, typename F>
+__device__ __forceinline__ void row_for_each(const T* __restrict__ row, const uint32_t n, const uint32_t tid, F&& f) {
+    constexpr uint32_t VEC = 16 / sizeof(T);
+    const uint32_t mis = (uint32_t)((reinterpret_cast<uintptr_t>(row) & 15u) / sizeof(T));
+    const uint32_t head = mis ? min(n, VEC - mis) : 0u;
+    if (tid < head) f(tid, row_load(row, tid));
+    const uint32_t nv = (n - head) / VEC;
+    const uint4* __restrict__ v = reinterpret_cast<const uint4*>(row + head);
+    constexpr int kInFlight = MSR_ROW_INFLIGHT;                    // independent 16-byte loads per thread and step
+    for (uint32_t j = tid; j < nv; j += kInFlight * kRowThreads) {
+        uint4 x[kInFlight];
+#pragma unroll
+        for (int t = 0; t < kInFlight; ++t) {
+            const uint32_t jt = j + t * kRowThreads;
+            x[t] = jt < nv ? __ldg(v + jt) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int t = 0; t < kInFlight; ++t) {
+            const uint32_t jt = j + t * kRowThreads;
+            if (jt < nv) {
+                float e[VEC];
+                row_unpack(row, x[t], e);
+#pragma unroll
+                for (uint32_t u = 0; u < VEC; ++u) f(head + jt * VEC + u, e[u]);
+            }
+        }
+    }
+    const uint32_t done = head + nv * VEC;
+    if (done + tid < n) f(done + tid, row_load(row, done + tid));
+}
+
 template <typename T>
-__global__ void __launch_bounds__(kRowThreads)
+__global__ void __launch_bounds__(kRowThreads, MSR_ROW_INFLIGHT > 2 ? 2 : 1)
 topk_rows_kernel(const RowsParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     RowsSmem* S = reinterpret_cast<RowsSmem*>(smem_raw);
@@ -441,12 +496,15 @@ topk_rows_kernel(const RowsParams P) {
     if (tid == 0) { S->vmax = 0; S->hits = 0; S->out_cnt = 0; S->cand_cnt = 0; }
     __syncthreads();
     {
-        uint32_t m = 0, h = 0;
-        for (uint32_t i = tid; i < n; i += kRowThreads) {
-            uint32_t kx = row_key(row_load(row, i));
-            m = max(m, kx);
-            h += (kx != 0);
-        }
+        // max and count of the rankable values (x > -inf; NaN fails the test and fmaxf skips it): two float ops per element,
+        // the key of the maximum is taken once at the end (max.f32 orders +0 above -0, as the keys do)
+        float mf = -INFINITY;
+        uint32_t h = 0;
+        row_for_each(row, n, tid, [&](uint32_t, float x) {
+            mf = fmaxf(mf, x);
+            h += (x > -INFINITY);
+        });
+        uint32_t m = row_key(mf);
         m = warp_reduce_max(m);
         h = warp_reduce_add(h);
         if (lane == 0) {
@@ -461,10 +519,9 @@ topk_rows_kernel(const RowsParams P) {
     for (uint32_t i = tid; i < n2out; i += kRowThreads) outk[i] = 0;
     __syncthreads();
     if (hits > 0 && hits <= P.k) {
-        for (uint32_t i = tid; i < n; i += kRowThreads) {
-            float x = row_load(row, i);
+        row_for_each(row, n, tid, [&](uint32_t i, float x) {
             if (row_key(x)) outk[atomicAdd(&S->out_cnt, 1u)] = make_key(x, (uint32_t)(P.col_base + (int32_t)i));
-        }
+        });
     } else if (hits > 0) {
         uint32_t remaining = kq, sh_prev = 32 - __clz(kmax), pref = 0, s = 0, cand_count = 0;
         for (;;) {
@@ -472,13 +529,24 @@ topk_rows_kernel(const RowsParams P) {
             const uint32_t width = sh_prev - s;
             for (uint32_t i = tid; i < kRowBins; i += kRowThreads) S->hist[i] = 0;
             __syncthreads();
-            for (uint32_t i = tid; i < n; i += kRowThreads) {
-                uint32_t kx = row_key(row_load(row, i));
+            // exact zeros (relu'd activation rows are mostly zeros) are counted in a register: one shared atomic per warp
+            // instead of one per element on a single address
+            const uint32_t kzero = f2ord(0.0f);
+            uint32_t zc = 0;
+            row_for_each(row, n, tid, [&](uint32_t, float x) {
+                if (__float_as_uint(x) == 0u) { ++zc; return; }       // +0.0 (its key is kzero)
+                const uint32_t kx = row_key(x);
                 if (kx) {
-                    uint32_t d = kmax - kx;
-                    uint32_t hi = sh_prev >= 32 ? 0u : (d >> sh_prev);
+                    const uint32_t d = kmax - kx;
+                    const uint32_t hi = sh_prev >= 32 ? 0u : (d >> sh_prev);
                     if (hi == pref) atomicAdd(&S->hist[(d >> s) & ((1u << width) - 1u)], 1u);
                 }
+            });
+            zc = warp_reduce_add(zc);
+            if (lane == 0 && zc && kzero <= kmax) {
+                const uint32_t d = kmax - kzero;
+                const uint32_t hi = sh_prev >= 32 ? 0u : (d >> sh_prev);
+                if (hi == pref) atomicAdd(&S->hist[(d >> s) & ((1u << width) - 1u)], zc);
             }
             __syncthreads();
             {
@@ -504,16 +572,21 @@ topk_rows_kernel(const RowsParams P) {
         }
         const uint32_t n_def = kq - remaining;
         const bool collect = cand_count <= (uint32_t)kRowCandMax;
-        for (uint32_t i = tid; i < n; i += kRowThreads) {
-            float xv = row_load(row, i);
-            uint32_t kx = row_key(xv);
+        // d >> s <= pref  <=>  d <= dmax  <=>  key >= kmax - dmax: one float compare rejects almost every element (keys are
+        // monotone in the value; NaN fails the compare, -inf has key 0 and is tested below)
+        const uint64_t dmax64 = (((uint64_t)pref + 1) << s) - 1;
+        const uint32_t klow = dmax64 >= (uint64_t)kmax ? 0u : kmax - (uint32_t)dmax64;
+        const float xlow = klow ? ord2f(klow) : -INFINITY;
+        row_for_each(row, n, tid, [&](uint32_t i, float xv) {
+            if (!(xv >= xlow)) return;
+            const uint32_t kx = row_key(xv);
             if (kx) {
-                uint32_t d = kmax - kx;
-                uint32_t x = d >> s;
+                const uint32_t d = kmax - kx;
+                const uint32_t x = d >> s;
                 if (x < pref) outk[atomicAdd(&S->out_cnt, 1u)] = make_key(xv, (uint32_t)(P.col_base + (int32_t)i));
                 else if (x == pref && collect) S->cand[atomicAdd(&S->cand_cnt, 1u)] = ~(((uint64_t)d << 32) | i);
             }
-        }
+        });
         __syncthreads();
         if (collect) {
             uint32_t n2 = pow2_ceil(cand_count);
