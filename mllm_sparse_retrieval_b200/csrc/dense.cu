@@ -81,63 +81,78 @@ __global__ void dense_convert_kernel(const float* __restrict__ src, __half* __re
     }
 }
 
-// Exact pass: one warp per doc row, kIpQ queries per pass resident in shared memory.  Each lane accumulates its
+// Exact pass: one warp per doc row, NQ (1, 2 or kIpQ) queries per pass resident in shared memory.  Each lane accumulates its
 // strided elements in ascending order with one fmaf chain per query, then a fixed xor-shuffle tree: the result is
-// deterministic and independent of nq / batch composition.
+// deterministic and independent of nq / batch composition / NQ.  A lane issues kIpLoads independent 16-byte loads of the
+// row before it uses the first (the pass is an HBM stream: 410 MB at the reference's own batch sizes of 1-4 queries).
+template <int NQ>
 __global__ void __launch_bounds__(kIpThreads)
 dense_ip_exact_kernel(const float* __restrict__ docs, uint32_t n_docs, uint32_t dim, const float* __restrict__ queries,
                       uint32_t nq, float* __restrict__ scores, size_t row_stride, const uint32_t* __restrict__ nq_dev,
                       uint32_t nq_off) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    float* qs = reinterpret_cast<float*>(smem_raw);           // [kIpQ][dim]
+    float* qs = reinterpret_cast<float*>(smem_raw);           // [NQ][dim]
     if (nq_dev) {                                             // the count lives on the device (mode-2 fallback list)
         const uint32_t have = *nq_dev;
         nq = min(nq, have > nq_off ? have - nq_off : 0u);
     }
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const bool vec = (dim & 3) == 0;
-    // groups of kIpQ queries: one per blockIdx.y, or (device-counted launches: gridDim.y == 1) all of them in turn, so that an
+    constexpr int kIpLoads = NQ > 2 ? 4 : 8;
+    // groups of NQ queries: one per blockIdx.y, or (device-counted launches: gridDim.y == 1) all of them in turn, so that an
     // empty list costs one wave of no-op CTAs and a listed query still gets the whole chip's bandwidth
-    for (uint32_t q0 = blockIdx.y * kIpQ; q0 < nq; q0 += gridDim.y * kIpQ) {
-    const uint32_t nqb = min((uint32_t)kIpQ, nq - q0);
+    for (uint32_t q0 = blockIdx.y * NQ; q0 < nq; q0 += gridDim.y * NQ) {
+    const uint32_t nqb = min((uint32_t)NQ, nq - q0);
     __syncthreads();                                          // the previous group's queries are no longer read
-    for (uint32_t i = threadIdx.x; i < kIpQ * dim; i += kIpThreads) {
+    for (uint32_t i = threadIdx.x; i < NQ * dim; i += kIpThreads) {
         uint32_t qq = i / dim;
         qs[i] = qq < nqb ? queries[(size_t)(q0 + qq) * dim + (i - qq * dim)] : 0.f;
     }
     __syncthreads();
     for (uint32_t row = blockIdx.x * kIpWarps + warp; row < n_docs; row += gridDim.x * kIpWarps) {
         const float* d = docs + (size_t)row * dim;
-        float acc[kIpQ];
+        float acc[NQ];
 #pragma unroll
-        for (int j = 0; j < kIpQ; ++j) acc[j] = 0.f;
+        for (int j = 0; j < NQ; ++j) acc[j] = 0.f;
         if (vec) {
             const float4* d4 = reinterpret_cast<const float4*>(d);
-            for (uint32_t i = lane; i < dim / 4; i += 32) {
-                float4 x = __ldg(d4 + i);
+            const uint32_t d4n = dim / 4;
+            for (uint32_t i0 = lane; i0 < d4n; i0 += 32 * kIpLoads) {
+                float4 x[kIpLoads];
 #pragma unroll
-                for (int j = 0; j < kIpQ; ++j) {
-                    float4 y = reinterpret_cast<const float4*>(qs + (size_t)j * dim)[i];
-                    acc[j] = fmaf(x.x, y.x, acc[j]); acc[j] = fmaf(x.y, y.y, acc[j]);
-                    acc[j] = fmaf(x.z, y.z, acc[j]); acc[j] = fmaf(x.w, y.w, acc[j]);
+                for (int u = 0; u < kIpLoads; ++u) {
+                    const uint32_t i = i0 + 32 * u;
+                    x[u] = i < d4n ? __ldg(d4 + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int u = 0; u < kIpLoads; ++u) {
+                    const uint32_t i = i0 + 32 * u;
+                    if (i < d4n) {
+#pragma unroll
+                        for (int j = 0; j < NQ; ++j) {
+                            const float4 y = reinterpret_cast<const float4*>(qs + (size_t)j * dim)[i];
+                            acc[j] = fmaf(x[u].x, y.x, acc[j]); acc[j] = fmaf(x[u].y, y.y, acc[j]);
+                            acc[j] = fmaf(x[u].z, y.z, acc[j]); acc[j] = fmaf(x[u].w, y.w, acc[j]);
+                        }
+                    }
                 }
             }
         } else {
             for (uint32_t i = lane; i < dim; i += 32) {
                 float x = __ldg(d + i);
 #pragma unroll
-                for (int j = 0; j < kIpQ; ++j) acc[j] = fmaf(x, qs[(size_t)j * dim + i], acc[j]);
+                for (int j = 0; j < NQ; ++j) acc[j] = fmaf(x, qs[(size_t)j * dim + i], acc[j]);
             }
         }
 #pragma unroll
-        for (int j = 0; j < kIpQ; ++j) {
+        for (int j = 0; j < NQ; ++j) {
 #pragma unroll
             for (int o = 16; o > 0; o >>= 1) acc[j] += __shfl_xor_sync(0xffffffffu, acc[j], o);
         }
         if (lane < nqb) {
             float v = acc[0];
 #pragma unroll
-            for (int j = 1; j < kIpQ; ++j) if ((int)lane == j) v = acc[j];
+            for (int j = 1; j < NQ; ++j) if ((int)lane == j) v = acc[j];
             scores[(size_t)(q0 + lane) * row_stride + row] = v;
         }
     }
@@ -255,18 +270,26 @@ static int dense_search_exact(msr_dense_index* h, uint32_t nq, const float* d_q,
     float* ts = (float*)(scratch + align_up((size_t)qc * row_stride * 4, 256));
     int32_t* td = (int32_t*)((unsigned char*)ts + align_up((size_t)qc * kk * 4, 256));
     uint32_t* tc = (uint32_t*)((unsigned char*)td + align_up((size_t)qc * kk * 4, 256));
-    const size_t smem = (size_t)kIpQ * h->dim * 4;
+    // queries per pass of the kernel: 1 or 2 for the reference's own batch sizes (less shared memory, more CTAs per SM, no
+    // multiplications by zero rows), else kIpQ
+    const uint32_t gq = nq_dev ? (uint32_t)kIpQ : (nq == 1 ? 1u : nq == 2 ? 2u : (uint32_t)kIpQ);
+    const size_t smem = (size_t)gq * h->dim * 4;
     static std::atomic<uint64_t> attr_set{0};
     if (attr_needed(attr_set)) {
-        MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_ip_exact_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kIpQ * 8192 * 4));
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_ip_exact_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 1 * 8192 * 4));
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_ip_exact_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * 8192 * 4));
+        MSR_CUDA_CHECK(cudaFuncSetAttribute(dense_ip_exact_kernel<kIpQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, kIpQ * 8192 * 4));
         attr_mark(attr_set);
     }
     for (uint32_t q0 = 0; q0 < nq; q0 += qc) {
         const uint32_t n = std::min(qc, nq - q0);
         // device-counted launches (mode-2 fallback, usually empty): ONE grid row that walks the listed query groups itself --
         // an empty list is one wave of no-op CTAs, a listed query is answered at the full width of the chip
-        dim3 grid(std::min<uint32_t>((h->n_docs + kIpWarps - 1) / kIpWarps, 148 * 8), nq_dev ? 1 : (n + kIpQ - 1) / kIpQ);
-        dense_ip_exact_kernel<<<grid, kIpThreads, smem, s>>>(h->v32, h->n_docs, h->dim, d_q + (size_t)q0 * h->dim, n, rows, row_stride, nq_dev, q0);
+        dim3 grid(std::min<uint32_t>((h->n_docs + kIpWarps - 1) / kIpWarps, 148 * 8), nq_dev ? 1 : (n + gq - 1) / gq);
+        const float* qp = d_q + (size_t)q0 * h->dim;
+        if (gq == 1) dense_ip_exact_kernel<1><<<grid, kIpThreads, smem, s>>>(h->v32, h->n_docs, h->dim, qp, n, rows, row_stride, nq_dev, q0);
+        else if (gq == 2) dense_ip_exact_kernel<2><<<grid, kIpThreads, smem, s>>>(h->v32, h->n_docs, h->dim, qp, n, rows, row_stride, nq_dev, q0);
+        else dense_ip_exact_kernel<kIpQ><<<grid, kIpThreads, smem, s>>>(h->v32, h->n_docs, h->dim, qp, n, rows, row_stride, nq_dev, q0);
         count_launch();
         MSR_CUDA_CHECK(cudaGetLastError());
         int rc = topk_rows_launch(n, h->n_docs, rows, row_stride, kk, h->doc_base, ts, td, tc, s, nq_dev, q0);
@@ -403,7 +426,9 @@ dense_rescore_kernel(const float* __restrict__ docs, uint32_t dim, int32_t doc_b
     __syncthreads();
     const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int32_t* mine = cand + (size_t)q * cap;
-    for (uint32_t r0 = warp * kRsPer; r0 < n; r0 += kRsWarps * kRsPer) {
+    // gridDim.y CTAs share a query's candidates (small batches: one CTA per query left most SMs idle -- 16 queries at depth
+    // 1000 took 1.0 ms here); every candidate is still scored by one warp in the same order
+    for (uint32_t r0 = (blockIdx.y * kRsWarps + warp) * kRsPer; r0 < n; r0 += gridDim.y * kRsWarps * kRsPer) {
         const float4* d4[kRsPer];
         float acc[kRsPer];
 #pragma unroll
@@ -596,7 +621,8 @@ static int dense_search_tc(msr_dense_index* h, uint32_t nq, const float* d_q, ui
         dense_select_kernel<<<n, kSelThreads, (size_t)L.cap * 8, s>>>(cand, cnt, L.cap, thr, qn, qe, h->stats, L.kk, h->n_docs,
                                                                       h->dim, h->doc_base, cd, ccnt, d_flags);
         if (h->profiling) MSR_CUDA_CHECK(cudaEventRecord(h->ev[2], s));
-        dense_rescore_kernel<<<n, kRsThreads, (size_t)h->dim * 4, s>>>(h->v32, h->dim, h->doc_base, q, cd, ccnt, L.cap, es);
+        const uint32_t rs_split = std::max<uint32_t>(1, std::min<uint32_t>(16, (2 * 148 + n - 1) / n));
+        dense_rescore_kernel<<<dim3(n, rs_split), kRsThreads, (size_t)h->dim * 4, s>>>(h->v32, h->dim, h->doc_base, q, cd, ccnt, L.cap, es);
         if (h->profiling) MSR_CUDA_CHECK(cudaEventRecord(h->ev[3], s));
         dense_final_kernel<<<n, kSelThreads, (size_t)L.cap * 8, s>>>(es, cd, ccnt, L.cap, k, d_os + (size_t)q0 * k,
                                                                      d_oi + (size_t)q0 * k);
