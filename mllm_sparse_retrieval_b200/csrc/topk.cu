@@ -430,6 +430,9 @@ __device__ __forceinline__ float row_load(const __nv_bfloat16* r, uint32_t i) { 
 #ifndef MSR_ROW_INFLIGHT
 #define MSR_ROW_INFLIGHT 2
 #endif
+#ifndef MSR_ROW_MINBLOCKS
+#define MSR_ROW_MINBLOCKS 4      // CTAs of 512 threads per SM the register allocation leaves room for (A/B: profiles/r2_rows_ab2.txt)
+#endif
 // 16 bytes of a row -> floats
 __device__ __forceinline__ void row_unpack(const float*, const uint4 x, float (&v)[4]) {
     v[0] = __uint_as_float(x.x); v[1] = __uint_as_float(x.y); v[2] = __uint_as_float(x.z); v[3] = __uint_as_float(x.w);
@@ -483,7 +486,7 @@ __device__ __forceinline__ void row_for_each(const T* __restrict__ row, const ui
 }
 
 template <typename T>
-__global__ void __launch_bounds__(kRowThreads, MSR_ROW_INFLIGHT > 2 ? 2 : 1)
+__global__ void __launch_bounds__(kRowThreads, MSR_ROW_MINBLOCKS)
 topk_rows_kernel(const RowsParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     RowsSmem* S = reinterpret_cast<RowsSmem*>(smem_raw);
@@ -494,22 +497,34 @@ topk_rows_kernel(const RowsParams P) {
     const T* row = reinterpret_cast<const T*>(P.scores) + (size_t)q * P.row_stride;
     const uint32_t n = P.n;
     if (tid == 0) { S->vmax = 0; S->hits = 0; S->out_cnt = 0; S->cand_cnt = 0; }
+    for (uint32_t i = tid; i < kRowBins; i += kRowThreads) S->hist[i] = 0;
     __syncthreads();
+    constexpr uint32_t kCoarseShift = 32 - kRowBinBits;          // coarse bin = top 11 bits of the key: sign, exponent, 2 mantissa bits
     {
-        // max and count of the rankable values (x > -inf; NaN fails the test and fmaxf skips it): two float ops per element,
-        // the key of the maximum is taken once at the end (max.f32 orders +0 above -0, as the keys do)
+        // One pass finds the maximum, the count of the rankable values (x > -inf; NaN fails the test) AND a first histogram,
+        // over the ABSOLUTE key bits (index 0 = largest values): when the bin of the k-th value holds few enough candidates
+        // the collecting pass follows at once -- two reads of the row instead of three.  Exact +0.0 (relu'd activation rows
+        // are mostly zeros) is counted in a register: one shared atomic per warp instead of one per element on one address.
         float mf = -INFINITY;
-        uint32_t h = 0;
+        uint32_t h = 0, zc = 0;
         row_for_each(row, n, tid, [&](uint32_t, float x) {
-            mf = fmaxf(mf, x);
-            h += (x > -INFINITY);
+            if (__float_as_uint(x) == 0u) { ++zc; return; }
+            if (x > -INFINITY) {
+                mf = fmaxf(mf, x);                              // max.f32 orders +0 above -0, as the keys do
+                ++h;
+                atomicAdd(&S->hist[(kRowBins - 1) - (f2ord(x) >> kCoarseShift)], 1u);
+            }
         });
+        if (zc) mf = fmaxf(mf, 0.0f);
+        h += zc;
         uint32_t m = row_key(mf);
         m = warp_reduce_max(m);
         h = warp_reduce_add(h);
+        zc = warp_reduce_add(zc);
         if (lane == 0) {
             if (m) atomicMax(&S->vmax, m);
             if (h) atomicAdd(&S->hits, h);
+            if (zc) atomicAdd(&S->hist[(kRowBins - 1) - (f2ord(0.0f) >> kCoarseShift)], zc);
         }
     }
     __syncthreads();
@@ -524,7 +539,36 @@ topk_rows_kernel(const RowsParams P) {
         });
     } else if (hits > 0) {
         uint32_t remaining = kq, sh_prev = 32 - __clz(kmax), pref = 0, s = 0, cand_count = 0;
-        for (;;) {
+        // keys >= k_def are certainly among the top kq, keys in [k_cand, k_def) are the candidates for the remaining places
+        uint64_t k_def = 0;
+        uint32_t k_cand = 0;
+        bool coarse;
+        {
+            // the coarse histogram of pass 1: bin of the kq-th largest value
+            uint32_t h4[4], ls = 0;
+#pragma unroll
+            for (int j = 0; j < 4; ++j) { h4[j] = S->hist[tid * 4 + j]; ls += h4[j]; }
+            uint32_t total;
+            uint32_t ex = rows_block_excl_scan(ls, S->wsum, &total);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                if (ex < remaining && ex + h4[j] >= remaining) {
+                    S->sel_b = tid * 4 + j; S->sel_clt = ex; S->sel_bcount = h4[j];
+                }
+                ex += h4[j];
+            }
+            __syncthreads();
+            coarse = S->sel_bcount <= (uint32_t)kRowCandMax;
+            if (coarse) {
+                const uint32_t bin = (kRowBins - 1) - S->sel_b;
+                remaining -= S->sel_clt;
+                cand_count = S->sel_bcount;
+                k_def = ((uint64_t)bin + 1) << kCoarseShift;
+                k_cand = max(bin << kCoarseShift, 1u);
+            }
+            __syncthreads();                                    // sel_* and hist are rewritten below
+        }
+        while (!coarse) {
             s = sh_prev > kRowBinBits ? sh_prev - kRowBinBits : 0;
             const uint32_t width = sh_prev - s;
             for (uint32_t i = tid; i < kRowBins; i += kRowThreads) S->hist[i] = 0;
@@ -568,24 +612,25 @@ topk_rows_kernel(const RowsParams P) {
             pref = (width >= 32 ? 0u : (pref << width)) | S->sel_b;
             sh_prev = s;
             cand_count = S->sel_bcount;
-            if (cand_count <= (uint32_t)kRowCandMax || s == 0) break;
+            if (cand_count <= (uint32_t)kRowCandMax || s == 0) {
+                // d >> s < pref  <=>  key > kmax - (pref << s);   d >> s == pref  <=>  key >= kmax - (((pref + 1) << s) - 1)
+                const uint64_t dlo = (uint64_t)pref << s, dhi = (((uint64_t)pref + 1) << s) - 1;
+                k_def = dlo > (uint64_t)kmax ? 0ull : (uint64_t)kmax - dlo + 1;
+                k_cand = dhi >= (uint64_t)kmax ? 1u : max(kmax - (uint32_t)dhi, 1u);
+                break;
+            }
         }
         const uint32_t n_def = kq - remaining;
         const bool collect = cand_count <= (uint32_t)kRowCandMax;
-        // d >> s <= pref  <=>  d <= dmax  <=>  key >= kmax - dmax: one float compare rejects almost every element (keys are
-        // monotone in the value; NaN fails the compare, -inf has key 0 and is tested below)
-        const uint64_t dmax64 = (((uint64_t)pref + 1) << s) - 1;
-        const uint32_t klow = dmax64 >= (uint64_t)kmax ? 0u : kmax - (uint32_t)dmax64;
-        const float xlow = klow ? ord2f(klow) : -INFINITY;
+        // one float compare rejects almost every element: keys are monotone in the value, NaN fails the compare, and the
+        // bound is at least the key of -FLT_MAX, so -inf (key 0, never returned) fails it too
+        k_cand = max(k_cand, 0x00800000u);
+        const float xlow = ord2f(k_cand);
         row_for_each(row, n, tid, [&](uint32_t i, float xv) {
             if (!(xv >= xlow)) return;
             const uint32_t kx = row_key(xv);
-            if (kx) {
-                const uint32_t d = kmax - kx;
-                const uint32_t x = d >> s;
-                if (x < pref) outk[atomicAdd(&S->out_cnt, 1u)] = make_key(xv, (uint32_t)(P.col_base + (int32_t)i));
-                else if (x == pref && collect) S->cand[atomicAdd(&S->cand_cnt, 1u)] = ~(((uint64_t)d << 32) | i);
-            }
+            if ((uint64_t)kx >= k_def) outk[atomicAdd(&S->out_cnt, 1u)] = make_key(xv, (uint32_t)(P.col_base + (int32_t)i));
+            else if (kx >= k_cand && collect) S->cand[atomicAdd(&S->cand_cnt, 1u)] = ~(((uint64_t)(kmax - kx) << 32) | i);
         });
         __syncthreads();
         if (collect) {
