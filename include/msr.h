@@ -223,6 +223,8 @@ int msr_dense_index_info(const msr_dense_index* h, uint32_t info[5]);
  * accumulated in a fixed order (|err| <= 1e-6 abs on unit vectors), out_ids int64 [nq,k] (FAISS convention:
  * -1 / -3.4028235e38 padding when k > n_docs).  Order = score desc, id asc.
  * mode: 0 = auto, 1 = exact fp32 CUDA-core pass only, 2 = tcgen05 fp16 pass + certified fp32 re-score.
+ * Auto is a cost rule only (the results are the same bits): mode 2 for nq >= 8, or when the fp16 copy of the index is
+ * large enough that reading half the bytes outweighs mode 2's fixed cost (>= 800 MB; >= 500 MB for nq >= 3); else mode 1.
  * Mode 2: approximate scores a(d) of all docs on the tensor cores with the selection FUSED into the GEMM epilogue (docs
  * with a(d) >= a per-query threshold, estimated from a strided sample of the index, are appended to a candidate buffer; no
  * score matrix is written).  With E = a Cauchy-Schwarz bound on |exact - a| from stored norms (fp16 rounding of both

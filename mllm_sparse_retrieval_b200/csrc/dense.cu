@@ -697,7 +697,13 @@ extern "C" int msr_dense_search(msr_dense_index* h, uint32_t nq, const float* qu
     int rc = use_device(h->device);
     if (rc) return rc;
     cudaStream_t s = (cudaStream_t)stream;
-    bool use_tc = mode == 2 || (mode == 0 && nq >= 16 && h->n_docs >= 4096);
+    // mode 0: both paths return the same bits, so this is a pure cost rule (profiles/r2_dense_modes.txt, cold, top-100):
+    //   exact pass   ~ 50 us + 4 bytes per element per group of 4 queries   (25 000 x 4096: 112 / 138 / 224 us at nq 1 / 4 / 8)
+    //   tensor path  ~170 us + 2 bytes per element, any nq up to 128         (25 000 x 4096: 182-195 us; 1.25 M x 4096: 1.9 ms
+    //                                                                         against 3.4 ms exact at nq = 1)
+    const size_t bytes16 = (size_t)h->n_docs * h->dim * 2;
+    const bool tc_pays = nq >= 8 || (nq >= 3 && bytes16 >= ((size_t)500 << 20)) || bytes16 >= ((size_t)800 << 20);
+    bool use_tc = mode == 2 || (mode == 0 && h->n_docs >= 4096 && tc_pays);
     if (use_tc && h->dim % 8 != 0) {
         MSR_REQUIRE(mode != 2, "msr_dense_search: mode 2 needs dim %% 8 == 0 (TMA row pitch), dim is %u", h->dim);
         use_tc = false;
