@@ -381,6 +381,7 @@ constexpr int kRowWarps = kRowThreads / 32;
 constexpr int kRowBins = 2048;
 constexpr int kRowBinBits = 11;
 constexpr int kRowCandMax = 1024;
+constexpr size_t kRowSumBytes = 32 * 1024 + 16;   // per-vector maxima kept by pass 1 (u16 each)
 
 struct RowsParams {
     uint32_t nq, n, k;
@@ -392,6 +393,8 @@ struct RowsParams {
     uint32_t* out_counts;
     const uint32_t* nq_dev;      // optional: rows [nq_off, *nq_dev) exist (count kept on the device); others are skipped
     uint32_t nq_off;
+    uint32_t sum_off, sum_cap;   // per-vector maxima of pass 1 (u16 key prefixes) at this byte offset of the dynamic shared
+                                 // memory, room for sum_cap vectors (0: none)
 };
 
 struct RowsSmem {
@@ -454,8 +457,10 @@ __device__ __forceinline__ void row_unpack(const __nv_bfloat16*, const uint4 x, 
 // f(i, row[i]) for every i < n, each element once, over the whole CTA: 16-byte loads (MSR_ROW_INFLIGHT in flight per thread) over the
 // aligned body of the row, scalar loads for the few elements before and after it.  A pass over a 131 072-wide fp16 row
 // with one 2-byte load per thread and step moved 64 bytes per warp instruction; this moves 512.
-template <typename T, typename F>
-__device__ __forceinline__ void row_for_each(const T* __restrict__ row, const uint32_t n, const uint32_t tid, F&& f) {
+// pre(j): load and visit 16-byte vector j of the body at all?   post(j, m): m = fmaxf over the vector's elements (NaN skipped).
+template <typename T, typename F, typename Pre, typename Post>
+__device__ __forceinline__ void row_for_each(const T* __restrict__ row, const uint32_t n, const uint32_t tid, F&& f, Pre&& pre,
+                                             Post&& post) {
     constexpr uint32_t VEC = 16 / sizeof(T);
     const uint32_t mis = (uint32_t)((reinterpret_cast<uintptr_t>(row) & 15u) / sizeof(T));
     const uint32_t head = mis ? min(n, VEC - mis) : 0u;
@@ -465,24 +470,40 @@ __device__ __forceinline__ void row_for_each(const T* __restrict__ row, const ui
     constexpr int kInFlight = MSR_ROW_INFLIGHT;                    // independent 16-byte loads per thread and step
     for (uint32_t j = tid; j < nv; j += kInFlight * kRowThreads) {
         uint4 x[kInFlight];
+        bool on[kInFlight];
 #pragma unroll
         for (int t = 0; t < kInFlight; ++t) {
             const uint32_t jt = j + t * kRowThreads;
-            x[t] = jt < nv ? __ldg(v + jt) : make_uint4(0, 0, 0, 0);
+            on[t] = jt < nv && pre(jt);
+            x[t] = on[t] ? __ldg(v + jt) : make_uint4(0, 0, 0, 0);
         }
 #pragma unroll
         for (int t = 0; t < kInFlight; ++t) {
             const uint32_t jt = j + t * kRowThreads;
-            if (jt < nv) {
+            if (on[t]) {
                 float e[VEC];
                 row_unpack(row, x[t], e);
+                float m = -INFINITY;
 #pragma unroll
-                for (uint32_t u = 0; u < VEC; ++u) f(head + jt * VEC + u, e[u]);
+                for (uint32_t u = 0; u < VEC; ++u) { f(head + jt * VEC + u, e[u]); m = fmaxf(m, e[u]); }
+                post(jt, m);
             }
         }
     }
     const uint32_t done = head + nv * VEC;
     if (done + tid < n) f(done + tid, row_load(row, done + tid));
+}
+template <typename T, typename F>
+__device__ __forceinline__ void row_for_each(const T* __restrict__ row, const uint32_t n, const uint32_t tid, F&& f) {
+    row_for_each(row, n, tid, f, [](uint32_t) { return true; }, [](uint32_t, float) {});
+}
+// number of 16-byte body vectors row_for_each visits
+template <typename T>
+__device__ __forceinline__ uint32_t row_body_vectors(const T* row, const uint32_t n) {
+    constexpr uint32_t VEC = 16 / sizeof(T);
+    const uint32_t mis = (uint32_t)((reinterpret_cast<uintptr_t>(row) & 15u) / sizeof(T));
+    const uint32_t head = mis ? min(n, VEC - mis) : 0u;
+    return (n - head) / VEC;
 }
 
 template <typename T>
@@ -496,6 +517,11 @@ topk_rows_kernel(const RowsParams P) {
     if (P.nq_dev && P.nq_off + q >= *P.nq_dev) return;
     const T* row = reinterpret_cast<const T*>(P.scores) + (size_t)q * P.row_stride;
     const uint32_t n = P.n;
+    // Pass 1 leaves the top 16 key bits of every 16-byte vector's maximum in shared memory (32 KB for a 131 072-wide fp16
+    // row); the collecting pass then loads only the vectors that can hold a candidate -- for activation rows a handful, so
+    // the row is read from HBM once instead of twice (the resident rows of all CTAs do not fit L2).
+    uint16_t* vsum = reinterpret_cast<uint16_t*>(smem_raw + P.sum_off);
+    const bool use_sum = P.sum_cap != 0 && row_body_vectors(row, n) <= P.sum_cap;
     if (tid == 0) { S->vmax = 0; S->hits = 0; S->out_cnt = 0; S->cand_cnt = 0; }
     for (uint32_t i = tid; i < kRowBins; i += kRowThreads) S->hist[i] = 0;
     __syncthreads();
@@ -514,7 +540,8 @@ topk_rows_kernel(const RowsParams P) {
                 ++h;
                 atomicAdd(&S->hist[(kRowBins - 1) - (f2ord(x) >> kCoarseShift)], 1u);
             }
-        });
+        }, [](uint32_t) { return true; },
+        [&](uint32_t j, float m) { if (use_sum) vsum[j] = (uint16_t)(row_key(m) >> 16); });
         if (zc) mf = fmaxf(mf, 0.0f);
         h += zc;
         uint32_t m = row_key(mf);
@@ -626,12 +653,13 @@ topk_rows_kernel(const RowsParams P) {
         // bound is at least the key of -FLT_MAX, so -inf (key 0, never returned) fails it too
         k_cand = max(k_cand, 0x00800000u);
         const float xlow = ord2f(k_cand);
+        const uint32_t kc16 = k_cand >> 16;                       // a vector whose maximum's key prefix is below holds no candidate
         row_for_each(row, n, tid, [&](uint32_t i, float xv) {
             if (!(xv >= xlow)) return;
             const uint32_t kx = row_key(xv);
             if ((uint64_t)kx >= k_def) outk[atomicAdd(&S->out_cnt, 1u)] = make_key(xv, (uint32_t)(P.col_base + (int32_t)i));
             else if (kx >= k_cand && collect) S->cand[atomicAdd(&S->cand_cnt, 1u)] = ~(((uint64_t)(kmax - kx) << 32) | i);
-        });
+        }, [&](uint32_t j) { return !use_sum || (uint32_t)vsum[j] >= kc16; }, [](uint32_t, float) {});
         __syncthreads();
         if (collect) {
             uint32_t n2 = pow2_ceil(cand_count);
@@ -699,10 +727,16 @@ int topk_rows_launch_typed(int dtype, uint32_t nq, uint32_t n, const void* score
     P.out_scores = out_scores; P.out_docs = out_docs; P.out_counts = out_counts;
     uint32_t n2 = 2;
     while (n2 < k) n2 <<= 1;
-    const size_t smem = sizeof(RowsSmem) + (size_t)n2 * 8;
+    // per-vector maxima of pass 1 behind the output keys when they fit 32 KB (rows up to 131 072 fp16 / 65 536 fp32 elements)
+    const size_t esz = dtype == 0 ? 4 : 2;
+    const size_t n_vec = (size_t)n * esz / 16 + 1;
+    const size_t off = sizeof(RowsSmem) + (size_t)n2 * 8;
+    P.sum_off = (uint32_t)off;
+    P.sum_cap = n_vec * 2 <= kRowSumBytes ? (uint32_t)n_vec : 0u;
+    const size_t smem = off + (P.sum_cap ? (size_t)P.sum_cap * 2 : 0);
     static std::atomic<uint64_t> attr_set{0};
     if (attr_needed(attr_set)) {
-        const int mx = (int)(sizeof(RowsSmem) + MSR_MAX_K * 8);
+        const int mx = (int)(sizeof(RowsSmem) + MSR_MAX_K * 8 + kRowSumBytes);
         MSR_CUDA_CHECK(cudaFuncSetAttribute(topk_rows_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
         MSR_CUDA_CHECK(cudaFuncSetAttribute(topk_rows_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
         MSR_CUDA_CHECK(cudaFuncSetAttribute(topk_rows_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, mx));
