@@ -469,8 +469,9 @@ def run_config5(a, rank, world, local_rank, root, ClockSampler):
            "scaling": "weak", "vs_baseline": None, "dtype": "u32", "data": "synthetic",
            "config": {"workload": f"synthetic {n_total}-doc sparse index ({per_gpu} docs/GPU, Zipf s=1, V={V}, {a.nnz_per_doc} nnz/doc, "
                                   f"{qs.nq} queries x {a.q_len} terms) + {H}-d dense flat-IP over the same {n_total} docs "
-                                  f"({a.c5_dense_nq} queries in batches of {dbatch}), top-{k}, doc-sharded x{world} with NCCL "
-                                  f"all-gather merge (BASELINE.json configs[4]; the named 10 M docs at 8 GPUs)",
+                                  f"({a.c5_dense_nq} queries in batches of {dbatch}), top-{k}, doc-sharded x{world}, lists exchanged by "
+                                  f"{'peer stores + one-warp barrier + merge' if px is not None else 'NCCL all-gather + merge'} "
+                                  f"(BASELINE.json configs[4]; the named 10 M docs at 8 GPUs)",
                       "docs_per_gpu": per_gpu, "n_docs": n_total, "nq": qs.nq, "k": k, "dense_nq": a.c5_dense_nq, "dim": H,
                       "l2": "per-GPU sparse index %d MB and dense index %d GB are larger than the 126 MB L2" %
                             (sidx.resident_bytes >> 20, per_gpu * H * 6 >> 30)},
